@@ -1,0 +1,233 @@
+/*
+ * mppi_b200.h — C ABI of libmppi_b200.so, a B200-native (sm_100a) MPPI engine.
+ *
+ * Drop-in boundary for the MPPI step of congkaishen/MotionPlanning
+ * (OptimalControl/MPPI).  The reference has no FFI; its boundary is the Julia
+ * function surface of OptimalControl/MPPI/src/setup.jl and MPPIUtils.jl.  Each
+ * entry point below names the reference interface (file:line, relative to the
+ * reference root) it replaces.  A Julia `ccall` shim over exactly these symbols
+ * is shown in INTEGRATION.md (julia/MPPIB200.jl); a ctypes twin lives in
+ * motionplanning_b200/_capi.py.
+ *
+ * Conventions
+ *   - every function returns int32_t status (MPPI_OK == 0) unless stated;
+ *   - never throws / aborts across the ABI; mppi_last_error() gives the text;
+ *   - all host-facing arrays are `double`, column-major (== Julia Matrix{Float64});
+ *     the one exception is the big noise tensor, whose element type follows
+ *     cfg.precision and whose shape is Julia (m, K, N) == C [N][K][m];
+ *   - the caller owns every buffer it passes, the library copies during the call
+ *     and keeps no host pointer; the library owns the handle and device memory;
+ *   - a handle is not thread-safe; distinct handles are independent.
+ */
+#ifndef MPPI_B200_H
+#define MPPI_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPPI_B200_VERSION 100 /* 0.1.0 */
+#define MPPI_MAX_NX 8
+#define MPPI_MAX_CIRCLES 64
+#define MPPI_MAX_BLOCKS 32
+#define MPPI_MAX_N 256
+
+/* status codes (the reference's only error path is error(...) in setup.jl:19-39) */
+enum {
+  MPPI_OK = 0,
+  MPPI_EINVAL = 1, /* bad sizes/values: setup.jl:19-39 checks + K/N/device ranges */
+  MPPI_ECUDA = 2,  /* CUDA runtime failure */
+  MPPI_ENCCL = 3,  /* NCCL failure / NCCL not loadable */
+  MPPI_ENOMEM = 4,
+  MPPI_ESTATE = 5  /* call order violated (e.g. get_costs before a step) */
+};
+
+/* vehicle model = which vehicledynamics.jl the reference would `include`
+ * (MPPIUtils.jl:3) */
+enum {
+  MPPI_MODEL_DYNAMIC7 = 0,  /* OptimalControl/MPPI/src/vehicledynamics.jl:1-54 */
+  MPPI_MODEL_KINEMATIC5 = 1 /* OptimalControl/Parking/src/VehicleModel.jl:1-21 */
+};
+enum { MPPI_FP32 = 0, MPPI_FP64 = 1 };
+enum {
+  MPPI_NOISE_SUPPLIED = 0, /* deterministic verification: host passes eps */
+  MPPI_NOISE_PHILOX = 1    /* in-kernel Philox4x32-10 + Box-Muller + chol(Sigma) */
+};
+/* planner = how the K rollouts are turned into a control:
+ *   MPPI : softmin-weighted mean of the clamped sampled controls (MPPIUtils.jl:154-203)
+ *   DWA  : constant control per candidate from a grid, arg-min selection
+ *          (OptimalControl/DynamicWindow/src/DWAUtils.jl:141-163) */
+enum { MPPI_PLANNER_MPPI = 0, MPPI_PLANNER_DWA = 1 };
+
+/* per-sample flag bits returned by mppi_get_flags */
+enum {
+  MPPI_FLAG_FEASIBLE = 1, /* all(constraint_his .== 1), MPPIUtils.jl:55 */
+  MPPI_FLAG_COLLIDED = 2, /* any ObstacleEvaluation hit, MPPIUtils.jl:125-126 / SAT */
+  MPPI_FLAG_OOB = 4       /* any BoundEvaluation hit, MPPIUtils.jl:139-148 */
+};
+
+/*
+ * POD configuration.  Fields mirror MPPISetting (types.jl:10-31) and the
+ * positional arguments of defineMPPI (setup.jl:3-17); the constants the
+ * reference hard-codes inside VehicleDynamics (vehicledynamics.jl:2-18,52),
+ * ObstacleEvaluation (MPPIUtils.jl:127) and TrajectoryRollout (MPPIUtils.jl:54)
+ * are explicit fields whose defaults (mppi_config_default) are those literals.
+ */
+typedef struct mppi_config {
+  uint32_t struct_size; /* = sizeof(mppi_config_t); ABI versioning */
+  int32_t model;        /* MPPI_MODEL_* */
+  int32_t n_x;          /* numStates: 7 (dynamic) or 5 (kinematic) */
+  int32_t m;            /* numControls: 2 (sr, ax) */
+  int32_t K;            /* SamplingNumber, global over all ranks */
+  int32_t N;            /* horizon steps */
+  int32_t B;            /* independent instances (batched mode); 1 otherwise */
+  int32_t precision;    /* MPPI_FP32 | MPPI_FP64 */
+  int32_t noise_mode;   /* MPPI_NOISE_* */
+  int32_t planner;      /* MPPI_PLANNER_* */
+  int32_t feasibility_count; /* types.jl:24 (1300); >= K disables the cut-off */
+  int32_t use_cuda_graph;    /* 1: one cudaGraphLaunch per step */
+  int32_t device;            /* CUDA device ordinal of this handle */
+  int32_t k_offset;          /* first global sample id owned by this handle */
+  int32_t K_local;           /* samples owned by this handle (0 => K) */
+  int32_t reserved0;
+  uint64_t seed;             /* Philox key */
+  double T;                  /* horizon seconds; dt = T/N (setup.jl:53) */
+  double lambda;             /* types.jl:28 */
+  double Sigma[4];           /* m x m covariance, column-major (setup.jl:56-57) */
+  double X0[MPPI_MAX_NX];
+  double goal[2];
+  double XL[MPPI_MAX_NX], XU[MPPI_MAX_NX];
+  double CL[2], CU[2];
+  double slack_penalty;    /* types.jl:30 = 1e5 */
+  double obstacle_penalty; /* MPPIUtils.jl:127 = 100*712.5 (DWA: 10000*712.5) */
+  double terminal_scale;   /* MPPIUtils.jl:54 = 1e4 */
+  /* vehicledynamics.jl:2-11 */
+  double la, lb, mass, Izz, g, mu, KFZF, KFZR, KFZX;
+  double tire[6];
+  double stage_w[6]; /* weights of v^2, r^2, ax^2, sr^2, sa^2, y^2 (:52) */
+  /* vehicle rectangle for SAT (hybrid_astar_utils.jl:193, main_hybrid_astar.jl:21) */
+  double veh_L, veh_W, veh_center_offset;
+} mppi_config_t;
+
+/* result of one step == MPPIResult (types.jl:36-44) + diagnostics.
+ * Control / Traj point into caller-allocated storage (may be NULL to skip). */
+typedef struct mppi_result {
+  double* Control;        /* N x m col-major  = r.Control  (MPPIUtils.jl:194) */
+  double* Traj;           /* (N+1) x n_x col-major = r.Traj (MPPIUtils.jl:193) */
+  double cost;            /* r.cost of the nominal rollout (:196) */
+  int32_t feasible;       /* r.Feasibility == :Feasible (:195) */
+  int32_t rollout_count;  /* r.RolloutCount = R + 1 (off-by-one kept, :171,182,197) */
+  int32_t feasible_count; /* r.FeasibleTrajCount (:198) */
+  int32_t argmin_index;   /* 1-based global index of the min-cost sample (:155) */
+  double rho;             /* min cost (:156) */
+  double eta;             /* sum exp(-(c-rho)/lambda) (:159-161) */
+  double time_s;          /* host wall time of the call = r.time (:173,199-200) */
+} mppi_result_t;
+
+/* One rank's contribution to the softmin combine (multi-GPU sample sharding):
+ * local min cost and its global index, local eta and local weighted control sum,
+ * both taken against the LOCAL rho; see DESIGN.md "multi-GPU". */
+typedef struct mppi_partial {
+  double rho;
+  double eta;
+  int64_t argmin_global; /* 0-based global sample id */
+  int32_t rollouts;      /* samples rolled out on this rank */
+  int32_t feasible;      /* feasible samples on this rank */
+  double S[2 * MPPI_MAX_N]; /* sum_k w_k * u_k, N x m col-major, unnormalised */
+} mppi_partial_t;
+
+/* fill cfg with the reference literals (main.jl:7-27, vehicledynamics.jl, types.jl) */
+int32_t mppi_config_default(mppi_config_t* cfg);
+int32_t mppi_version(void);
+
+/* defineMPPI (setup.jl:3-59): validates like setup.jl:19-39, allocates device state */
+typedef struct mppi_handle mppi_handle_t;
+int32_t mppi_create(const mppi_config_t* cfg, mppi_handle_t** out);
+int32_t mppi_destroy(mppi_handle_t* h);
+/* error text of the last failing call on h (h == NULL: last create failure) */
+const char* mppi_last_error(const mppi_handle_t* h);
+
+/* ShiftInitialCondition (MPPIUtils.jl:24-27); x0 is n x B col-major */
+int32_t mppi_set_x0(mppi_handle_t* h, const double* x0, int32_t n);
+/* defineMPPINominalControl!(mppi, U) (setup.jl:70-73); U is N x m (x B) col-major */
+int32_t mppi_set_nominal(mppi_handle_t* h, const double* U, int32_t N, int32_t m);
+/* defineMPPINominalControl!(mppi, U, Sigma) second form (setup.jl:74-78) + lambda */
+int32_t mppi_set_sigma_lambda(mppi_handle_t* h, const double* Sigma, double lambda);
+/* defineMPPIobs! (setup.jl:61-64); xyr is 3 x M_c col-major: [x, y, r] per circle */
+int32_t mppi_set_circles(mppi_handle_t* h, const double* xyr, int32_t M_c);
+/* polygon walls, block = [cx, cy, psi, half_len, half_wid] (CollisionDetection
+ * utils.jl:14-25); 5 x M_p col-major */
+int32_t mppi_set_blocks(mppi_handle_t* h, const double* blocks, int32_t M_p);
+/* set goal (MPPISetting.goal) without re-creating the handle */
+int32_t mppi_set_goal(mppi_handle_t* h, const double* goal2);
+/* DWA candidate grid (DynamicWindow/src/setup.jl:59-85): K x m col-major constant
+ * controls; only for planner == MPPI_PLANNER_DWA */
+int32_t mppi_set_candidates(mppi_handle_t* h, const double* ctrl, int32_t K, int32_t m);
+
+/* MPPIPlan (MPPIUtils.jl:169-203).  noise == NULL in PHILOX mode; in SUPPLIED
+ * mode it is the host eps tensor [N][K_local][m] of float (FP32) or double (FP64).
+ * Synchronous: on return `out` and the caller's Control/Traj are filled. */
+int32_t mppi_step(mppi_handle_t* h, const void* noise, mppi_result_t* out);
+
+/* main.jl:60-62 without the host round trip: U_nom <- last U_new, on device */
+int32_t mppi_adopt_nominal(mppi_handle_t* h);
+/* device-resident iteration for closed loops / benchmarking: launches one
+ * iteration (adopting the previous result as nominal when adopt != 0) and does
+ * NOT synchronise or copy results; pair with mppi_sync / mppi_fetch_result */
+int32_t mppi_step_async(mppi_handle_t* h, int32_t adopt);
+int32_t mppi_sync(mppi_handle_t* h);
+int32_t mppi_fetch_result(mppi_handle_t* h, mppi_result_t* out);
+
+/* per-sample outputs of the last step (TrajectoryCollection[i].cost / .Feasibility) */
+int32_t mppi_get_costs(mppi_handle_t* h, double* costs /* K_local */);
+int32_t mppi_get_flags(mppi_handle_t* h, uint8_t* flags /* K_local */);
+/* dump the eps actually used by the last step ([N][K_local][m], element type by
+ * precision) so the oracle can replay device-generated Philox noise */
+int32_t mppi_get_noise(mppi_handle_t* h, void* eps);
+/* plot support (MPPIUtils.jl:221-223): xy of every `stride`-th sampled trajectory,
+ * float [n_samples][N+1][2]; re-rolls those samples on device */
+int32_t mppi_get_sample_xy(mppi_handle_t* h, int32_t stride, float* xy, int32_t* n_samples);
+
+/* batched multi-instance step (config 5): x0s n_x x B, Us N x m x B in,
+ * Us_out N x m x B, costs_out B (nominal rollout cost), feasible_out B */
+int32_t mppi_step_batched(mppi_handle_t* h, const double* x0s, const double* Us,
+                          double* Us_out, double* costs_out, int32_t* feasible_out);
+
+/* ---- multi-GPU sample sharding (one process per GPU) ------------------------
+ * Split-phase form: step_local runs rollout + local softmin partials on this
+ * rank's shard; the caller exchanges mppi_partial_t between ranks (any
+ * transport); step_combine folds all ranks' partials in rank order and runs the
+ * nominal rollout.  With mppi_comm_init the exchange is an in-library NCCL
+ * all-gather captured in the step graph and mppi_step does all of it. */
+int32_t mppi_step_local(mppi_handle_t* h, const void* noise, mppi_partial_t* partial_out);
+int32_t mppi_step_combine(mppi_handle_t* h, const mppi_partial_t* partials, int32_t n_ranks,
+                          mppi_result_t* out);
+#define MPPI_COMM_ID_BYTES 128
+int32_t mppi_comm_unique_id(uint8_t id[MPPI_COMM_ID_BYTES]);
+int32_t mppi_comm_init(mppi_handle_t* h, const uint8_t id[MPPI_COMM_ID_BYTES], int32_t rank,
+                       int32_t n_ranks);
+
+/* timings of the last step in microseconds (CUDA events on the handle's stream):
+ * [0] rollout, [1] softmin+update, [2] combine+nominal rollout, [3] whole device step */
+int32_t mppi_get_timings(mppi_handle_t* h, float us[4]);
+/* toggle per-kernel event timing (disables graph replay for that step) */
+int32_t mppi_set_profiling(mppi_handle_t* h, int32_t on);
+/* number of kernels the library launched on this handle so far */
+int64_t mppi_launch_count(const mppi_handle_t* h);
+
+/* batched pose-vs-obstacle query on device: the block_collision_check of
+ * PathPlanning/HybridAstar/src/hybrid_astar_utils.jl:193-201 for n poses
+ * (x, y, psi) 3 x n col-major against the handle's circles and blocks;
+ * hit[i] = number of obstacles pose i collides with */
+int32_t mppi_check_poses(mppi_handle_t* h, const double* poses, int32_t n, int32_t* hit);
+
+/* FP32 FMA-chain micro-benchmark on this handle's device; returns TFLOP/s
+ * (denominator of the rollout kernel's roofline) */
+int32_t mppi_measure_fp32_peak(mppi_handle_t* h, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPPI_B200_H */

@@ -1,0 +1,249 @@
+// mppi_api.cu — extern "C" entry points declared in include/mppi_b200.h.
+// Each function cites the reference interface it replaces in the header.
+#include "mppi_extra.cuh"
+#include "mppi_pipeline.cuh"
+
+using namespace mppi;
+
+#define H_CHECK(h)            \
+  if (!(h)) return MPPI_EINVAL; \
+  cudaSetDevice((h)->cfg.device)
+
+static int fail(mppi_handle* h, int code, const std::string& msg) {
+  if (h) h->err = msg; else create_error() = msg;
+  return code;
+}
+
+extern "C" {
+
+int32_t mppi_version(void) { return MPPI_B200_VERSION; }
+
+int32_t mppi_config_default(mppi_config_t* c) {
+  if (!c) return MPPI_EINVAL;
+  memset(c, 0, sizeof(*c));
+  c->struct_size = sizeof(mppi_config_t);
+  c->model = MPPI_MODEL_DYNAMIC7; c->n_x = 7; c->m = 2;        // main.jl:12-13
+  c->K = 1500; c->N = 20; c->B = 1;                            // main.jl:22,14
+  c->precision = MPPI_FP32; c->noise_mode = MPPI_NOISE_PHILOX; c->planner = MPPI_PLANNER_MPPI;
+  c->feasibility_count = 1300;                                 // types.jl:24
+  c->use_cuda_graph = 1; c->device = 0; c->k_offset = 0; c->K_local = 0;
+  c->seed = 0x5EED0001ull;
+  c->T = 3.0; c->lambda = 25.0;                                // main.jl:15,24
+  c->Sigma[0] = 0.05; c->Sigma[1] = 0.0; c->Sigma[2] = 0.0; c->Sigma[3] = 0.1;   // main.jl:27
+  const double pi = 3.141592653589793;
+  const double X0[7] = {0, 0, 0, 0, 0, 5, 0};                                   // main.jl:7
+  const double XL[7] = {-10, -20, -2, -pi / 2, -pi / 2, 1, -pi / 9};           // main.jl:8
+  const double XU[7] = {130, 20, 2, pi / 2, pi / 2, 10, pi / 9};               // main.jl:9
+  for (int i = 0; i < 7; ++i) { c->X0[i] = X0[i]; c->XL[i] = XL[i]; c->XU[i] = XU[i]; }
+  c->goal[0] = 110; c->goal[1] = 0;                                             // main.jl:23
+  c->CL[0] = -0.5; c->CL[1] = -2.5; c->CU[0] = 0.5; c->CU[1] = 2.5;             // main.jl:10-11
+  c->slack_penalty = 1e5;                                                       // types.jl:30
+  c->obstacle_penalty = 100.0 * 712.5;                                          // MPPIUtils.jl:127
+  c->terminal_scale = 10000.0;                                                  // MPPIUtils.jl:54
+  c->la = 1.56; c->lb = 1.64; c->mass = 2020; c->Izz = 4095; c->g = 9.81; c->mu = 0.8;   // vehicledynamics.jl:2-7
+  c->KFZF = 1018.28 / 2; c->KFZR = 963.34 / 2; c->KFZX = 186.22;                          // :8-10
+  const double tire[6] = {-10.4, 1.3, 1.0, 0.1556, -0.0023, 41.3705};                     // :11
+  for (int i = 0; i < 6; ++i) c->tire[i] = tire[i];
+  const double w[6] = {1, 1, 5, 3, 2, 10};                                                // :52
+  for (int i = 0; i < 6; ++i) c->stage_w[i] = w[i];
+  c->veh_L = 3; c->veh_W = 2; c->veh_center_offset = 1.5;   // main_hybrid_astar.jl:21, hybrid_astar_utils.jl:193
+  return MPPI_OK;
+}
+
+const char* mppi_last_error(const mppi_handle_t* h) { return h ? h->err.c_str() : create_error().c_str(); }
+
+int64_t mppi_launch_count(const mppi_handle_t* h) { return h ? h->launches : 0; }
+
+static int validate(const mppi_config_t* c, std::string* why) {
+  char buf[256];
+  // same checks, same wording as setup.jl:19-39 where they apply to a fixed-size POD
+  if (c->struct_size != sizeof(mppi_config_t)) { snprintf(buf, sizeof buf, "struct_size (%u) must be %zu", c->struct_size, sizeof(mppi_config_t)); *why = buf; return MPPI_EINVAL; }
+  if (c->m <= 0) { snprintf(buf, sizeof buf, "Controls (%d) must be > 0", c->m); *why = buf; return MPPI_EINVAL; }
+  if (c->n_x <= 0) { snprintf(buf, sizeof buf, "States (%d) must be > 0", c->n_x); *why = buf; return MPPI_EINVAL; }
+  if (c->m != 2) { snprintf(buf, sizeof buf, "Controls (%d) must be 2 (sr, ax) for the bicycle models", c->m); *why = buf; return MPPI_EINVAL; }
+  const int want = c->model == MPPI_MODEL_DYNAMIC7 ? 7 : 5;
+  if (c->model != MPPI_MODEL_DYNAMIC7 && c->model != MPPI_MODEL_KINEMATIC5) { *why = "unknown model"; return MPPI_EINVAL; }
+  if (c->n_x != want) { snprintf(buf, sizeof buf, "States (%d) must match the model (%d)", c->n_x, want); *why = buf; return MPPI_EINVAL; }
+  if (c->K <= 0) { snprintf(buf, sizeof buf, "SamplingNumber (%d) must be > 0", c->K); *why = buf; return MPPI_EINVAL; }
+  if (c->N <= 0 || c->N > MPPI_MAX_N) { snprintf(buf, sizeof buf, "N (%d) must be in 1..%d", c->N, MPPI_MAX_N); *why = buf; return MPPI_EINVAL; }
+  if (c->B <= 0) { snprintf(buf, sizeof buf, "B (%d) must be > 0", c->B); *why = buf; return MPPI_EINVAL; }
+  if (!(c->T > 0)) { *why = "T must be > 0"; return MPPI_EINVAL; }
+  if (!(c->lambda > 0)) { *why = "lambda must be > 0"; return MPPI_EINVAL; }
+  if (c->precision != MPPI_FP32 && c->precision != MPPI_FP64) { *why = "unknown precision"; return MPPI_EINVAL; }
+  if (c->noise_mode != MPPI_NOISE_SUPPLIED && c->noise_mode != MPPI_NOISE_PHILOX) { *why = "unknown noise_mode"; return MPPI_EINVAL; }
+  if (c->planner != MPPI_PLANNER_MPPI && c->planner != MPPI_PLANNER_DWA) { *why = "unknown planner"; return MPPI_EINVAL; }
+  const int Kl = c->K_local > 0 ? c->K_local : c->K;
+  if (c->k_offset < 0 || c->k_offset + Kl > c->K) { *why = "sample shard [k_offset, k_offset+K_local) must lie inside [0, K)"; return MPPI_EINVAL; }
+  const double det = c->Sigma[0] * c->Sigma[3] - c->Sigma[1] * c->Sigma[2];
+  if (!(c->Sigma[0] > 0) || !(det > 0)) { *why = "Sigma must be positive definite"; return MPPI_EINVAL; }
+  if (c->planner == MPPI_PLANNER_DWA && (Kl != c->K || c->B != 1)) { *why = "DWA planner runs unsharded, B = 1"; return MPPI_EINVAL; }
+  return MPPI_OK;
+}
+
+int32_t mppi_destroy(mppi_handle_t* h) {
+  if (!h) return MPPI_EINVAL;
+  cudaSetDevice(h->cfg.device);
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  drop_graphs(h);
+  if (h->comm && nccl_api().CommDestroy) nccl_api().CommDestroy(h->comm);
+  void* dev[] = {h->d_in, h->d_eps, h->d_costs, h->d_flags, h->d_scratch, h->d_scratch_tmpl, h->d_iter, h->d_Spart,
+                 h->d_eta_part, h->d_partial, h->d_gathered, h->d_res, h->d_traj, h->d_cand};
+  for (void* p : dev) if (p) cudaFree(p);
+  void* host[] = {h->h_in, h->h_res, h->h_traj, h->h_partial, h->h_gathered};
+  for (void* p : host) if (p) cudaFreeHost(p);
+  for (auto& e : h->ev) if (e) cudaEventDestroy(e);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+  return MPPI_OK;
+}
+
+static int create_impl(mppi_handle* h) {
+  const mppi_config_t& c = h->cfg;
+  int ndev = 0;
+  MPPI_CUDA(h, cudaGetDeviceCount(&ndev));
+  if (c.device < 0 || c.device >= ndev) { h->err = "device ordinal out of range"; return MPPI_EINVAL; }
+  MPPI_CUDA(h, cudaSetDevice(c.device));
+  MPPI_CUDA(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  for (auto& e : h->ev) MPPI_CUDA(h, cudaEventCreate(&e));
+  const size_t B = c.B, N = c.N, K = h->K_local, rs = real_size(h);
+  h->plen = PART_HDR + 2 * c.N;
+  int ks = (h->K_local + 2047) / 2048;
+  h->ksplit = ks < 1 ? 1 : (ks > 64 ? 64 : ks);
+  h->cutoff = c.feasibility_count < c.K;
+  MPPI_CUDA(h, cudaMalloc(&h->d_in, B * (MPPI_MAX_NX + 2 * N) * sizeof(double)));
+  if (c.planner == MPPI_PLANNER_MPPI) MPPI_CUDA(h, cudaMalloc(&h->d_eps, B * N * K * 2 * rs));
+  MPPI_CUDA(h, cudaMalloc(&h->d_costs, B * K * rs));
+  MPPI_CUDA(h, cudaMalloc(&h->d_flags, B * K));
+  MPPI_CUDA(h, cudaMalloc(&h->d_scratch, B * sizeof(Scratch)));
+  MPPI_CUDA(h, cudaMalloc(&h->d_scratch_tmpl, B * sizeof(Scratch)));
+  MPPI_CUDA(h, cudaMalloc(&h->d_iter, sizeof(unsigned int)));
+  MPPI_CUDA(h, cudaMalloc(&h->d_Spart, B * h->ksplit * N * 2 * rs));
+  MPPI_CUDA(h, cudaMalloc(&h->d_eta_part, B * h->ksplit * rs));
+  MPPI_CUDA(h, cudaMalloc(&h->d_partial, B * h->plen * sizeof(double)));
+  MPPI_CUDA(h, cudaMalloc(&h->d_gathered, 8 * B * h->plen * sizeof(double)));
+  MPPI_CUDA(h, cudaMalloc(&h->d_res, B * (RES_SCALARS + 2 * N) * sizeof(double)));
+  MPPI_CUDA(h, cudaMalloc(&h->d_traj, B * (N + 1) * c.n_x * sizeof(double)));
+  if (c.planner == MPPI_PLANNER_DWA) MPPI_CUDA(h, cudaMalloc(&h->d_cand, K * 2 * sizeof(double)));
+  MPPI_CUDA(h, cudaMallocHost(&h->h_in, B * (MPPI_MAX_NX + 2 * N) * sizeof(double)));
+  MPPI_CUDA(h, cudaMallocHost(&h->h_res, B * (RES_SCALARS + 2 * N) * sizeof(double)));
+  MPPI_CUDA(h, cudaMallocHost(&h->h_traj, (N + 1) * c.n_x * sizeof(double)));
+  MPPI_CUDA(h, cudaMallocHost(&h->h_partial, B * h->plen * sizeof(double)));
+  MPPI_CUDA(h, cudaMallocHost(&h->h_gathered, 8 * B * h->plen * sizeof(double)));
+  // inputs: X0 from the config for every instance, zero nominal (setup.jl:55)
+  memset(h->h_in, 0, B * (MPPI_MAX_NX + 2 * N) * sizeof(double));
+  for (size_t b = 0; b < B; ++b)
+    for (int i = 0; i < c.n_x; ++i) h->h_in[b * MPPI_MAX_NX + i] = c.X0[i];
+  MPPI_CUDA(h, cudaMemcpy(h->d_in, h->h_in, B * (MPPI_MAX_NX + 2 * N) * sizeof(double), cudaMemcpyHostToDevice));
+  std::vector<Scratch> tmpl(B);
+  for (auto& s : tmpl) { s.rho_key = ~0ull; s.argmin = ~0u; s.feasible_count = 0; s.k_eff = h->K_local; s.pad = 0; }
+  MPPI_CUDA(h, cudaMemcpy(h->d_scratch_tmpl, tmpl.data(), B * sizeof(Scratch), cudaMemcpyHostToDevice));
+  MPPI_CUDA(h, cudaMemset(h->d_iter, 0, sizeof(unsigned int)));
+  MPPI_CUDA(h, cudaMemset(h->d_res, 0, B * (RES_SCALARS + 2 * N) * sizeof(double)));
+  rebuild_params(h);
+  return MPPI_OK;
+}
+
+int32_t mppi_create(const mppi_config_t* cfg, mppi_handle_t** out) {
+  if (!cfg || !out) return fail(nullptr, MPPI_EINVAL, "null argument");
+  *out = nullptr;
+  std::string why;
+  int rc = validate(cfg, &why);
+  if (rc != MPPI_OK) return fail(nullptr, rc, why);
+  mppi_handle* h = new (std::nothrow) mppi_handle();
+  if (!h) return fail(nullptr, MPPI_ENOMEM, "out of host memory");
+  h->cfg = *cfg;
+  h->K_local = cfg->K_local > 0 ? cfg->K_local : cfg->K;
+  h->cfg.K_local = h->K_local;
+  rc = create_impl(h);
+  if (rc != MPPI_OK) { create_error() = h->err; mppi_destroy(h); return rc; }
+  *out = h;
+  return MPPI_OK;
+}
+
+static int quiesce(mppi_handle* h) {   // pinned inputs are about to change: no step may be in flight
+  MPPI_CUDA(h, cudaStreamSynchronize(h->stream));
+  return MPPI_OK;
+}
+
+int32_t mppi_set_x0(mppi_handle_t* h, const double* x0, int32_t n) {
+  H_CHECK(h);
+  char buf[160];
+  if (!x0) return fail(h, MPPI_EINVAL, "null x0");
+  if (n != h->cfg.n_x) {   // setup.jl:25-27
+    snprintf(buf, sizeof buf, "Length of X0 (%d) must match number of states (%d)", n, h->cfg.n_x);
+    return fail(h, MPPI_EINVAL, buf);
+  }
+  int rc = quiesce(h); if (rc) return rc;
+  for (int b = 0; b < h->cfg.B; ++b)
+    for (int i = 0; i < n; ++i) h->h_in[size_t(b) * MPPI_MAX_NX + i] = x0[size_t(b) * n + i];
+  MPPI_CUDA(h, cudaMemcpyAsync(h->d_in, h->h_in, size_t(h->cfg.B) * MPPI_MAX_NX * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  return MPPI_OK;
+}
+
+int32_t mppi_set_nominal(mppi_handle_t* h, const double* U, int32_t N, int32_t m) {
+  H_CHECK(h);
+  if (!U) return fail(h, MPPI_EINVAL, "null U");
+  if (N != h->cfg.N || m != h->cfg.m) return fail(h, MPPI_EINVAL, "NominalControl must be N x numControls");
+  int rc = quiesce(h); if (rc) return rc;
+  const size_t B = h->cfg.B, off = B * MPPI_MAX_NX, n = B * 2 * N;
+  memcpy(h->h_in + off, U, n * sizeof(double));
+  MPPI_CUDA(h, cudaMemcpyAsync(h->d_in + off, h->h_in + off, n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  return MPPI_OK;
+}
+
+int32_t mppi_set_sigma_lambda(mppi_handle_t* h, const double* Sigma, double lambda) {
+  H_CHECK(h);
+  if (!Sigma) return fail(h, MPPI_EINVAL, "null Sigma");
+  const double det = Sigma[0] * Sigma[3] - Sigma[1] * Sigma[2];
+  if (!(Sigma[0] > 0) || !(det > 0) || !(lambda > 0)) return fail(h, MPPI_EINVAL, "Sigma must be positive definite and lambda > 0");
+  int rc = quiesce(h); if (rc) return rc;
+  for (int i = 0; i < 4; ++i) h->cfg.Sigma[i] = Sigma[i];
+  h->cfg.lambda = lambda;
+  rebuild_params(h);
+  drop_graphs(h);
+  return MPPI_OK;
+}
+
+int32_t mppi_set_circles(mppi_handle_t* h, const double* xyr, int32_t M_c) {
+  H_CHECK(h);
+  if (M_c < 0 || M_c > MPPI_MAX_CIRCLES || (M_c > 0 && !xyr)) return fail(h, MPPI_EINVAL, "circle count out of range");
+  int rc = quiesce(h); if (rc) return rc;
+  h->circles.assign(xyr, xyr + size_t(3) * M_c);
+  rebuild_params(h);
+  drop_graphs(h);
+  return MPPI_OK;
+}
+
+int32_t mppi_set_blocks(mppi_handle_t* h, const double* blocks, int32_t M_p) {
+  H_CHECK(h);
+  if (M_p < 0 || M_p > MPPI_MAX_BLOCKS || (M_p > 0 && !blocks)) return fail(h, MPPI_EINVAL, "block count out of range");
+  int rc = quiesce(h); if (rc) return rc;
+  h->blocks.assign(blocks, blocks + size_t(5) * M_p);
+  rebuild_params(h);
+  drop_graphs(h);
+  return MPPI_OK;
+}
+
+int32_t mppi_set_goal(mppi_handle_t* h, const double* goal2) {
+  H_CHECK(h);
+  if (!goal2) return fail(h, MPPI_EINVAL, "null goal");
+  int rc = quiesce(h); if (rc) return rc;
+  h->cfg.goal[0] = goal2[0]; h->cfg.goal[1] = goal2[1];
+  rebuild_params(h);
+  drop_graphs(h);
+  return MPPI_OK;
+}
+
+int32_t mppi_set_candidates(mppi_handle_t* h, const double* ctrl, int32_t K, int32_t m) {
+  H_CHECK(h);
+  if (h->cfg.planner != MPPI_PLANNER_DWA) return fail(h, MPPI_ESTATE, "candidates are only used by the DWA planner");
+  if (!ctrl || K != h->K_local || m != 2) return fail(h, MPPI_EINVAL, "candidates must be K x 2");
+  int rc = quiesce(h); if (rc) return rc;
+  MPPI_CUDA(h, cudaMemcpy(h->d_cand, ctrl, size_t(K) * 2 * sizeof(double), cudaMemcpyHostToDevice));
+  h->have_candidates = true;
+  return MPPI_OK;
+}
+
+}  // extern "C"
+
+#include "mppi_api_step.inc"

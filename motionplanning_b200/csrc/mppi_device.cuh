@@ -1,0 +1,136 @@
+// mppi_device.cuh — device-side building blocks of the B200 MPPI engine:
+// math traits (FP32 fast path / FP64 verification path), the two vehicle models,
+// circle and rectangle (separating-axis) obstacle tests, bounds, Philox noise.
+//
+// Reference semantics (paths relative to the reference root):
+//   dynamic bicycle    OptimalControl/MPPI/src/vehicledynamics.jl:1-54
+//   kinematic bicycle  OptimalControl/Parking/src/VehicleModel.jl:1-21
+//   Heun step          OptimalControl/MPPI/src/MPPIUtils.jl:76-90
+//   circles            OptimalControl/MPPI/src/MPPIUtils.jl:120-132
+//   rectangles / SAT   PathPlanning/CollisionDetection/src/utils.jl:14-74,
+//                      PathPlanning/HybridAstar/src/hybrid_astar_utils.jl:193-201
+//   bounds             OptimalControl/MPPI/src/MPPIUtils.jl:135-151
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/mppi_b200.h"
+
+namespace mppi {
+
+// ---------------------------------------------------------------------------
+// Static parameters: passed BY VALUE as a __grid_constant__ kernel argument, so
+// every field is a constant-bank operand (no load instruction, warp-uniform).
+// Rebuilt (and the step graph re-captured) only when the configuration changes.
+// ---------------------------------------------------------------------------
+template <class R>
+struct StaticParams {
+  int K, K_local, k_offset, N, B;
+  int n_circles, n_blocks, planner;
+  int feasibility_count, n_x;
+  uint32_t seed_lo, seed_hi;
+  R dt, half_dt, lambda, inv_lambda;
+  R L00, L10, L11;            // chol(Sigma), lower
+  R G00, G01, G10, G11;       // lambda * inv(Sigma)  (g_j = G * U_nom[j])
+  R goal[2];
+  R XL[MPPI_MAX_NX], XU[MPPI_MAX_NX];
+  R CL[2], CU[2];
+  R slack, obs_pen, term_scale;
+  // vehicle (vehicledynamics.jl:2-18), pre-folded where the folding is exact
+  R la, lb, inv_mass_num /*unused*/, mass, Izz, mu, KFZX;
+  R FZF0, FZR0;               // KFZF*g, KFZR*g
+  R tireB, tireC, tireD, tireE;  // B = tire[0]/mu, C = tire[1], D = tire[2], E = tire[3]
+  R Lwb;                      // la + lb
+  R w[6];                     // stage cost weights v2, r2, ax2, sr2, sa2, y2
+  R veh_off, veh_hl, veh_hw;  // rectangle: centre offset, half length, half width
+  R circ[MPPI_MAX_CIRCLES][3];  // x, y, r^2
+  R blk[MPPI_MAX_BLOCKS][6];    // cx, cy, cos(psi), sin(psi), half_len, half_wid
+};
+
+// per-instance scratch, reset from a template by one D2D copy at the head of a step
+struct Scratch {
+  unsigned long long rho_key;  // atomicMin: FP32 (ordered cost bits << 32 | local k); FP64 ordered cost bits
+  unsigned int argmin;         // FP64 path / cut-off path: min local k with cost == rho
+  int feasible_count;          // atomicAdd
+  int k_eff;                   // samples that participate (cut-off); K_local when disabled
+  int pad;
+};
+
+// layout of the per-rank partial exchanged between GPUs (doubles)
+enum { PART_RHO = 0, PART_ETA = 1, PART_ARGMIN = 2, PART_ROLLOUTS = 3, PART_FEASIBLE = 4, PART_HDR = 8 };
+// layout of the per-instance result scalars (doubles)
+enum { RES_COST = 0, RES_FEASIBLE = 1, RES_ROLLOUTS = 2, RES_FEASCOUNT = 3, RES_ARGMIN = 4, RES_RHO = 5,
+       RES_ETA = 6, RES_FLAGS = 7, RES_SCALARS = 8 };
+
+template <class R>
+struct Buffers {
+  const double* x0;     // [B][MPPI_MAX_NX]
+  const double* U;      // [B][2*N]  col-major N x m (host layout)
+  R* eps;               // [B][N][K_local][2]
+  R* costs;             // [B][K_local]
+  uint8_t* flags;       // [B][K_local]
+  Scratch* scratch;     // [B]
+  unsigned int* iter;   // Philox iteration counter (device-incremented)
+  R* Spart;             // [B][ksplit][N][2]  unnormalised weighted control sums
+  R* eta_part;          // [B][ksplit]
+  double* partial;      // [B][PART_HDR + 2N]   this rank's partial
+  const double* gathered;  // [G][B][PART_HDR + 2N]  all ranks' partials (G == 1: == partial)
+  double* res_scalars;  // [B][RES_SCALARS]
+  double* res_control;  // [B][2*N]  col-major N x m
+  double* res_traj;     // [B][(N+1)*n_x] col-major (N+1) x n_x
+  const double* cand;   // DWA: [K][2] col-major K x m candidates
+  int ksplit;
+  int n_ranks;
+};
+
+// ---------------------------------------------------------------------------
+// math traits
+// ---------------------------------------------------------------------------
+template <class R> struct Math;
+
+template <> struct Math<float> {
+  // Fast path: MUFU-based intrinsics.  |abs err| of sin/cos.approx <= 2^-21.4 on
+  // [-pi, pi]; well inside the 1e-4 relative cost tolerance of FP32 mode.
+  static __device__ __forceinline__ void sincos(float x, float* s, float* c) { __sincosf(x, s, c); }
+  static __device__ __forceinline__ float tan(float x) { return __tanf(x); }
+  static __device__ __forceinline__ float div(float a, float b) { return __fdividef(a, b); }
+  static __device__ __forceinline__ float exp(float x) { return __expf(x); }
+  static __device__ __forceinline__ float sin(float x) { return __sinf(x); }
+  static __device__ __forceinline__ float fabs(float x) { return fabsf(x); }
+  static __device__ __forceinline__ float fmax(float a, float b) { return fmaxf(a, b); }
+  static __device__ __forceinline__ float fmin(float a, float b) { return fminf(a, b); }
+  // atan: odd minimax polynomial on [0,1] + reciprocal reduction (no MUFU atan exists)
+  static __device__ __forceinline__ float atan(float x) {
+    const float ax = fabsf(x);
+    const bool big = ax > 1.0f;
+    const float z = big ? __fdividef(1.0f, ax) : ax;
+    const float z2 = z * z;
+    // minimax fit of atan(z)/z in z^2, degree 7 (Lawson-reweighted LSQ);
+    // max abs error 1.5e-7 on [0,1] evaluated in FP32.
+    float p = -0.004054558929055929f;
+    p = fmaf(p, z2, 0.021862929686903954f);
+    p = fmaf(p, z2, -0.05591228976845741f);
+    p = fmaf(p, z2, 0.09642194956541061f);
+    p = fmaf(p, z2, -0.1390862911939621f);
+    p = fmaf(p, z2, 0.19946566224098206f);
+    p = fmaf(p, z2, -0.33329859375953674f);
+    p = fmaf(p, z2, 0.9999993443489075f);
+    float r = p * z;
+    r = big ? (1.57079632679f - r) : r;
+    return copysignf(r, x);
+  }
+};
+
+template <> struct Math<double> {
+  static __device__ __forceinline__ void sincos(double x, double* s, double* c) { ::sincos(x, s, c); }
+  static __device__ __forceinline__ double tan(double x) { return ::tan(x); }
+  static __device__ __forceinline__ double div(double a, double b) { return a / b; }
+  static __device__ __forceinline__ double exp(double x) { return ::exp(x); }
+  static __device__ __forceinline__ double sin(double x) { return ::sin(x); }
+  static __device__ __forceinline__ double atan(double x) { return ::atan(x); }
+  static __device__ __forceinline__ double fabs(double x) { return ::fabs(x); }
+  static __device__ __forceinline__ double fmax(double a, double b) { return ::fmax(a, b); }
+  static __device__ __forceinline__ double fmin(double a, double b) { return ::fmin(a, b); }
+};
+
+}  // namespace mppi

@@ -1,0 +1,176 @@
+// mppi_handle.cuh — host-side handle: configuration, device/pinned buffers,
+// static parameter blocks, NCCL (dlopen'ed lazily; no link-time dependency).
+#pragma once
+#include <dlfcn.h>
+#include <nccl.h>   // declarations only; symbols are resolved with dlsym at mppi_comm_init
+
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "mppi_update.cuh"
+
+namespace mppi {
+
+struct NcclApi {
+  void* lib = nullptr;
+  decltype(&ncclGetUniqueId) GetUniqueId = nullptr;
+  decltype(&ncclCommInitRank) CommInitRank = nullptr;
+  decltype(&ncclAllGather) AllGather = nullptr;
+  decltype(&ncclCommDestroy) CommDestroy = nullptr;
+  decltype(&ncclGetErrorString) GetErrorString = nullptr;
+  std::string err;
+  bool load() {
+    if (lib) return true;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* n : names) {
+      lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+      if (lib) break;
+    }
+    if (!lib) { err = std::string("cannot dlopen libnccl: ") + dlerror(); return false; }
+#define MPPI_NCCL_SYM(f) f = (decltype(f))dlsym(lib, "nccl" #f); if (!f) { err = "missing symbol nccl" #f; lib = nullptr; return false; }
+    MPPI_NCCL_SYM(GetUniqueId) MPPI_NCCL_SYM(CommInitRank) MPPI_NCCL_SYM(AllGather)
+    MPPI_NCCL_SYM(CommDestroy) MPPI_NCCL_SYM(GetErrorString)
+#undef MPPI_NCCL_SYM
+    return true;
+  }
+};
+inline NcclApi& nccl_api() { static NcclApi a; return a; }
+
+}  // namespace mppi
+
+using mppi::Scratch;
+
+struct mppi_handle {
+  mppi_config_t cfg;
+  std::string err;
+  cudaStream_t stream = nullptr;
+  int K_local = 0, ksplit = 1, plen = 0;
+  bool cutoff = false;
+  std::vector<double> circles, blocks;   // host copies (3 x Mc, 5 x Mp col-major)
+  // device
+  double* d_in = nullptr;        // [B][8] x0 then [B][2N] U  (d_x0 = d_in, d_U = d_in + 8B)
+  void* d_eps = nullptr;
+  void* d_costs = nullptr;
+  uint8_t* d_flags = nullptr;
+  Scratch* d_scratch = nullptr;
+  Scratch* d_scratch_tmpl = nullptr;
+  unsigned int* d_iter = nullptr;
+  void* d_Spart = nullptr;
+  void* d_eta_part = nullptr;
+  double* d_partial = nullptr;   // [B][plen]
+  double* d_gathered = nullptr;  // [G][B][plen]
+  double* d_res = nullptr;       // [B][RES_SCALARS] then [B][2N]
+  double* d_traj = nullptr;      // [B][(N+1)*n_x]
+  double* d_cand = nullptr;      // DWA candidates K x 2 col-major
+  // pinned host mirrors
+  double* h_in = nullptr;
+  double* h_res = nullptr;
+  double* h_traj = nullptr;
+  double* h_partial = nullptr;
+  double* h_gathered = nullptr;
+  // static params
+  mppi::StaticParams<float> pf;
+  mppi::StaticParams<double> pd;
+  // graphs, keyed by variant
+  std::map<int, cudaGraphExec_t> graphs;
+  // multi-GPU
+  ncclComm_t comm = nullptr;
+  int rank = 0, n_ranks = 1;
+  // profiling
+  cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  bool profiling = false;
+  float us[4] = {0, 0, 0, 0};
+  int64_t launches = 0;
+  bool stepped = false;
+  bool have_candidates = false;
+};
+
+namespace mppi {
+
+inline std::string& create_error() { static std::string e; return e; }
+
+#define MPPI_CUDA(h, call)                                                                   \
+  do {                                                                                       \
+    cudaError_t e_ = (call);                                                                 \
+    if (e_ != cudaSuccess) {                                                                 \
+      (h)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                         \
+      return (e_ == cudaErrorMemoryAllocation) ? MPPI_ENOMEM : MPPI_ECUDA;                   \
+    }                                                                                        \
+  } while (0)
+
+template <class R>
+void build_params(const mppi_handle* h, StaticParams<R>* p) {
+  const mppi_config_t& c = h->cfg;
+  memset(p, 0, sizeof(*p));
+  p->K = c.K; p->K_local = h->K_local; p->k_offset = c.k_offset; p->N = c.N; p->B = c.B;
+  p->n_circles = int(h->circles.size() / 3); p->n_blocks = int(h->blocks.size() / 5);
+  p->planner = c.planner; p->feasibility_count = c.feasibility_count; p->n_x = c.n_x;
+  p->seed_lo = uint32_t(c.seed); p->seed_hi = uint32_t(c.seed >> 32);
+  const double dt = c.T / c.N;   // setup.jl:53
+  p->dt = R(dt); p->half_dt = R(dt) / R(2); p->lambda = R(c.lambda); p->inv_lambda = R(1.0 / c.lambda);
+  // Sigma col-major [s00, s10, s01, s11]; chol lower; lambda*inv(Sigma)
+  const double s00 = c.Sigma[0], s10 = c.Sigma[1], s01 = c.Sigma[2], s11 = c.Sigma[3];
+  const double l00 = std::sqrt(s00), l10 = s10 / l00, l11 = std::sqrt(s11 - l10 * l10);
+  p->L00 = R(l00); p->L10 = R(l10); p->L11 = R(l11);
+  const double det = s00 * s11 - s01 * s10;
+  const double i00 = s11 / det, i10 = -s10 / det, i01 = -s01 / det, i11 = s00 / det;   // inv(r,c)
+  p->G00 = R(c.lambda * i00); p->G01 = R(c.lambda * i10); p->G10 = R(c.lambda * i01); p->G11 = R(c.lambda * i11);
+  for (int i = 0; i < 2; ++i) { p->goal[i] = R(c.goal[i]); p->CL[i] = R(c.CL[i]); p->CU[i] = R(c.CU[i]); }
+  for (int i = 0; i < MPPI_MAX_NX; ++i) { p->XL[i] = R(c.XL[i]); p->XU[i] = R(c.XU[i]); }
+  p->slack = R(c.slack_penalty); p->obs_pen = R(c.obstacle_penalty); p->term_scale = R(c.terminal_scale);
+  p->la = R(c.la); p->lb = R(c.lb); p->mass = R(c.mass); p->Izz = R(c.Izz); p->mu = R(c.mu); p->KFZX = R(c.KFZX);
+  p->FZF0 = R(c.KFZF) * R(c.g); p->FZR0 = R(c.KFZR) * R(c.g);
+  p->tireB = R(c.tire[0]) / R(c.mu); p->tireC = R(c.tire[1]); p->tireD = R(c.tire[2]); p->tireE = R(c.tire[3]);
+  p->Lwb = R(c.la) + R(c.lb);
+  for (int i = 0; i < 6; ++i) p->w[i] = R(c.stage_w[i]);
+  p->veh_off = R(c.veh_center_offset); p->veh_hl = R(c.veh_L) / R(2); p->veh_hw = R(c.veh_W) / R(2);
+  for (int o = 0; o < p->n_circles; ++o) {
+    const R r = R(h->circles[3 * o + 2]);
+    p->circ[o][0] = R(h->circles[3 * o]); p->circ[o][1] = R(h->circles[3 * o + 1]); p->circ[o][2] = r * r;
+  }
+  for (int b = 0; b < p->n_blocks; ++b) {
+    const double* bl = &h->blocks[5 * b];
+    p->blk[b][0] = R(bl[0]); p->blk[b][1] = R(bl[1]);
+    p->blk[b][2] = R(std::cos(bl[2])); p->blk[b][3] = R(std::sin(bl[2]));
+    p->blk[b][4] = R(bl[3]); p->blk[b][5] = R(bl[4]);
+  }
+}
+
+inline void rebuild_params(mppi_handle* h) {
+  build_params(h, &h->pf);
+  build_params(h, &h->pd);
+}
+
+inline void drop_graphs(mppi_handle* h) {
+  for (auto& kv : h->graphs) cudaGraphExecDestroy(kv.second);
+  h->graphs.clear();
+}
+
+template <class R>
+Buffers<R> make_buffers(const mppi_handle* h) {
+  Buffers<R> b;
+  const int B = h->cfg.B;
+  b.x0 = h->d_in;
+  b.U = h->d_in + size_t(B) * MPPI_MAX_NX;
+  b.eps = (R*)h->d_eps; b.costs = (R*)h->d_costs; b.flags = h->d_flags;
+  b.scratch = h->d_scratch; b.iter = h->d_iter;
+  b.Spart = (R*)h->d_Spart; b.eta_part = (R*)h->d_eta_part;
+  b.partial = h->d_partial;
+  b.gathered = h->d_gathered;
+  b.res_scalars = h->d_res;
+  b.res_control = h->d_res + size_t(B) * RES_SCALARS;
+  b.res_traj = h->d_traj;
+  b.cand = h->d_cand;
+  b.ksplit = h->ksplit;
+  b.n_ranks = h->n_ranks;
+  return b;
+}
+
+inline size_t real_size(const mppi_handle* h) { return h->cfg.precision == MPPI_FP64 ? 8 : 4; }
+
+}  // namespace mppi

@@ -1,0 +1,223 @@
+// mppi_kernels.cuh — the kernels of one MPPI iteration (MPPIPlan, MPPIUtils.jl:169-203):
+//   rollout_kernel   K-sample rollout + fused stage/obstacle/bound/terminal cost,
+//                    noise (supplied | Philox | DWA grid), per-block min -> atomicMin
+//   cutoff_kernel    optional emulation of the reference's sequential feasibility cut-off
+//   update_kernel    softmin weights on the fly + weighted control sum (HBM-bound stream)
+//   finalize_kernel  partial -> (multi-rank) combine -> U_new -> nominal rollout
+#pragma once
+#include "mppi_models.cuh"
+
+namespace mppi {
+
+enum { SRC_SUPPLIED = 0, SRC_PHILOX = 1, SRC_DWA = 2 };
+constexpr int ROLLOUT_BS = 128;
+constexpr int UPDATE_BS = 256;
+constexpr int UPDATE_JG = 4;
+constexpr int FINAL_BS = 256;
+constexpr int CUTOFF_BS = 1024;
+
+template <class R> struct Vec2;
+template <> struct Vec2<float> { using type = float2; };
+template <> struct Vec2<double> { using type = double2; };
+
+__device__ __forceinline__ unsigned long long shfl_xor_u64(unsigned long long v, int m) {
+  return __shfl_xor_sync(0xffffffffu, v, m);
+}
+__device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long t = shfl_xor_u64(v, o);
+    v = t < v ? t : v;
+  }
+  return v;
+}
+template <class T>
+__device__ __forceinline__ T warp_sum(T v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// pack (cost, local sample id) so that an unsigned min gives (min cost, first index)
+__device__ __forceinline__ unsigned long long make_key(float c, unsigned int k) {
+  return ((unsigned long long)ordered_bits(c) << 32) | k;
+}
+__device__ __forceinline__ unsigned long long make_key(double c, unsigned int) { return ordered_bits(c); }
+__device__ __forceinline__ float key_cost(unsigned long long key, float) { return unordered_bits((uint32_t)(key >> 32)); }
+__device__ __forceinline__ double key_cost(unsigned long long key, double) { return unordered_bits(key); }
+
+// ---------------------------------------------------------------------------
+// rollout + cost.  One sample per thread; state, running cost and flags live in
+// registers; U_nom[j] and g_j = lambda*inv(Sigma)*U_nom[j] are broadcast from
+// shared memory; bounds, obstacle tables and vehicle constants are constant-bank
+// operands (StaticParams is a __grid_constant__ argument).
+// Schedule (MPPIUtils.jl:39-53): states x_1..x_N are each tested once against
+// obstacles and bounds (x_0 never is); stage cost is taken at the pre-step state.
+// ---------------------------------------------------------------------------
+template <class R, class Model, int SRC>
+__global__ void __launch_bounds__(ROLLOUT_BS)
+rollout_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) {
+  using R2 = typename Vec2<R>::type;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  R* sU = reinterpret_cast<R*>(smem_raw);  // [N][4]: u0, u1, g0, g1
+  __shared__ unsigned long long s_key[ROLLOUT_BS / 32];
+  __shared__ int s_feas[ROLLOUT_BS / 32];
+
+  const int b = blockIdx.y;
+  const int N = p.N;
+  const int k = blockIdx.x * ROLLOUT_BS + threadIdx.x;
+  const bool active = k < p.K_local;
+  const double* Ub = buf.U + size_t(b) * 2 * N;
+  if (SRC != SRC_DWA) {
+    for (int j = threadIdx.x; j < N; j += ROLLOUT_BS) {
+      const R u0 = R(Ub[j]), u1 = R(Ub[N + j]);
+      sU[4 * j + 0] = u0;
+      sU[4 * j + 1] = u1;
+      sU[4 * j + 2] = p.G00 * u0 + p.G01 * u1;
+      sU[4 * j + 3] = p.G10 * u0 + p.G11 * u1;
+    }
+    __syncthreads();
+  }
+
+  R cost = R(0);
+  int hits = 0;
+  R viol = R(0);
+  if (active) {
+    const double* x0 = buf.x0 + size_t(b) * MPPI_MAX_NX;
+    Model veh;
+    veh.init(p, x0);
+    const R gx0 = veh.s[0] - p.goal[0], gy0 = veh.s[1] - p.goal[1];
+    const R d0 = gx0 * gx0 + gy0 * gy0;
+    R stage = R(0);
+    R2* eps = reinterpret_cast<R2*>(buf.eps) + size_t(b) * N * p.K_local + k;
+    R cu0 = R(0), cu1 = R(0);
+    uint4 rnd = make_uint4(0, 0, 0, 0);
+    unsigned int iter = 0;
+    if (SRC == SRC_PHILOX) iter = *buf.iter;
+    if (SRC == SRC_DWA) {
+      cu0 = R(buf.cand[k]);
+      cu1 = R(buf.cand[size_t(p.K_local) + k]);
+    }
+    R2 e_next = R2{R(0), R(0)};
+    if (SRC == SRC_SUPPLIED) e_next = eps[0];
+    for (int j = 0; j < N; ++j) {
+      R u0, u1;
+      if (SRC == SRC_DWA) {
+        u0 = cu0; u1 = cu1;
+      } else {
+        R2 e;
+        if (SRC == SRC_SUPPLIED) {
+          e = e_next;
+          if (j + 1 < N) e_next = eps[size_t(j + 1) * p.K_local];   // prefetch next step's noise
+        } else {
+          if ((j & 1) == 0) rnd = philox4x32_10(make_uint4(uint32_t(p.k_offset + k), uint32_t(j >> 1), iter, uint32_t(b)),
+                                                p.seed_lo, p.seed_hi);
+          float z0, z1;
+          box_muller((j & 1) ? rnd.z : rnd.x, (j & 1) ? rnd.w : rnd.y, &z0, &z1);
+          e.x = p.L00 * R(z0);                       // eps = chol(Sigma) * z   (MPPIUtils.jl:6)
+          e.y = p.L10 * R(z0) + p.L11 * R(z1);
+          eps[size_t(j) * p.K_local] = e;            // kept for the update kernel / oracle replay
+        }
+        const R n0 = sU[4 * j + 0], n1 = sU[4 * j + 1];
+        u0 = Math<R>::fmin(Math<R>::fmax(n0 + e.x, p.CL[0]), p.CU[0]);   // PushInBounds (:13-20)
+        u1 = Math<R>::fmin(Math<R>::fmax(n1 + e.y, p.CL[1]), p.CU[1]);
+        stage += sU[4 * j + 2] * (u0 - n0) + sU[4 * j + 3] * (u1 - n1);  // lambda*U_nom'*inv(Sigma)*(u-U_nom) (:45)
+      }
+      stage += veh.stage_cost(p, u0, u1);            // VehicleDynamics cost at the pre-step state
+      veh.step(p, u0, u1);                           // Rungekutta2 (:76-90)
+      hits += circle_hits(p, veh.s[0], veh.s[1]);    // x_{j+1}: ObstacleEvaluation
+      hits += block_hits(p, veh.s[0], veh.s[1], veh.sn, veh.cs);
+      viol += bound_violation<R, Model::NX>(p, veh.s);   // BoundEvaluation
+    }
+    stage += veh.stage_cost(p, R(0), R(0));          // terminal slot: VehicleDynamics(x_N, [0,0]) (:49,:53)
+    const R gx = veh.s[0] - p.goal[0], gy = veh.s[1] - p.goal[1];
+    const R term = Math<R>::div(gx * gx + gy * gy, d0) * p.term_scale;   // (:54)
+    cost = stage + p.slack * viol + p.obs_pen * R(hits) + term;
+    buf.costs[size_t(b) * p.K_local + k] = cost;
+    buf.flags[size_t(b) * p.K_local + k] =
+        uint8_t(((hits == 0 && !(viol > R(0))) ? MPPI_FLAG_FEASIBLE : 0) | (hits ? MPPI_FLAG_COLLIDED : 0) |
+                ((viol > R(0)) ? MPPI_FLAG_OOB : 0));
+  }
+  // block epilogue: (min cost, first index) and feasible count -> one atomic each
+  unsigned long long key = active ? make_key(cost, (unsigned int)k) : 0xFFFFFFFFFFFFFFFFull;
+  key = warp_min_u64(key);
+  const unsigned feas_mask = __ballot_sync(0xffffffffu, active && hits == 0 && !(viol > R(0)));
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (lane == 0) { s_key[wid] = key; s_feas[wid] = __popc(feas_mask); }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int f = 0;
+#pragma unroll
+    for (int w = 0; w < ROLLOUT_BS / 32; ++w) { key = s_key[w] < key ? s_key[w] : key; f += s_feas[w]; }
+    atomicMin(&buf.scratch[b].rho_key, key);
+    if (f) atomicAdd(&buf.scratch[b].feasible_count, f);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Feasibility cut-off (MPPIUtils.jl:175,185): the reference stops sampling right
+// after the (feasibility_count+1)-th feasible sample; emulate by a prefix count
+// in sample order, then recompute (min, argmin) over the surviving prefix.
+// One block per instance.  Only launched when feasibility_count < K.
+// ---------------------------------------------------------------------------
+template <class R>
+__global__ void __launch_bounds__(CUTOFF_BS) cutoff_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) {
+  __shared__ int s_cnt[CUTOFF_BS];
+  __shared__ int s_keff, s_feas;
+  __shared__ unsigned long long s_key[CUTOFF_BS / 32];
+  __shared__ unsigned int s_arg[CUTOFF_BS / 32];
+  const int b = blockIdx.x, t = threadIdx.x;
+  const int K = p.K_local;
+  const uint8_t* fl = buf.flags + size_t(b) * K;
+  const R* cs = buf.costs + size_t(b) * K;
+  const int chunk = (K + CUTOFF_BS - 1) / CUTOFF_BS;
+  const int k0 = min(t * chunk, K), k1 = min(k0 + chunk, K);
+  int cnt = 0;
+  for (int k = k0; k < k1; ++k) cnt += fl[k] & MPPI_FLAG_FEASIBLE;
+  s_cnt[t] = cnt;
+  if (t == 0) { s_keff = K; s_feas = -1; }
+  __syncthreads();
+  // inclusive scan (Hillis-Steele; one block, not on the fast path)
+  for (int o = 1; o < CUTOFF_BS; o <<= 1) {
+    const int v = (t >= o) ? s_cnt[t - o] : 0;
+    __syncthreads();
+    s_cnt[t] += v;
+    __syncthreads();
+  }
+  const int incl = s_cnt[t], excl = incl - cnt;
+  const int target = p.feasibility_count + 1;   // loop exits once FeasibilityCount > feasibility_count
+  if (excl < target && target <= incl) {
+    int seen = excl;
+    for (int k = k0; k < k1; ++k) {
+      seen += fl[k] & MPPI_FLAG_FEASIBLE;
+      if (seen == target) { s_keff = k + 1; s_feas = target; break; }
+    }
+  }
+  __syncthreads();
+  const int keff = s_keff;
+  unsigned long long key = 0xFFFFFFFFFFFFFFFFull;
+  unsigned int arg = 0xFFFFFFFFu;
+  for (int k = k0; k < min(k1, keff); ++k) {
+    const unsigned long long kk = make_key(cs[k], (unsigned int)k);
+    if (kk < key) { key = kk; arg = k; }
+  }
+  // block min of (key, arg) — lexicographic so ties resolve to the first index
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long ok = shfl_xor_u64(key, o);
+    const unsigned int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (ok < key || (ok == key && oa < arg)) { key = ok; arg = oa; }
+  }
+  if ((t & 31) == 0) { s_key[t >> 5] = key; s_arg[t >> 5] = arg; }
+  __syncthreads();
+  if (t == 0) {
+    for (int w = 0; w < CUTOFF_BS / 32; ++w)
+      if (s_key[w] < key || (s_key[w] == key && s_arg[w] < arg)) { key = s_key[w]; arg = s_arg[w]; }
+    Scratch& sc = buf.scratch[b];
+    sc.rho_key = key;
+    sc.argmin = arg;
+    sc.k_eff = keff;
+    sc.feasible_count = (s_feas >= 0) ? s_feas : s_cnt[CUTOFF_BS - 1];
+  }
+}
+
+}  // namespace mppi

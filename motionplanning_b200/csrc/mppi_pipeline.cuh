@@ -1,0 +1,156 @@
+// mppi_pipeline.cuh — enqueue one MPPI iteration on the handle's stream, either
+// eagerly (profiling) or under stream capture into a CUDA graph that is
+// instantiated once per variant and replayed with a single cudaGraphLaunch.
+#pragma once
+#include "mppi_handle.cuh"
+
+namespace mppi {
+
+// what a step variant contains (bitmask)
+enum {
+  V_H2D_IN = 1,      // pinned x0/U_nom -> device
+  V_ADOPT = 2,       // U_nom <- previous U_new, device to device (main.jl:60-62)
+  V_LOCAL = 4,       // scratch reset, rollout, [cut-off], update
+  V_PARTIAL = 8,     // finalize<PH_PARTIAL>
+  V_D2H_PARTIAL = 16,
+  V_H2D_GATHERED = 32,
+  V_NCCL = 64,       // in-library all-gather of the partials
+  V_COMBINE = 128,   // finalize<PH_COMBINE> (+ nominal rollout)
+  V_D2H_RES = 256,
+  V_FUSED_FINAL = 512  // finalize<PH_PARTIAL|PH_COMBINE> in one kernel (single rank)
+};
+
+template <class R> const StaticParams<R>& params_of(const mppi_handle* h);
+template <> inline const StaticParams<float>& params_of<float>(const mppi_handle* h) { return h->pf; }
+template <> inline const StaticParams<double>& params_of<double>(const mppi_handle* h) { return h->pd; }
+
+template <class R, class Model, int SRC>
+int enqueue_variant(mppi_handle* h, int v, bool timed) {
+  const StaticParams<R>& p = params_of<R>(h);
+  Buffers<R> buf = make_buffers<R>(h);
+  if (v & V_FUSED_FINAL) { buf.gathered = buf.partial; buf.n_ranks = 1; }   // single rank: combine reads its own partial
+  const int B = h->cfg.B, N = h->cfg.N, K = h->K_local, nx = h->cfg.n_x;
+  cudaStream_t s = h->stream;
+  const size_t in_bytes = size_t(B) * (MPPI_MAX_NX + 2 * N) * sizeof(double);
+  const size_t res_bytes = size_t(B) * (RES_SCALARS + 2 * N) * sizeof(double);
+  const size_t smemU = size_t(N) * 4 * sizeof(R);
+
+  if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[0], s));
+  if (v & V_H2D_IN) MPPI_CUDA(h, cudaMemcpyAsync(h->d_in, h->h_in, in_bytes, cudaMemcpyHostToDevice, s));
+  if (v & V_ADOPT)
+    MPPI_CUDA(h, cudaMemcpyAsync(h->d_in + size_t(B) * MPPI_MAX_NX, h->d_res + size_t(B) * RES_SCALARS,
+                                 size_t(B) * 2 * N * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  if (v & V_LOCAL) {
+    MPPI_CUDA(h, cudaMemcpyAsync(h->d_scratch, h->d_scratch_tmpl, size_t(B) * sizeof(Scratch), cudaMemcpyDeviceToDevice, s));
+    dim3 grid((K + ROLLOUT_BS - 1) / ROLLOUT_BS, B);
+    rollout_kernel<R, Model, SRC><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
+    h->launches++;
+    if (h->cutoff && SRC != SRC_DWA) {
+      cutoff_kernel<R><<<B, CUTOFF_BS, 0, s>>>(p, buf);
+      h->launches++;
+    }
+    if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[1], s));
+    if (SRC != SRC_DWA) {
+      dim3 ug(h->ksplit, (N + UPDATE_JG - 1) / UPDATE_JG, B);
+      update_kernel<R><<<ug, UPDATE_BS, 0, s>>>(p, buf);
+      h->launches++;
+    }
+    if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[2], s));
+  }
+  const size_t smemF = size_t(N) * 6 * sizeof(R);
+  if (v & V_FUSED_FINAL) {
+    finalize_kernel<R, Model, SRC, PH_PARTIAL | PH_COMBINE><<<B, FINAL_BS, smemF, s>>>(p, buf);
+    h->launches++;
+  }
+  if (v & V_PARTIAL) {
+    finalize_kernel<R, Model, SRC, PH_PARTIAL><<<B, FINAL_BS, smemF, s>>>(p, buf);
+    h->launches++;
+  }
+  if (v & V_D2H_PARTIAL)
+    MPPI_CUDA(h, cudaMemcpyAsync(h->h_partial, h->d_partial, size_t(B) * h->plen * sizeof(double), cudaMemcpyDeviceToHost, s));
+  if (v & V_H2D_GATHERED)
+    MPPI_CUDA(h, cudaMemcpyAsync(h->d_gathered, h->h_gathered, size_t(h->n_ranks) * B * h->plen * sizeof(double),
+                                 cudaMemcpyHostToDevice, s));
+  if (v & V_NCCL) {
+    NcclApi& api = nccl_api();
+    ncclResult_t r = api.AllGather(h->d_partial, h->d_gathered, size_t(B) * h->plen, ncclFloat64, h->comm, s);
+    if (r != ncclSuccess) { h->err = std::string("ncclAllGather: ") + api.GetErrorString(r); return MPPI_ENCCL; }
+  }
+  if (v & V_COMBINE) {
+    finalize_kernel<R, Model, SRC, PH_COMBINE><<<B, FINAL_BS, smemF, s>>>(p, buf);
+    h->launches++;
+  }
+  if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[3], s));
+  if (v & V_D2H_RES) {
+    MPPI_CUDA(h, cudaMemcpyAsync(h->h_res, h->d_res, res_bytes, cudaMemcpyDeviceToHost, s));
+    if (B == 1)
+      MPPI_CUDA(h, cudaMemcpyAsync(h->h_traj, h->d_traj, size_t(N + 1) * nx * sizeof(double), cudaMemcpyDeviceToHost, s));
+  }
+  if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[4], s));
+  MPPI_CUDA(h, cudaGetLastError());
+  return MPPI_OK;
+}
+
+inline int source_of(const mppi_handle* h) {
+  if (h->cfg.planner == MPPI_PLANNER_DWA) return SRC_DWA;
+  return h->cfg.noise_mode == MPPI_NOISE_PHILOX ? SRC_PHILOX : SRC_SUPPLIED;
+}
+
+template <class R, class Model>
+int enqueue_src(mppi_handle* h, int v, bool timed) {
+  switch (source_of(h)) {
+    case SRC_PHILOX: return enqueue_variant<R, Model, SRC_PHILOX>(h, v, timed);
+    case SRC_DWA: return enqueue_variant<R, Model, SRC_DWA>(h, v, timed);
+    default: return enqueue_variant<R, Model, SRC_SUPPLIED>(h, v, timed);
+  }
+}
+template <class R>
+int enqueue_model(mppi_handle* h, int v, bool timed) {
+  if (h->cfg.model == MPPI_MODEL_DYNAMIC7) return enqueue_src<R, Dyn7<R>>(h, v, timed);
+  return enqueue_src<R, Kin5<R>>(h, v, timed);
+}
+inline int enqueue(mppi_handle* h, int v, bool timed) {
+  if (h->cfg.precision == MPPI_FP64) return enqueue_model<double>(h, v, timed);
+  return enqueue_model<float>(h, v, timed);
+}
+
+// number of kernels a variant launches (for mppi_launch_count under graph replay)
+inline int kernels_in(const mppi_handle* h, int v) {
+  int n = 0;
+  const bool dwa = h->cfg.planner == MPPI_PLANNER_DWA;
+  if (v & V_LOCAL) n += 1 + ((h->cutoff && !dwa) ? 1 : 0) + (dwa ? 0 : 1);
+  if (v & V_FUSED_FINAL) n++;
+  if (v & V_PARTIAL) n++;
+  if (v & V_COMBINE) n++;
+  return n;
+}
+
+// run a variant: graph replay (captured on first use) or eager when profiling / graphs are off
+inline int run_variant(mppi_handle* h, int v) {
+  const bool use_graph = h->cfg.use_cuda_graph && !h->profiling;
+  if (!use_graph) {
+    int rc = enqueue(h, v, h->profiling);
+    return rc;
+  }
+  auto it = h->graphs.find(v);
+  if (it == h->graphs.end()) {
+    cudaGraph_t g = nullptr;
+    const int64_t before = h->launches;
+    MPPI_CUDA(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+    int rc = enqueue(h, v, false);
+    cudaError_t e = cudaStreamEndCapture(h->stream, &g);
+    h->launches = before;
+    if (rc != MPPI_OK) { if (g) cudaGraphDestroy(g); return rc; }
+    if (e != cudaSuccess) { h->err = std::string("cudaStreamEndCapture: ") + cudaGetErrorString(e); return MPPI_ECUDA; }
+    cudaGraphExec_t ex = nullptr;
+    e = cudaGraphInstantiate(&ex, g, 0);
+    cudaGraphDestroy(g);
+    if (e != cudaSuccess) { h->err = std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e); return MPPI_ECUDA; }
+    it = h->graphs.emplace(v, ex).first;
+  }
+  MPPI_CUDA(h, cudaGraphLaunch(it->second, h->stream));
+  h->launches += kernels_in(h, v);
+  return MPPI_OK;
+}
+
+}  // namespace mppi

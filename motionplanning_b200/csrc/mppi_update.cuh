@@ -1,0 +1,277 @@
+// mppi_update.cuh — softmin weighting + weighted control update, and the
+// finalize (partial -> combine -> nominal rollout) kernel.
+#pragma once
+#include "mppi_kernels.cuh"
+
+namespace mppi {
+
+// 2 consecutive samples x 2 controls of one horizon step: [k][0..1], [k+1][0..1]
+template <class R> struct Pair;
+template <> struct Pair<float> {
+  float4 v;
+  __device__ __forceinline__ void load(const float* p) { v = __ldcs(reinterpret_cast<const float4*>(p)); }
+  __device__ __forceinline__ void load1(const float* p) { const float2 t = __ldcs(reinterpret_cast<const float2*>(p)); v = make_float4(t.x, t.y, 0.f, 0.f); }
+};
+template <> struct Pair<double> {
+  double4 v;
+  __device__ __forceinline__ void load(const double* p) {
+    const double2 a = __ldcs(reinterpret_cast<const double2*>(p)), c = __ldcs(reinterpret_cast<const double2*>(p) + 1);
+    v = make_double4(a.x, a.y, c.x, c.y);
+  }
+  __device__ __forceinline__ void load1(const double* p) { const double2 a = __ldcs(reinterpret_cast<const double2*>(p)); v = make_double4(a.x, a.y, 0., 0.); }
+};
+
+// ---------------------------------------------------------------------------
+// update_kernel: S[j][c] = sum_k exp(-(c_k - rho)/lambda) * clamp(U_nom[j][c] + eps[j][k][c])
+// (MPPIUtils.jl:154-167 weights, :187-190 weighted sum of the CLAMPED controls;
+// the 1/eta normalisation is applied once in finalize).  A K x (N*m) streaming
+// reduction: each eps element is read exactly once, 16 B per lane per load,
+// UPDATE_JG independent loads in flight per lane; weights are recomputed from
+// the (L2-resident) costs, never materialised.  HBM/L2-bound; no tensor cores —
+// this is a GEMV-shaped contraction with arithmetic intensity ~0.5 flop/B.
+// grid = (ksplit, ceil(N/UPDATE_JG), B); deterministic: fixed partition, fixed
+// tree, partials summed in fixed order by finalize (no float atomics).
+// ---------------------------------------------------------------------------
+template <class R>
+__global__ void __launch_bounds__(UPDATE_BS) update_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) {
+  __shared__ R s_red[UPDATE_BS / 32][2 * UPDATE_JG + 1];
+  const int b = blockIdx.z, N = p.N, K = p.K_local;
+  const int j0 = blockIdx.y * UPDATE_JG;
+  const Scratch sc = buf.scratch[b];
+  const int keff = sc.k_eff;
+  const R rho = key_cost(sc.rho_key, R(0));
+  int chunk = (K + gridDim.x - 1) / gridDim.x;
+  chunk = (chunk + 1) & ~1;
+  const int k0 = blockIdx.x * chunk, k1 = min(k0 + chunk, keff);
+  const bool lead = (blockIdx.y == 0);
+  const bool vec_ok = (K & 1) == 0;
+
+  R n0[UPDATE_JG], n1[UPDATE_JG], acc0[UPDATE_JG], acc1[UPDATE_JG];
+  const double* Ub = buf.U + size_t(b) * 2 * N;
+#pragma unroll
+  for (int jj = 0; jj < UPDATE_JG; ++jj) {
+    const int j = min(j0 + jj, N - 1);
+    n0[jj] = R(Ub[j]); n1[jj] = R(Ub[N + j]);
+    acc0[jj] = R(0); acc1[jj] = R(0);
+  }
+  R eta = R(0);
+  const R* cs = buf.costs + size_t(b) * K;
+  const R* eb = buf.eps + size_t(b) * N * K * 2;
+  for (int k = k0 + 2 * threadIdx.x; k < k1; k += 2 * UPDATE_BS) {
+    const bool two = (k + 1 < k1);
+    const R c0 = cs[k], c1 = two ? cs[k + 1] : R(0);
+    const R w0 = Math<R>::exp((rho - c0) * p.inv_lambda);
+    const R w1 = two ? Math<R>::exp((rho - c1) * p.inv_lambda) : R(0);
+    if (lead) {
+      eta += w0 + w1;
+      if (sizeof(R) == 8) {   // FP64 key carries no index: first index with cost == rho
+        if (c0 == rho) atomicMin(&buf.scratch[b].argmin, (unsigned int)k);
+        if (two && c1 == rho) atomicMin(&buf.scratch[b].argmin, (unsigned int)(k + 1));
+      }
+    }
+    Pair<R> e[UPDATE_JG];
+#pragma unroll
+    for (int jj = 0; jj < UPDATE_JG; ++jj) {
+      const int j = min(j0 + jj, N - 1);
+      const R* src = eb + (size_t(j) * K + k) * 2;
+      if (two && vec_ok) e[jj].load(src);
+      else { e[jj].load1(src); if (two) { Pair<R> t; t.load1(src + 2); e[jj].v.z = t.v.x; e[jj].v.w = t.v.y; } }
+    }
+#pragma unroll
+    for (int jj = 0; jj < UPDATE_JG; ++jj) {
+      const R ua0 = Math<R>::fmin(Math<R>::fmax(n0[jj] + e[jj].v.x, p.CL[0]), p.CU[0]);
+      const R ua1 = Math<R>::fmin(Math<R>::fmax(n1[jj] + e[jj].v.y, p.CL[1]), p.CU[1]);
+      const R ub0 = Math<R>::fmin(Math<R>::fmax(n0[jj] + e[jj].v.z, p.CL[0]), p.CU[0]);
+      const R ub1 = Math<R>::fmin(Math<R>::fmax(n1[jj] + e[jj].v.w, p.CL[1]), p.CU[1]);
+      acc0[jj] += w0 * ua0 + w1 * ub0;
+      acc1[jj] += w0 * ua1 + w1 * ub1;
+    }
+  }
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+  for (int jj = 0; jj < UPDATE_JG; ++jj) {
+    acc0[jj] = warp_sum(acc0[jj]);
+    acc1[jj] = warp_sum(acc1[jj]);
+  }
+  eta = warp_sum(eta);
+  if (lane == 0) {
+#pragma unroll
+    for (int jj = 0; jj < UPDATE_JG; ++jj) { s_red[wid][2 * jj] = acc0[jj]; s_red[wid][2 * jj + 1] = acc1[jj]; }
+    s_red[wid][2 * UPDATE_JG] = eta;
+  }
+  __syncthreads();
+  if (threadIdx.x < 2 * UPDATE_JG + 1) {
+    R s = R(0);
+#pragma unroll
+    for (int w = 0; w < UPDATE_BS / 32; ++w) s += s_red[w][threadIdx.x];
+    if (threadIdx.x == 2 * UPDATE_JG) {
+      if (lead) buf.eta_part[size_t(b) * gridDim.x + blockIdx.x] = s;
+    } else {
+      const int j = j0 + (threadIdx.x >> 1);
+      if (j < N) buf.Spart[((size_t(b) * gridDim.x + blockIdx.x) * N + j) * 2 + (threadIdx.x & 1)] = s;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// finalize_kernel.  One block per instance.
+//   PH_PARTIAL: sum the update partials in fixed order -> this rank's
+//               (rho, eta, argmin, counts, S) against its LOCAL rho.
+//   PH_COMBINE: fold all ranks' partials in rank order with the rescale
+//               e^{-(rho_g - rho)/lambda} (one-shot softmin combine), U_new = S/eta,
+//               then the final nominal rollout (MPPIUtils.jl:192-198) on thread 0.
+// DWA (DWAUtils.jl:152-158): U_new = the arg-min candidate, replicated over the horizon.
+// ---------------------------------------------------------------------------
+enum { PH_PARTIAL = 1, PH_COMBINE = 2 };
+
+template <class R, class Model, int SRC, int PHASES>
+__global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  R* sU = reinterpret_cast<R*>(smem_raw);        // [N][4]: U_nom0, U_nom1, g0, g1
+  R* sNew = sU + 4 * p.N;                        // [N][2]: U_new
+  __shared__ double s_scale[8];
+  __shared__ double s_hdr[4];
+  const int b = blockIdx.x, N = p.N, t = threadIdx.x;
+  const int plen = PART_HDR + 2 * N;
+  double* part = buf.partial + size_t(b) * plen;
+  const Scratch sc = buf.scratch[b];
+
+  if (PHASES & PH_PARTIAL) {
+    if (SRC == SRC_DWA) {
+      // arg-min candidate (DWAUtils.jl:152).  FP32 keys carry the index; FP64 keys do not:
+      // first index whose cost equals rho.
+      __shared__ unsigned int s_arg;
+      const R rho = key_cost(sc.rho_key, R(0));
+      if (t == 0) s_arg = (sizeof(R) == 4) ? (unsigned int)(sc.rho_key & 0xFFFFFFFFull) : 0xFFFFFFFFu;
+      __syncthreads();
+      if (sizeof(R) == 8) {
+        const R* cs = buf.costs + size_t(b) * p.K_local;
+        for (int k = t; k < p.K_local; k += FINAL_BS)
+          if (cs[k] == rho) atomicMin(&s_arg, (unsigned int)k);
+        __syncthreads();
+      }
+      if (t == 0) {
+        part[PART_RHO] = double(rho);
+        part[PART_ETA] = 1.0;
+        part[PART_ARGMIN] = double(s_arg) + double(p.k_offset);
+        part[PART_ROLLOUTS] = double(sc.k_eff);
+        part[PART_FEASIBLE] = double(sc.feasible_count);
+      }
+    } else {
+      for (int i = t; i < 2 * N; i += FINAL_BS) {   // i = c*N + j (col-major N x m)
+        const int c = i / N, j = i - c * N;
+        double s = 0.0;
+        for (int ks = 0; ks < buf.ksplit; ++ks) s += double(buf.Spart[((size_t(b) * buf.ksplit + ks) * N + j) * 2 + c]);
+        part[PART_HDR + i] = s;
+      }
+      if (t == 0) {
+        double eta = 0.0;
+        for (int ks = 0; ks < buf.ksplit; ++ks) eta += double(buf.eta_part[size_t(b) * buf.ksplit + ks]);
+        part[PART_RHO] = double(key_cost(sc.rho_key, R(0)));
+        part[PART_ETA] = eta;
+        // FP32 key carries the index unless the cut-off kernel wrote argmin explicitly
+        const unsigned int arg = (sizeof(R) == 4 && sc.argmin == 0xFFFFFFFFu) ? (unsigned int)(sc.rho_key & 0xFFFFFFFFull) : sc.argmin;
+        part[PART_ARGMIN] = double(arg) + double(p.k_offset);
+        part[PART_ROLLOUTS] = double(sc.k_eff);
+        part[PART_FEASIBLE] = double(sc.feasible_count);
+      }
+    }
+    __syncthreads();   // block-scope visibility of `part` for the combine phase (G == 1)
+  }
+  if (!(PHASES & PH_COMBINE)) return;
+
+  const int G = buf.n_ranks;
+  const double* gat = buf.gathered;   // [G][B][plen]
+  if (t == 0) {
+    // global rho = isless-min over ranks (NaN last); ties -> lowest rank == lowest global index
+    int best = 0;
+    double rho = gat[(size_t(0) * p.B + b) * plen + PART_RHO];
+    for (int g = 1; g < G; ++g) {
+      const double r = gat[(size_t(g) * p.B + b) * plen + PART_RHO];
+      if (r < rho || (r == r && rho != rho)) { rho = r; best = g; }
+    }
+    double eta = 0.0, rollouts = 0.0, feas = 0.0;
+    for (int g = 0; g < G; ++g) {
+      const double* pg = gat + (size_t(g) * p.B + b) * plen;
+      const double sc_g = (G == 1) ? 1.0 : exp(-(pg[PART_RHO] - rho) / double(p.lambda));
+      s_scale[g] = sc_g;
+      eta += pg[PART_ETA] * sc_g;
+      rollouts += pg[PART_ROLLOUTS];
+      feas += pg[PART_FEASIBLE];
+    }
+    s_hdr[0] = eta;
+    double* rs = buf.res_scalars + size_t(b) * RES_SCALARS;
+    rs[RES_ROLLOUTS] = rollouts + 1.0;   // RolloutCount starts at 1 (MPPIUtils.jl:171,197)
+    rs[RES_FEASCOUNT] = feas;
+    rs[RES_ARGMIN] = gat[(size_t(best) * p.B + b) * plen + PART_ARGMIN] + 1.0;   // 1-based like Julia
+    rs[RES_RHO] = rho;
+    rs[RES_ETA] = eta;
+  }
+  // stage old nominal + g for the nominal rollout's control-cost term (evaluated
+  // against the OLD U_nom: MPPIUtils.jl:192 runs before main.jl:62 replaces it)
+  const double* Ub = buf.U + size_t(b) * 2 * N;
+  for (int j = t; j < N; j += FINAL_BS) {
+    const R u0 = (SRC == SRC_DWA) ? R(0) : R(Ub[j]), u1 = (SRC == SRC_DWA) ? R(0) : R(Ub[N + j]);
+    sU[4 * j + 0] = u0; sU[4 * j + 1] = u1;
+    sU[4 * j + 2] = p.G00 * u0 + p.G01 * u1;
+    sU[4 * j + 3] = p.G10 * u0 + p.G11 * u1;
+  }
+  __syncthreads();
+  double* rc = buf.res_control + size_t(b) * 2 * N;
+  if (SRC == SRC_DWA) {
+    const size_t arg = size_t(buf.res_scalars[size_t(b) * RES_SCALARS + RES_ARGMIN] - 1.0) - p.k_offset;
+    for (int i = t; i < 2 * N; i += FINAL_BS) {
+      const int c = i / N, j = i - c * N;
+      const double u = buf.cand[size_t(c) * p.K_local + arg];
+      rc[i] = u;
+      sNew[2 * j + c] = R(u);
+    }
+  } else {
+    const double eta = s_hdr[0];
+    for (int i = t; i < 2 * N; i += FINAL_BS) {
+      const int c = i / N, j = i - c * N;
+      double s = 0.0;
+      for (int g = 0; g < G; ++g) s += gat[(size_t(g) * p.B + b) * plen + PART_HDR + i] * s_scale[g];
+      const double u = s / eta;
+      rc[i] = u;
+      sNew[2 * j + c] = R(u);
+    }
+  }
+  __syncthreads();
+  if (t == 0) {
+    // final nominal rollout, TrajectoryRollout(MPPI, MPPICtrl) (MPPIUtils.jl:192)
+    const int NX = Model::NX;
+    double* tr = buf.res_traj + size_t(b) * (N + 1) * NX;   // col-major (N+1) x n_x
+    Model veh;
+    veh.init(p, buf.x0 + size_t(b) * MPPI_MAX_NX);
+    const R gx0 = veh.s[0] - p.goal[0], gy0 = veh.s[1] - p.goal[1];
+    const R d0 = gx0 * gx0 + gy0 * gy0;
+    R stage = R(0), viol = R(0);
+    int hits = 0;
+#pragma unroll
+    for (int i = 0; i < NX; ++i) tr[size_t(i) * (N + 1)] = double(veh.s[i]);
+    for (int j = 0; j < N; ++j) {
+      const R u0 = sNew[2 * j], u1 = sNew[2 * j + 1];
+      if (SRC != SRC_DWA) stage += sU[4 * j + 2] * (u0 - sU[4 * j]) + sU[4 * j + 3] * (u1 - sU[4 * j + 1]);
+      stage += veh.stage_cost(p, u0, u1);
+      veh.step(p, u0, u1);
+      hits += circle_hits(p, veh.s[0], veh.s[1]);
+      hits += block_hits(p, veh.s[0], veh.s[1], veh.sn, veh.cs);
+      viol += bound_violation<R, Model::NX>(p, veh.s);
+#pragma unroll
+      for (int i = 0; i < NX; ++i) tr[size_t(i) * (N + 1) + j + 1] = double(veh.s[i]);
+    }
+    stage += veh.stage_cost(p, R(0), R(0));
+    const R gx = veh.s[0] - p.goal[0], gy = veh.s[1] - p.goal[1];
+    const R term = Math<R>::div(gx * gx + gy * gy, d0) * p.term_scale;
+    const R cost = stage + p.slack * viol + p.obs_pen * R(hits) + term;
+    double* rs = buf.res_scalars + size_t(b) * RES_SCALARS;
+    const bool feas = (hits == 0 && !(viol > R(0)));
+    rs[RES_COST] = double(cost);
+    rs[RES_FEASIBLE] = feas ? 1.0 : 0.0;
+    rs[RES_FLAGS] = double((feas ? MPPI_FLAG_FEASIBLE : 0) | (hits ? MPPI_FLAG_COLLIDED : 0) | ((viol > R(0)) ? MPPI_FLAG_OOB : 0));
+    if (b == 0) *buf.iter += 1;   // next step draws fresh Philox noise
+  }
+}
+
+}  // namespace mppi

@@ -1,0 +1,298 @@
+"""Host-side mirror of the reference's Julia MPPI interface, over the C ABI.
+
+Same names, positional arguments and error behaviour as
+OptimalControl/MPPI/src/setup.jl and MPPIUtils.jl (Julia's `!` suffix is dropped:
+``defineMPPIobs!`` -> ``defineMPPIobs``), so the parity tests read like the
+reference's own ``main.jl``:
+
+    mppi = defineMPPI(numStates, numControls, lambda_, X0, goal, SamplingNumber, Sigma, N, T, XL, XU, CL, CU)
+    defineMPPIobs(mppi, [[50.0, 1, 2.5], ...])
+    ShiftInitialCondition(mppi, states)
+    defineMPPINominalControl(mppi, NominalControls)
+    MPPIPlan(mppi)
+    mppi.r.Control, mppi.r.Traj, mppi.r.Feasibility, mppi.r.cost, mppi.r.RolloutCount
+
+Everything numerical happens in libmppi_b200.so (CUDA, sm_100a).  No CPU path.
+julia/MPPIB200.jl is the same shim written with `ccall`.
+"""
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import _capi as capi
+
+
+class MPPIError(RuntimeError):
+    """Raised where the reference calls error(...) (setup.jl:19-39) or the library fails."""
+
+
+def _dptr(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+@dataclass
+class MPPISetting:  # types.jl:10-31
+    numStates: int = 0
+    numControls: int = 0
+    X0: np.ndarray = None
+    XL: np.ndarray = None
+    XU: np.ndarray = None
+    CL: np.ndarray = None
+    CU: np.ndarray = None
+    dt: float = 0.0
+    T: float = 0.0
+    N: int = 0
+    goal: np.ndarray = None
+    obstacle_list: list = field(default_factory=list)
+    block_list: list = field(default_factory=list)
+    SamplingNumber: int = 0
+    FeasibilityCount: int = 1300
+    NominalControl: np.ndarray = None
+    Σ: np.ndarray = None
+    Sigma: np.ndarray = None
+    lambda_: float = 0.02
+    SlackPenalty: float = 1e5
+
+
+class MPPIPlanner:  # types.jl:32-34
+    """``p.TrajectoryCollection`` is materialised lazily from device memory."""
+
+    def __init__(self, searcher):
+        self._m = searcher
+
+    @property
+    def costs(self):
+        return self._m._costs()
+
+    @property
+    def flags(self):
+        return self._m._flags()
+
+    def sample_xy(self, stride=1):
+        """xy of every stride-th sampled trajectory (plotRes, MPPIUtils.jl:221-223)."""
+        return self._m._sample_xy(stride)
+
+
+@dataclass
+class MPPIResult:  # types.jl:36-44
+    Traj: np.ndarray = None
+    Control: np.ndarray = None
+    Feasibility: str = "InFeasible"
+    cost: float = 1e6
+    time: float = 0.0
+    FeasibleTrajCount: int = 0
+    RolloutCount: int = 0
+    argmin: int = 0
+    rho: float = 0.0
+    eta: float = 0.0
+
+
+class MPPISearcher:  # types.jl:46-50
+    def __init__(self, cfg):
+        self._lib = capi.load()
+        self._cfg = cfg
+        self._h = capi._H()
+        rc = self._lib.mppi_create(C.byref(cfg), C.byref(self._h))
+        if rc != capi.MPPI_OK:
+            raise MPPIError(self._lib.mppi_last_error(None).decode())
+        self.s = MPPISetting()
+        self.p = MPPIPlanner(self)
+        self.r = MPPIResult()
+
+    # -- plumbing ---------------------------------------------------------
+    def _check(self, rc):
+        if rc != capi.MPPI_OK:
+            raise MPPIError(self._lib.mppi_last_error(self._h).decode())
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.mppi_destroy(self._h)
+            self._h = capi._H()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def K_local(self):
+        return self._cfg.K_local if self._cfg.K_local > 0 else self._cfg.K
+
+    def _costs(self):
+        out = np.empty(self._cfg.B * self.K_local, dtype=np.float64)
+        self._check(self._lib.mppi_get_costs(self._h, _dptr(out)))
+        return out
+
+    def _flags(self):
+        out = np.empty(self._cfg.B * self.K_local, dtype=np.uint8)
+        self._check(self._lib.mppi_get_flags(self._h, out.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return out
+
+    def noise(self):
+        """eps used by the last step, shape (N, K_local, m) in C order == Julia (m, K, N)."""
+        dt = np.float64 if self._cfg.precision == capi.FP64 else np.float32
+        out = np.empty((self._cfg.N, self.K_local, 2), dtype=dt)
+        self._check(self._lib.mppi_get_noise(self._h, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def _sample_xy(self, stride):
+        n = C.c_int32(0)
+        self._check(self._lib.mppi_get_sample_xy(self._h, stride, None, C.byref(n)))
+        out = np.empty((n.value, self._cfg.N + 1, 2), dtype=np.float32)
+        self._check(self._lib.mppi_get_sample_xy(self._h, stride, out.ctypes.data_as(C.POINTER(C.c_float)), C.byref(n)))
+        return out
+
+    def timings_us(self):
+        us = (C.c_float * 4)()
+        self._check(self._lib.mppi_get_timings(self._h, us))
+        return list(us)
+
+    def launch_count(self):
+        return int(self._lib.mppi_launch_count(self._h))
+
+
+def _fill(arr, vals):
+    for i, v in enumerate(vals):
+        arr[i] = float(v)
+
+
+def defineMPPI(numStates=0, numControls=0, lambda_=0.25, X0=None, goal=None, SamplingNumber=500, Sigma=None,
+               N=15, T=3.0, XL=None, XU=None, CL=None, CU=None, *, model=None, precision=capi.FP32,
+               noise_mode=capi.NOISE_PHILOX, seed=0x5EED0001, device=0, FeasibilityCount=1300,
+               use_cuda_graph=True, k_offset=0, K_local=0, B=1, planner=capi.PLANNER_MPPI, **overrides):
+    """defineMPPI (setup.jl:3-59).  Positional arguments as in the reference; keyword-only
+    arguments select what the reference fixes by `include` or does not have (model,
+    precision, noise source, device, sample shard)."""
+    X0 = np.full(numStates, np.nan) if X0 is None else np.asarray(X0, dtype=np.float64)
+    goal = np.full(2, np.nan) if goal is None else np.asarray(goal, dtype=np.float64)
+    Sigma = np.eye(max(numControls, 0)) if Sigma is None else np.asarray(Sigma, dtype=np.float64)
+    XL = np.full(numStates, np.nan) if XL is None else np.asarray(XL, dtype=np.float64)
+    XU = np.full(numStates, np.nan) if XU is None else np.asarray(XU, dtype=np.float64)
+    CL = np.full(numControls, np.nan) if CL is None else np.asarray(CL, dtype=np.float64)
+    CU = np.full(numControls, np.nan) if CU is None else np.asarray(CU, dtype=np.float64)
+    # setup.jl:19-39, same order and wording
+    if numControls <= 0:
+        raise MPPIError(f"Controls ({numControls}) must be > 0")
+    if numStates <= 0:
+        raise MPPIError(f"States ({numStates}) must be > 0")
+    x0_len = X0.shape[0] if X0.ndim == 1 else X0.shape[0]
+    if x0_len != numStates:
+        raise MPPIError(f"Length of X0 ({x0_len}) must match number of states ({numStates})")
+    if len(XL) != numStates:
+        raise MPPIError(f"Length of XL ({len(XL)}) must match number of states ({numStates})")
+    if len(XU) != numStates:
+        raise MPPIError(f"Length of XU ({len(XU)}) must match number of states ({numStates})")
+    if len(CL) != numControls:
+        raise MPPIError(f"Length of CL ({len(CL)}) must match number of controls ({numControls})")
+    if len(CU) != numControls:
+        raise MPPIError(f"Length of CU ({len(CU)}) must match number of controls ({numControls})")
+
+    cfg = capi.default_config()
+    if model is None:
+        model = capi.MODEL_DYNAMIC7 if numStates == 7 else capi.MODEL_KINEMATIC5
+    cfg.model, cfg.n_x, cfg.m = model, numStates, numControls
+    cfg.K, cfg.N, cfg.B = int(SamplingNumber), int(N), int(B)
+    cfg.precision, cfg.noise_mode, cfg.planner = precision, noise_mode, planner
+    cfg.feasibility_count = int(FeasibilityCount)
+    cfg.use_cuda_graph = 1 if use_cuda_graph else 0
+    cfg.device, cfg.k_offset, cfg.K_local = device, k_offset, K_local
+    cfg.seed = seed
+    cfg.T, cfg.lambda_ = float(T), float(lambda_)
+    _fill(cfg.Sigma, np.asarray(Sigma, dtype=np.float64).reshape(-1, order="F"))
+    x0_first = X0 if X0.ndim == 1 else X0[:, 0]
+    _fill(cfg.X0, x0_first)
+    _fill(cfg.goal, goal)
+    _fill(cfg.XL, XL)
+    _fill(cfg.XU, XU)
+    _fill(cfg.CL, CL)
+    _fill(cfg.CU, CU)
+    for k, v in overrides.items():
+        cur = getattr(cfg, k)
+        if hasattr(cur, "__len__"):
+            _fill(cur, v)
+        else:
+            setattr(cfg, k, v)
+
+    mppi = MPPISearcher(cfg)
+    s = mppi.s
+    s.goal, s.numStates, s.numControls, s.lambda_ = goal, numStates, numControls, lambda_
+    s.X0, s.XL, s.XU, s.CL, s.CU = X0, XL, XU, CL, CU
+    s.T, s.N, s.dt = T, N, T / N  # setup.jl:53
+    s.SamplingNumber = SamplingNumber
+    s.FeasibilityCount = FeasibilityCount
+    shape = (N, numControls) if B == 1 else (N, numControls, B)
+    s.NominalControl = np.zeros(shape)  # setup.jl:55
+    s.Σ = s.Sigma = Sigma
+    if X0.ndim == 2:
+        ShiftInitialCondition(mppi, X0)
+    return mppi
+
+
+def defineMPPIobs(mppi, obstacle_list):
+    """defineMPPIobs! (setup.jl:61-64): list of [x, y, r] circles."""
+    mppi.s.obstacle_list = obstacle_list
+    a = np.ascontiguousarray(np.asarray(obstacle_list, dtype=np.float64).reshape(-1, 3))
+    mppi._check(mppi._lib.mppi_set_circles(mppi._h, _dptr(a), a.shape[0]))
+
+
+def defineMPPIblocks(mppi, block_list):
+    """Polygon walls, block = [cx, cy, psi, half_len, half_wid] (CollisionDetection utils.jl:14-25)."""
+    mppi.s.block_list = block_list
+    a = np.ascontiguousarray(np.asarray(block_list, dtype=np.float64).reshape(-1, 5))
+    mppi._check(mppi._lib.mppi_set_blocks(mppi._h, _dptr(a), a.shape[0]))
+
+
+def defineMPPINominalControl(mppi, *args):
+    """defineMPPINominalControl! (setup.jl:70-80): (U) or (U, Sigma)."""
+    U = np.asarray(args[0], dtype=np.float64)
+    mppi.s.NominalControl = U
+    Uf = np.asfortranarray(U)
+    if U.ndim == 3:  # (N, m, B): instance-major blocks of col-major N x m
+        Uf = np.ascontiguousarray(np.transpose(U, (2, 1, 0)))
+    mppi._check(mppi._lib.mppi_set_nominal(mppi._h, _dptr(Uf), U.shape[0], U.shape[1]))
+    if len(args) > 1:
+        Sigma = np.asarray(args[1], dtype=np.float64)
+        mppi.s.Σ = mppi.s.Sigma = Sigma
+        Sf = np.asfortranarray(Sigma)
+        mppi._check(mppi._lib.mppi_set_sigma_lambda(mppi._h, _dptr(Sf), float(mppi.s.lambda_)))
+
+
+def ShiftInitialCondition(mppi, X0):
+    """ShiftInitialCondition (MPPIUtils.jl:24-27)."""
+    X0 = np.asarray(X0, dtype=np.float64)
+    mppi.s.X0 = X0
+    a = np.ascontiguousarray(X0 if X0.ndim == 1 else X0.T)  # (B, n_x) rows == n_x x B col-major
+    mppi._check(mppi._lib.mppi_set_x0(mppi._h, _dptr(a), X0.shape[0]))
+
+
+def MPPIPlan(mppi, noise=None):
+    """MPPIPlan (MPPIUtils.jl:169-203).  `noise` (N, K, m) only in SUPPLIED-noise mode."""
+    cfg = mppi._cfg
+    N, nx = cfg.N, cfg.n_x
+    ctrl = np.empty((N, 2), dtype=np.float64, order="F")
+    traj = np.empty((N + 1, nx), dtype=np.float64, order="F")
+    res = capi.Result()
+    res.Control, res.Traj = _dptr(ctrl), _dptr(traj)
+    nptr = None
+    if noise is not None:
+        want = np.float64 if cfg.precision == capi.FP64 else np.float32
+        noise = np.ascontiguousarray(noise, dtype=want)
+        if noise.shape != (N, mppi.K_local, 2):
+            raise MPPIError(f"noise must have shape (N, K, m) = ({N}, {mppi.K_local}, 2), got {noise.shape}")
+        nptr = noise.ctypes.data_as(C.c_void_p)
+    mppi._check(mppi._lib.mppi_step(mppi._h, nptr, C.byref(res)))
+    _store(mppi, res, ctrl, traj)
+    return None
+
+
+def _store(mppi, res, ctrl, traj):
+    r = mppi.r
+    r.Traj, r.Control = traj, ctrl  # MPPIUtils.jl:193-194
+    r.Feasibility = "Feasible" if res.feasible else "InFeasible"  # :195
+    r.cost = res.cost  # :196
+    r.RolloutCount = res.rollout_count  # :197
+    r.FeasibleTrajCount = res.feasible_count  # :198
+    r.time = res.time_s  # :200
+    r.argmin, r.rho, r.eta = res.argmin_index, res.rho, res.eta

@@ -1,0 +1,195 @@
+// oracle_capi.cpp — extern "C" surface of the CPU oracle for ctypes.
+// TEST INFRASTRUCTURE ONLY (see mppi_oracle.hpp header): loaded by tests/,
+// __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
+#include "mppi_oracle_plan.hpp"
+
+using namespace oracle;
+
+template <class R>
+static Params<R> make_params(const mppi_config_t* c, const double* circles, int Mc,
+                             const double* blocks, int Mp) {
+  Params<R> p;
+  p.model = c->model; p.n_x = c->n_x; p.m = c->m; p.N = c->N;
+  p.dt = R(c->T / c->N);  // setup.jl:53
+  p.lambda = R(c->lambda);
+  for (int i = 0; i < 4; ++i) p.Sigma[i] = R(c->Sigma[i]);
+  for (int i = 0; i < 2; ++i) { p.goal[i] = R(c->goal[i]); p.CL[i] = R(c->CL[i]); p.CU[i] = R(c->CU[i]); }
+  for (int i = 0; i < MPPI_MAX_NX; ++i) { p.XL[i] = R(c->XL[i]); p.XU[i] = R(c->XU[i]); }
+  p.slack_penalty = R(c->slack_penalty); p.obstacle_penalty = R(c->obstacle_penalty);
+  p.terminal_scale = R(c->terminal_scale);
+  p.la = R(c->la); p.lb = R(c->lb); p.mass = R(c->mass); p.Izz = R(c->Izz); p.g = R(c->g);
+  p.mu = R(c->mu); p.KFZF = R(c->KFZF); p.KFZR = R(c->KFZR); p.KFZX = R(c->KFZX);
+  for (int i = 0; i < 6; ++i) { p.tire[i] = R(c->tire[i]); p.w[i] = R(c->stage_w[i]); }
+  p.veh_L = R(c->veh_L); p.veh_W = R(c->veh_W); p.veh_off = R(c->veh_center_offset);
+  p.planner = c->planner;
+  p.circles.resize(size_t(3) * Mc);
+  for (int i = 0; i < 3 * Mc; ++i) p.circles[i] = R(circles[i]);
+  p.blocks.resize(size_t(5) * Mp);
+  for (int i = 0; i < 5 * Mp; ++i) p.blocks[i] = R(blocks[i]);
+  p.wall_pts.resize(size_t(10) * Mp);
+  for (int i = 0; i < Mp; ++i) get_rectangle_pts(&p.blocks[5 * i], &p.wall_pts[10 * i]);  // Block2Pts
+  return p;
+}
+
+template <class R>
+static void plan_impl(const mppi_config_t* cfg, const double* circles, int Mc, const double* blocks,
+                      int Mp, const double* x0, const double* Unom, const void* eps_or_cand,
+                      int threads, int want_margin, double* costs, uint8_t* flags, double* margins,
+                      double* U_new, double* traj, double* scalars) {
+  Params<R> p = make_params<R>(cfg, circles, Mc, blocks, Mp);
+  const int N = p.N, m = p.m, nx = p.n_x, K = cfg->K;
+  R x0r[MPPI_MAX_NX];
+  for (int i = 0; i < nx; ++i) x0r[i] = R(x0[i]);
+  std::vector<R> nom(size_t(N) * m, R(0));
+  if (Unom)
+    for (int j = 0; j < N; ++j)
+      for (int c = 0; c < m; ++c) nom[j * m + c] = R(Unom[c * N + j]);  // col-major in
+  PlanOut<R> out;
+  if (cfg->planner == MPPI_PLANNER_DWA) {
+    const double* cand = (const double*)eps_or_cand;  // K x m col-major
+    std::vector<R> cr(size_t(K) * m);
+    for (int k = 0; k < K; ++k)
+      for (int c = 0; c < m; ++c) cr[size_t(k) * m + c] = R(cand[size_t(c) * K + k]);
+    dwa_plan(p, x0r, cr.data(), K, threads, &out);
+  } else {
+    mppi_plan(p, x0r, nom.data(), (const R*)eps_or_cand, K, cfg->feasibility_count, threads,
+              want_margin != 0, &out);
+  }
+  if (costs) for (int k = 0; k < K; ++k) costs[k] = double(out.costs[k]);
+  if (flags) for (int k = 0; k < K; ++k) flags[k] = out.flags[k];
+  if (margins && want_margin && !out.margins.empty())
+    for (int k = 0; k < K; ++k) margins[k] = double(out.margins[k]);
+  if (U_new)
+    for (int j = 0; j < N; ++j)
+      for (int c = 0; c < m; ++c) U_new[c * N + j] = double(out.control[j * m + c]);
+  if (traj)
+    for (int j = 0; j <= N; ++j)
+      for (int i = 0; i < nx; ++i) traj[i * (N + 1) + j] = double(out.nominal.states_his[size_t(j) * nx + i]);
+  if (scalars) {
+    scalars[0] = double(out.nominal.cost_total);
+    scalars[1] = out.nominal.feasible ? 1.0 : 0.0;
+    scalars[2] = out.rollout_count;
+    scalars[3] = out.feasible_count;
+    scalars[4] = out.argmin + 1;  // 1-based like Julia's argmin
+    scalars[5] = double(out.rho);
+    scalars[6] = double(out.eta);
+    scalars[7] = out.seconds;
+    scalars[8] = double(out.nominal_margin);
+    scalars[9] = (out.nominal.collided ? 2.0 : 0.0) + (out.nominal.oob ? 4.0 : 0.0);
+  }
+}
+
+template <class R>
+static void rollout_impl(const mppi_config_t* cfg, const double* circles, int Mc,
+                         const double* blocks, int Mp, const double* x0, const double* Unom,
+                         const double* ctrl, double* traj, double* scalars) {
+  Params<R> p = make_params<R>(cfg, circles, Mc, blocks, Mp);
+  const int N = p.N, m = p.m, nx = p.n_x;
+  R x0r[MPPI_MAX_NX];
+  for (int i = 0; i < nx; ++i) x0r[i] = R(x0[i]);
+  std::vector<R> nom(size_t(N) * m, R(0)), u(size_t(N) * m, R(0));
+  for (int j = 0; j < N; ++j)
+    for (int c = 0; c < m; ++c) {
+      if (Unom) nom[j * m + c] = R(Unom[c * N + j]);
+      u[j * m + c] = R(ctrl[c * N + j]);
+    }
+  Rollout<R> ro;
+  Margin<R> mg;
+  trajectory_rollout(p, x0r, u.data(), nom.data(), &ro, &mg, true);
+  if (traj)
+    for (int j = 0; j <= N; ++j)
+      for (int i = 0; i < nx; ++i) traj[i * (N + 1) + j] = double(ro.states_his[size_t(j) * nx + i]);
+  scalars[0] = double(ro.cost_total);
+  scalars[1] = ro.feasible ? 1.0 : 0.0;
+  scalars[2] = ro.collided ? 1.0 : 0.0;
+  scalars[3] = ro.oob ? 1.0 : 0.0;
+  scalars[4] = double(mg.v);
+}
+
+extern "C" {
+
+// MPPIPlan / DWAPlan on supplied noise (MPPI: eps [N][K][m] of float|double by
+// `precision`; DWA: candidates K x m col-major double).  Arrays are col-major double.
+int oracle_plan(const mppi_config_t* cfg, const double* circles, int Mc, const double* blocks, int Mp,
+                const double* x0, const double* Unom, const void* eps_or_cand, int precision,
+                int threads, int want_margin, double* costs, uint8_t* flags, double* margins,
+                double* U_new, double* traj, double* scalars) {
+  if (precision == MPPI_FP32)
+    plan_impl<float>(cfg, circles, Mc, blocks, Mp, x0, Unom, eps_or_cand, threads, want_margin, costs,
+                     flags, margins, U_new, traj, scalars);
+  else
+    plan_impl<double>(cfg, circles, Mc, blocks, Mp, x0, Unom, eps_or_cand, threads, want_margin, costs,
+                      flags, margins, U_new, traj, scalars);
+  return 0;
+}
+
+// TrajectoryRollout of one control sequence (N x m col-major, already clamped).
+int oracle_rollout(const mppi_config_t* cfg, const double* circles, int Mc, const double* blocks,
+                   int Mp, const double* x0, const double* Unom, const double* ctrl, int precision,
+                   double* traj, double* scalars) {
+  if (precision == MPPI_FP32) rollout_impl<float>(cfg, circles, Mc, blocks, Mp, x0, Unom, ctrl, traj, scalars);
+  else rollout_impl<double>(cfg, circles, Mc, blocks, Mp, x0, Unom, ctrl, traj, scalars);
+  return 0;
+}
+
+// VehicleDynamics(states, ctrl) -> (dstates, constraint, cost), FP64.
+int oracle_vehicle_dynamics(const mppi_config_t* cfg, const double* x, const double* u, double* dx,
+                            double* cons_cost) {
+  Params<double> p = make_params<double>(cfg, nullptr, 0, nullptr, 0);
+  vehicle_dynamics(p, x, u, dx, &cons_cost[0], &cons_cost[1]);
+  return 0;
+}
+
+int oracle_rungekutta2(const mppi_config_t* cfg, const double* x, const double* u, double* x_next,
+                       double* cons_cost) {
+  Params<double> p = make_params<double>(cfg, nullptr, 0, nullptr, 0);
+  int cons; double pc;
+  rungekutta2(p, x, u, p.dt, x_next, &cons, &pc);
+  cons_cost[0] = cons; cons_cost[1] = pc;
+  return 0;
+}
+
+void oracle_get_rectangle_pts(const double* block, double* pts10) { get_rectangle_pts(block, pts10); }
+int oracle_sat(const double* base, int nb, const double* other, int no) {
+  return separating_axis_theorem<double>(base, nb, other, no, nullptr) ? 1 : 0;
+}
+// ConvexCollision on point sets (2 x n col-major); 1 = collision-free
+int oracle_convex_collision(const double* p1, int n1, const double* p2, int n2) {
+  return convex_collision<double>(p1, n1, p2, n2, nullptr) ? 1 : 0;
+}
+double oracle_mod_pi(double a) { return mod_pi(a); }
+
+// block_collision_check per pose: hit[i] = number of obstacles pose i collides with
+int oracle_check_poses(const mppi_config_t* cfg, const double* circles, int Mc, const double* blocks,
+                       int Mp, const double* poses, int n, int* hit, double* margins) {
+  Params<double> p = make_params<double>(cfg, circles, Mc, blocks, Mp);
+  for (int i = 0; i < n; ++i) {
+    const double s[2] = {poses[3 * i], poses[3 * i + 1]};
+    int cons = 1; double cost = 0; Margin<double> mg;
+    obstacle_evaluation_circles(p, s, &cons, &cost, &mg);
+    obstacle_evaluation_blocks(p, poses[3 * i], poses[3 * i + 1], poses[3 * i + 2], &cons, &cost, &mg);
+    hit[i] = int(std::lround(cost / p.obstacle_penalty));
+    if (margins) margins[i] = mg.v;
+  }
+  return 0;
+}
+
+void oracle_philox4x32_10(const uint32_t* ctr, const uint32_t* key, uint32_t* out) {
+  philox4x32_10(ctr, key, out);
+}
+
+int oracle_generate_noise(const double* Sigma, uint64_t seed, uint32_t iteration, uint32_t instance,
+                          int k_offset, int K, int N, int precision, void* eps) {
+  if (precision == MPPI_FP32) generate_noise<float>(Sigma, seed, iteration, instance, k_offset, K, N, (float*)eps);
+  else generate_noise<double>(Sigma, seed, iteration, instance, k_offset, K, N, (double*)eps);
+  return 0;
+}
+
+int oracle_weights(const double* cost, int n, double lambda, double* w, double* rho_eta, int* argmin) {
+  std::vector<double> wv;
+  calculate_mppi_weights(cost, n, lambda, &wv, argmin, &rho_eta[0], &rho_eta[1]);
+  for (int i = 0; i < n; ++i) w[i] = wv[i];
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,198 @@
+"""ctypes wrapper of the CPU oracle (oracle/libmppi_oracle.so).
+
+Test infrastructure: imported only by tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs.  Never by the product.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from motionplanning_b200 import _capi as capi
+from motionplanning_b200 import mppi as host
+
+_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(_ROOT, "oracle")
+ORACLE_SO = os.path.join(ORACLE_DIR, "libmppi_oracle.so")
+
+_lib = None
+_dp = C.POINTER(C.c_double)
+
+
+def _d(a):
+    return None if a is None else a.ctypes.data_as(_dp)
+
+
+def load():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(ORACLE_SO):
+            subprocess.check_call(["make", "-C", ORACLE_DIR])
+        _lib = C.CDLL(ORACLE_SO)
+        _lib.oracle_mod_pi.restype = C.c_double
+        _lib.oracle_mod_pi.argtypes = [C.c_double]
+    return _lib
+
+
+def make_config(args, kwargs):
+    """Build the mppi_config_t that defineMPPI(*args, **kwargs) would build, without a GPU."""
+    (numStates, numControls, lambda_, X0, goal, K, Sigma, N, T, XL, XU, CL, CU) = args
+    kw = dict(kwargs)
+    cfg = capi.default_config()
+    cfg.model = kw.pop("model", capi.MODEL_DYNAMIC7 if numStates == 7 else capi.MODEL_KINEMATIC5)
+    cfg.n_x, cfg.m, cfg.K, cfg.N, cfg.B = numStates, numControls, K, N, kw.pop("B", 1)
+    cfg.precision = kw.pop("precision", capi.FP32)
+    cfg.noise_mode = kw.pop("noise_mode", capi.NOISE_PHILOX)
+    cfg.planner = kw.pop("planner", capi.PLANNER_MPPI)
+    cfg.feasibility_count = kw.pop("FeasibilityCount", 1300)
+    cfg.seed = kw.pop("seed", 0x5EED0001)
+    cfg.k_offset, cfg.K_local = kw.pop("k_offset", 0), kw.pop("K_local", 0)
+    kw.pop("device", None), kw.pop("use_cuda_graph", None)
+    cfg.T, cfg.lambda_ = float(T), float(lambda_)
+    host._fill(cfg.Sigma, np.asarray(Sigma, dtype=np.float64).reshape(-1, order="F"))
+    x0 = np.asarray(X0, dtype=np.float64)
+    host._fill(cfg.X0, x0 if x0.ndim == 1 else x0[:, 0])
+    host._fill(cfg.goal, goal), host._fill(cfg.XL, XL), host._fill(cfg.XU, XU)
+    host._fill(cfg.CL, CL), host._fill(cfg.CU, CU)
+    for k, v in kw.items():
+        cur = getattr(cfg, k)
+        if hasattr(cur, "__len__"):
+            host._fill(cur, v)
+        else:
+            setattr(cfg, k, v)
+    return cfg
+
+
+def _obs(circles, blocks):
+    c = np.ascontiguousarray(np.asarray(circles, dtype=np.float64).reshape(-1, 3))
+    b = np.ascontiguousarray(np.asarray(blocks, dtype=np.float64).reshape(-1, 5))
+    return c, b
+
+
+def plan(cfg, circles, blocks, x0, Unom, eps_or_cand, precision=capi.FP64, threads=1, want_margin=False):
+    """MPPIPlan / DWAPlan on supplied noise.  Returns a dict of numpy outputs."""
+    lib = load()
+    c, b = _obs(circles, blocks)
+    N, nx, K = cfg.N, cfg.n_x, cfg.K
+    x0 = np.ascontiguousarray(x0, dtype=np.float64)
+    Un = None if Unom is None else np.asfortranarray(np.asarray(Unom, dtype=np.float64))
+    if cfg.planner == capi.PLANNER_DWA:
+        src = np.asfortranarray(np.asarray(eps_or_cand, dtype=np.float64))
+    else:
+        src = np.ascontiguousarray(eps_or_cand, dtype=np.float64 if precision == capi.FP64 else np.float32)
+        assert src.shape == (N, K, 2), src.shape
+    costs = np.empty(K)
+    flags = np.empty(K, dtype=np.uint8)
+    margins = np.full(K, np.inf)
+    U_new = np.empty((N, 2), order="F")
+    traj = np.empty((N + 1, nx), order="F")
+    sc = np.zeros(10)
+    lib.oracle_plan(C.byref(cfg), _d(c), c.shape[0], _d(b), b.shape[0], _d(x0), _d(Un),
+                    src.ctypes.data_as(C.c_void_p), precision, threads, 1 if want_margin else 0,
+                    _d(costs), flags.ctypes.data_as(C.POINTER(C.c_uint8)), _d(margins), _d(U_new), _d(traj), _d(sc))
+    return dict(costs=costs, flags=flags, margins=margins, Control=U_new, Traj=traj, cost=sc[0],
+                feasible=bool(sc[1]), rollout_count=int(sc[2]), feasible_count=int(sc[3]), argmin=int(sc[4]),
+                rho=sc[5], eta=sc[6], seconds=sc[7], nominal_margin=sc[8], nominal_flags=int(sc[9]))
+
+
+def rollout(cfg, circles, blocks, x0, Unom, ctrl, precision=capi.FP64):
+    lib = load()
+    c, b = _obs(circles, blocks)
+    N, nx = cfg.N, cfg.n_x
+    x0 = np.ascontiguousarray(x0, dtype=np.float64)
+    Un = None if Unom is None else np.asfortranarray(np.asarray(Unom, dtype=np.float64))
+    u = np.asfortranarray(np.asarray(ctrl, dtype=np.float64))
+    traj = np.empty((N + 1, nx), order="F")
+    sc = np.zeros(5)
+    lib.oracle_rollout(C.byref(cfg), _d(c), c.shape[0], _d(b), b.shape[0], _d(x0), _d(Un), _d(u), precision,
+                       _d(traj), _d(sc))
+    return dict(Traj=traj, cost=sc[0], feasible=bool(sc[1]), collided=bool(sc[2]), oob=bool(sc[3]), margin=sc[4])
+
+
+def vehicle_dynamics(cfg, x, u):
+    lib = load()
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    u = np.ascontiguousarray(u, dtype=np.float64)
+    dx = np.zeros(cfg.n_x)
+    cc = np.zeros(2)
+    lib.oracle_vehicle_dynamics(C.byref(cfg), _d(x), _d(u), _d(dx), _d(cc))
+    return dx, cc[0], cc[1]
+
+
+def rungekutta2(cfg, x, u):
+    lib = load()
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    u = np.ascontiguousarray(u, dtype=np.float64)
+    xn = np.zeros(cfg.n_x)
+    cc = np.zeros(2)
+    lib.oracle_rungekutta2(C.byref(cfg), _d(x), _d(u), _d(xn), _d(cc))
+    return xn, int(cc[0]), cc[1]
+
+
+def get_rectangle_pts(block):
+    lib = load()
+    b = np.ascontiguousarray(block, dtype=np.float64)
+    pts = np.zeros((5, 2))
+    lib.oracle_get_rectangle_pts(_d(b), _d(pts))
+    return pts.T.copy()  # 2 x 5 like Julia
+
+
+def _cols(p):
+    return np.ascontiguousarray(np.asarray(p, dtype=np.float64).T)  # (n, 2) rows == 2 x n col-major
+
+
+def sat(base, other):
+    lib = load()
+    a, b = _cols(base), _cols(other)
+    return bool(lib.oracle_sat(_d(a), a.shape[0], _d(b), b.shape[0]))
+
+
+def convex_collision(p1, p2):
+    lib = load()
+    a, b = _cols(p1), _cols(p2)
+    return bool(lib.oracle_convex_collision(_d(a), a.shape[0], _d(b), b.shape[0]))
+
+
+def mod_pi(a):
+    return load().oracle_mod_pi(float(a))
+
+
+def check_poses(cfg, circles, blocks, poses):
+    lib = load()
+    c, b = _obs(circles, blocks)
+    p = np.ascontiguousarray(np.asarray(poses, dtype=np.float64).reshape(-1, 3))
+    hit = np.zeros(p.shape[0], dtype=np.int32)
+    mg = np.zeros(p.shape[0])
+    lib.oracle_check_poses(C.byref(cfg), _d(c), c.shape[0], _d(b), b.shape[0], _d(p), p.shape[0],
+                           hit.ctypes.data_as(C.POINTER(C.c_int32)), _d(mg))
+    return hit, mg
+
+
+def philox(ctr, key):
+    lib = load()
+    c = np.asarray(ctr, dtype=np.uint32)
+    k = np.asarray(key, dtype=np.uint32)
+    out = np.zeros(4, dtype=np.uint32)
+    u32 = C.POINTER(C.c_uint32)
+    lib.oracle_philox4x32_10(c.ctypes.data_as(u32), k.ctypes.data_as(u32), out.ctypes.data_as(u32))
+    return out
+
+
+def generate_noise(Sigma, seed, iteration, K, N, precision=capi.FP64, k_offset=0, instance=0):
+    lib = load()
+    S = np.asarray(Sigma, dtype=np.float64).reshape(-1, order="F").copy()
+    out = np.empty((N, K, 2), dtype=np.float64 if precision == capi.FP64 else np.float32)
+    lib.oracle_generate_noise(_d(S), C.c_uint64(seed), C.c_uint32(iteration), C.c_uint32(instance), k_offset, K, N,
+                              precision, out.ctypes.data_as(C.c_void_p))
+    return out
+
+
+def weights(costs, lambda_):
+    lib = load()
+    c = np.ascontiguousarray(costs, dtype=np.float64)
+    w = np.empty_like(c)
+    re = np.zeros(2)
+    am = C.c_int(0)
+    lib.oracle_weights(_d(c), c.shape[0], C.c_double(lambda_), _d(w), _d(re), C.byref(am))
+    return w, re[0], re[1], am.value

@@ -1,0 +1,168 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle on identical supplied noise.
+
+Tolerances (BASELINE.json north_star): per-sample costs and updated controls within 1e-9
+relative in FP64 verification mode and 1e-4 relative in FP32 mode; argmin index and
+feasibility / collision flags identical.  In FP32 mode "identical flags" is checked outside a
+guard band: samples for which some threshold comparison in the FP64 oracle sits closer than
+GUARD (relative) to flipping are excluded and counted.
+"""
+import numpy as np
+import pytest
+
+import motionplanning_b200 as m
+import oracle_lib as orc
+from motionplanning_b200 import scenarios as sc
+
+capi = m.capi
+pytestmark = pytest.mark.gpu
+
+FP64_TOL = 1e-9
+FP32_TOL = 1e-4
+GUARD = 1e-4
+
+
+def run_pair(args, kw, circles, blocks, precision, Unom=None, eps=None, iteration=0):
+    """Run one MPPIPlan on the GPU and in the oracle on the same supplied noise."""
+    kw = dict(kw, precision=precision, noise_mode=capi.NOISE_SUPPLIED)
+    K, N = args[5], args[7]
+    if eps is None:
+        eps = orc.generate_noise(args[6], kw.get("seed", sc.SEED), iteration, K, N, capi.FP64)
+    mppi = m.defineMPPI(*args, **kw)
+    if circles:
+        m.defineMPPIobs(mppi, circles)
+    if blocks:
+        m.defineMPPIblocks(mppi, blocks)
+    if Unom is not None:
+        m.defineMPPINominalControl(mppi, Unom)
+    m.MPPIPlan(mppi, eps)
+    cfg = orc.make_config(args, kw)
+    # the FP64 oracle is the arbiter in both modes; in FP32 mode it sees the noise the GPU saw
+    eps_ref = eps.astype(np.float32).astype(np.float64) if precision == capi.FP32 else eps
+    ref = orc.plan(cfg, circles, blocks, args[3], np.zeros((N, 2)) if Unom is None else Unom, eps_ref, capi.FP64,
+                   threads=8, want_margin=True)
+    return mppi, ref
+
+
+def check(mppi, ref, precision):
+    tol = FP64_TOL if precision == capi.FP64 else FP32_TOL
+    costs, flags = mppi.p.costs, mppi.p.flags
+    R = ref["rollout_count"] - 1
+    ok = np.ones(len(costs), dtype=bool)
+    if precision == capi.FP32:
+        ok = ref["margins"] > GUARD
+        assert (~ok[:R]).sum() <= 0.02 * R, f"{(~ok[:R]).sum()} guard-band samples of {R}"
+    ok[R:] = False  # samples past the feasibility cut-off are never drawn by the reference
+    rel = np.abs(costs - ref["costs"]) / np.maximum(np.abs(ref["costs"]), 1e-300)
+    assert rel[ok].max() <= tol, f"per-sample cost rel err {rel[ok].max():.3e}"
+    assert np.array_equal(flags[ok], ref["flags"][ok]), "feasible/collided/oob flags differ"
+    assert mppi.r.RolloutCount == ref["rollout_count"]
+    if precision == capi.FP64:
+        assert mppi.r.argmin == ref["argmin"]
+        assert mppi.r.FeasibleTrajCount == ref["feasible_count"]
+        assert mppi.r.rho == pytest.approx(ref["rho"], rel=tol)
+    else:
+        # argmin must be identical unless the two best costs are closer than FP32 can resolve
+        srt = np.sort(ref["costs"][:R])
+        if (srt[1] - srt[0]) > 4 * tol * abs(srt[0]) and ok[ref["argmin"] - 1]:
+            assert mppi.r.argmin == ref["argmin"]
+    assert mppi.r.eta == pytest.approx(ref["eta"], rel=10 * tol if precision == capi.FP64 else 2e-3)
+    scale = max(np.abs(ref["Control"]).max(), 1e-12)
+    du = np.abs(mppi.r.Control - ref["Control"]).max() / scale
+    assert du <= tol, f"updated control err {du:.3e} (normwise)"
+    dtr = np.abs(mppi.r.Traj - ref["Traj"]).max()
+    assert dtr <= (1e-9 if precision == capi.FP64 else 2e-3), f"nominal trajectory err {dtr:.3e}"
+    if ref["nominal_margin"] > GUARD or precision == capi.FP64:
+        assert mppi.r.cost == pytest.approx(ref["cost"], rel=tol)
+        assert mppi.r.Feasibility == ("Feasible" if ref["feasible"] else "InFeasible")
+
+
+def warm_nominal(N, seed=3):
+    """A non-trivial nominal control so the lambda*U_nom'*inv(Sigma)*(u-U_nom) term is exercised."""
+    rng = np.random.RandomState(seed)
+    t = np.linspace(0, 1, N)
+    return np.stack([0.1 * np.sin(4 * t) + 0.02 * rng.randn(N), 0.8 * np.cos(3 * t) + 0.1 * rng.randn(N)], axis=1)
+
+
+@pytest.mark.parametrize("precision", [capi.FP64, capi.FP32])
+def test_config1_kinematic_circles(built, precision):
+    args, kw, circles, blocks = sc.config(0)
+    mppi, ref = run_pair(args, kw, circles, blocks, precision)
+    check(mppi, ref, precision)
+    mppi, ref = run_pair(args, kw, circles, blocks, precision, Unom=warm_nominal(args[7]))
+    check(mppi, ref, precision)
+
+
+@pytest.mark.parametrize("precision", [capi.FP64, capi.FP32])
+def test_reference_demo_dynamic_circles_with_cutoff(built, precision):
+    """The scenario the reference actually ships (MPPI/main.jl:7-30): 7-state dynamic bicycle,
+    3 circles, K=1500, N=20, T=3, FeasibilityCount=1300 (cut-off active)."""
+    X0, XL, XU = sc.X0_DYN, sc.XL_DYN, sc.XU_DYN
+    args = (7, 2, 25.0, X0, [110, 0], 1500, sc.SIGMA, 20, 3.0, XL, XU, sc.CL, sc.CU)
+    kw = dict(FeasibilityCount=1300)
+    mppi, ref = run_pair(args, kw, sc.CIRCLES, [], precision)
+    check(mppi, ref, precision)
+    # a state close to the first obstacle so that collisions and infeasible samples occur
+    args2 = (7, 2, 25.0, [42.0, 0.6, 0.1, 0.02, 0.05, 8.0, 0.01], [110, 0], 1500, sc.SIGMA, 20, 3.0, XL, XU, sc.CL, sc.CU)
+    mppi, ref = run_pair(args2, kw, sc.CIRCLES, [], precision, Unom=warm_nominal(20))
+    assert (ref["flags"] & capi.FLAG_COLLIDED).any() and (ref["flags"] & capi.FLAG_FEASIBLE).any()
+    check(mppi, ref, precision)
+
+
+@pytest.mark.parametrize("precision", [capi.FP64, capi.FP32])
+def test_cutoff_triggers(built, precision):
+    """K = 2048 > 1301 feasible: the reference's early exit truncates the collection (MPPIUtils.jl:175,185)."""
+    args, kw, circles, blocks = sc.config(0, K=2048)
+    kw["FeasibilityCount"] = 1300
+    mppi, ref = run_pair(args, kw, circles, blocks, precision)
+    assert ref["rollout_count"] - 1 < 2048 and ref["feasible_count"] == 1301
+    check(mppi, ref, precision)
+
+
+@pytest.mark.parametrize("precision", [capi.FP64, capi.FP32])
+def test_config3_parking_polygon_walls(built, precision):
+    args, kw, circles, blocks = sc.config(2, K=4096, N=80)
+    mppi, ref = run_pair(args, kw, circles, blocks, precision)
+    assert (ref["flags"] & capi.FLAG_COLLIDED).any()
+    check(mppi, ref, precision)
+
+
+@pytest.mark.parametrize("precision", [capi.FP64, capi.FP32])
+@pytest.mark.parametrize("M_p", [3, 16])
+def test_config4_dynamic_polygon_walls(built, precision, M_p):
+    args, kw, circles, blocks = sc.config(3, K=4096, N=100, M_p=M_p)
+    mppi, ref = run_pair(args, kw, circles, blocks, precision, Unom=warm_nominal(100))
+    check(mppi, ref, precision)
+
+
+def test_odd_sizes_and_ragged_tail(built):
+    """K not a multiple of the block size / of 2, N odd: ragged edges of every kernel."""
+    for K, N in [(1, 1), (3, 7), (129, 33), (1001, 51)]:
+        args, kw, circles, blocks = sc.config(0, K=K, N=N)
+        mppi, ref = run_pair(args, kw, circles, blocks, capi.FP64, Unom=warm_nominal(N))
+        check(mppi, ref, capi.FP64)
+
+
+def test_no_obstacles_and_many_circles(built):
+    args, kw, _, _ = sc.config(0, K=512, N=20)
+    mppi, ref = run_pair(args, kw, [], [], capi.FP64)
+    check(mppi, ref, capi.FP64)
+    rng = np.random.RandomState(0)
+    circles = [[rng.uniform(5, 60), rng.uniform(-6, 6), rng.uniform(0.5, 2.0)] for _ in range(64)]
+    mppi, ref = run_pair(args, kw, circles, [], capi.FP64)
+    assert (ref["flags"] & capi.FLAG_COLLIDED).any()
+    check(mppi, ref, capi.FP64)
+
+
+def test_graph_and_eager_agree_bitwise(built):
+    args, kw, circles, blocks = sc.config(0, K=2048)
+    eps = orc.generate_noise(args[6], sc.SEED, 0, 2048, 50, capi.FP64)
+    outs = []
+    for graph in (True, False):
+        k2 = dict(kw, precision=capi.FP32, noise_mode=capi.NOISE_SUPPLIED, use_cuda_graph=graph)
+        mppi = m.defineMPPI(*args, **k2)
+        m.defineMPPIobs(mppi, circles)
+        m.MPPIPlan(mppi, eps)
+        m.MPPIPlan(mppi, eps)  # replay
+        outs.append((mppi.r.Control.copy(), mppi.p.costs.copy(), mppi.r.cost))
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+    assert outs[0][2] == outs[1][2]

@@ -1,0 +1,96 @@
+"""Pin the oracle's VehicleDynamics (vehicledynamics.jl:1-54) against the reference's own
+committed closed-loop logs (tests/golden/*.csv, made by tests/golden/make_golden.py from
+OptimalControl/MPPI/MPPITrajectory.csv and OptimalControl/DynamicWindow/DWATrajectory.csv).
+
+main.jl:76-78 integrates the plant with explicit Euler at 1 ms:
+    row[k+1] = row[k] + VehicleDynamics(row[k], u)[1] * 1e-3
+so each consecutive row pair is a known-answer vector for the derivative output.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as orc
+from motionplanning_b200 import _capi as capi
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+DT = 1e-3
+
+
+def _pairs(name):
+    a = np.loadtxt(os.path.join(GOLD, name), delimiter=",", comments="#")
+    return a[:, 0].astype(int), a[:, 1:8], a[:, 8:15]
+
+
+@pytest.mark.parametrize("name", ["mppi_plant_pairs.csv", "dwa_plant_pairs.csv"])
+def test_vehicle_dynamics_matches_reference_logs(built, name):
+    cfg = capi.default_config()
+    ks, xk, xk1 = _pairs(name)
+    assert len(ks) > 300
+    worst = 0.0
+    for x, xn in zip(xk, xk1):
+        # controls recovered from the log: dsa = sr, dux = ax  (vehicledynamics.jl:48-49)
+        sr = (xn[6] - x[6]) / DT
+        ax = (xn[5] - x[5]) / DT
+        dx, cons, cost = orc.vehicle_dynamics(cfg, x, [sr, ax])
+        pred = x + dx * DT
+        worst = max(worst, np.abs(pred - xn).max())
+        assert cons == 0.0
+    assert worst <= 1e-12, worst
+
+
+def test_stage_cost_formula(built):
+    # vehicledynamics.jl:52 evaluated by hand
+    cfg = capi.default_config()
+    x = np.array([3.0, 0.7, -0.3, 0.2, 0.1, 6.0, 0.05])
+    u = np.array([0.25, -1.5])
+    _, _, cost = orc.vehicle_dynamics(cfg, x, u)
+    want = x[2] ** 2 * 1 + 1 * x[3] ** 2 + 5 * u[1] ** 2 + 3 * u[0] ** 2 + 2 * x[6] ** 2 + 10 * x[1] ** 2
+    assert cost == pytest.approx(want, rel=1e-15)
+
+
+def test_ux_clamp_only_affects_position_and_dv(built):
+    # vehicledynamics.jl:40-42: ux <- max(ux, 0) AFTER the slip angles
+    cfg = capi.default_config()
+    x = np.array([0.0, 0.0, 0.4, 0.1, 0.3, -2.0, 0.02])
+    dx, _, _ = orc.vehicle_dynamics(cfg, x, [0.0, 0.0])
+    assert dx[0] == pytest.approx(-0.4 * np.sin(0.3), rel=1e-14)   # ux term vanished
+    assert dx[1] == pytest.approx(0.4 * np.cos(0.3), rel=1e-14)
+    # slips still use ux = -2: compare with a by-hand evaluation
+    mu, B, Cc, E = 0.8, -10.4 / 0.8, 1.3, 0.1556
+    den = -2.0 + 0.01
+    af = np.arctan((0.4 + 1.56 * 0.1) / den) - 0.02
+    ar = np.arctan((0.4 - 1.64 * 0.1) / den)
+    rv = 0.1 * 0.4
+    FZF = 2 * (1018.28 / 2 * 9.81 - (0 - rv) * 186.22)
+    FZR = 2 * (963.34 / 2 * 9.81 + (0 - rv) * 186.22)
+    fy = lambda FZ, a: mu * FZ * 1.0 * np.sin(Cc * np.arctan(B * a - E * (B * a - np.arctan(B * a))))
+    FY1, FY2 = fy(FZF, af), fy(FZR, ar)
+    assert dx[2] == pytest.approx((FY1 + FY2) / 2020 - 0.1 * 0.0, rel=1e-13)
+    assert dx[3] == pytest.approx((FY1 * 1.56 - FY2 * 1.64) / 4095, rel=1e-13)
+
+
+def test_kinematic_model(built):
+    # Parking/src/VehicleModel.jl:14-18
+    cfg = capi.default_config()
+    cfg.model, cfg.n_x = capi.MODEL_KINEMATIC5, 5
+    x = np.array([1.0, -0.5, 0.3, 4.0, 0.1])
+    dx, cons, cost = orc.vehicle_dynamics(cfg, x, [0.2, -1.0])
+    L = 1.56 + 1.64
+    np.testing.assert_allclose(dx, [4 * np.cos(0.3), 4 * np.sin(0.3), 4 / L * np.tan(0.1), -1.0, 0.2], rtol=1e-15)
+    assert cons == 0.0
+    assert cost == pytest.approx(5 * 1.0 + 3 * 0.04 + 2 * 0.01 + 10 * 0.25, rel=1e-15)
+
+
+def test_heun_step(built):
+    # MPPIUtils.jl:76-90
+    cfg = capi.default_config()
+    x = np.array([0.0, 0.1, 0.2, 0.05, 0.1, 5.0, 0.01])
+    u = [0.1, 1.0]
+    dt = cfg.T / cfg.N
+    k1, _, c1 = orc.vehicle_dynamics(cfg, x, u)
+    k2, _, _ = orc.vehicle_dynamics(cfg, x + k1 * dt, u)
+    xn, cons, pc = orc.rungekutta2(cfg, x, u)
+    np.testing.assert_allclose(xn, x + dt * (k1 + k2) / 2, rtol=0, atol=1e-15)
+    assert cons == 1 and pc == c1

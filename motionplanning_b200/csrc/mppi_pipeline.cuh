@@ -148,7 +148,11 @@ inline int run_variant(mppi_handle* h, int v) {
     if (e != cudaSuccess) { h->err = std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e); return MPPI_ECUDA; }
     it = h->graphs.emplace(v, ex).first;
   }
+  // bracket the replay with events on the launching stream so callers can read the
+  // device time of the whole step (mppi_get_timings()[3]) without a profiler
+  MPPI_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
   MPPI_CUDA(h, cudaGraphLaunch(it->second, h->stream));
+  MPPI_CUDA(h, cudaEventRecord(h->ev[4], h->stream));
   h->launches += kernels_in(h, v);
   return MPPI_OK;
 }

@@ -152,6 +152,95 @@ class MPPISearcher:  # types.jl:46-50
     def launch_count(self):
         return int(self._lib.mppi_launch_count(self._h))
 
+    # -- device-resident loop (main.jl:59-62 without the host round trip) ---
+    def step_async(self, adopt=False):
+        self._check(self._lib.mppi_step_async(self._h, 1 if adopt else 0))
+
+    def sync(self):
+        self._check(self._lib.mppi_sync(self._h))
+
+    def adopt_nominal(self):
+        self._check(self._lib.mppi_adopt_nominal(self._h))
+
+    def fetch_result(self):
+        N, nx = self._cfg.N, self._cfg.n_x
+        ctrl = np.empty((N, 2), dtype=np.float64, order="F")
+        traj = np.empty((N + 1, nx), dtype=np.float64, order="F")
+        res = capi.Result()
+        res.Control, res.Traj = _dptr(ctrl), _dptr(traj)
+        self._check(self._lib.mppi_fetch_result(self._h, C.byref(res)))
+        _store(self, res, ctrl, traj)
+
+    def set_profiling(self, on):
+        self._check(self._lib.mppi_set_profiling(self._h, 1 if on else 0))
+
+    def measure_fp32_peak(self):
+        v = C.c_double(0)
+        self._check(self._lib.mppi_measure_fp32_peak(self._h, C.byref(v)))
+        return v.value
+
+    def check_poses(self, poses):
+        """hit count per pose (x, y, psi) against the handle's circles and blocks
+        (block_collision_check, HybridAstar/src/hybrid_astar_utils.jl:193-201)."""
+        p = np.ascontiguousarray(np.asarray(poses, dtype=np.float64).reshape(-1, 3))
+        hit = np.zeros(p.shape[0], dtype=np.int32)
+        self._check(self._lib.mppi_check_poses(self._h, _dptr(p), p.shape[0], hit.ctypes.data_as(C.POINTER(C.c_int32))))
+        return hit
+
+    # -- sample sharding across GPUs -----------------------------------------
+    def step_local(self, noise=None):
+        """Rollout + local softmin partial on this handle's shard; returns capi.Partial."""
+        part = capi.Partial()
+        nptr = None
+        if noise is not None:
+            want = np.float64 if self._cfg.precision == capi.FP64 else np.float32
+            noise = np.ascontiguousarray(noise, dtype=want)
+            nptr = noise.ctypes.data_as(C.c_void_p)
+        self._check(self._lib.mppi_step_local(self._h, nptr, C.byref(part)))
+        return part
+
+    def step_combine(self, partials):
+        """Fold all ranks' partials (rank order) and run the nominal rollout; fills self.r."""
+        arr = (capi.Partial * len(partials))(*partials)
+        N, nx = self._cfg.N, self._cfg.n_x
+        ctrl = np.empty((N, 2), dtype=np.float64, order="F")
+        traj = np.empty((N + 1, nx), dtype=np.float64, order="F")
+        res = capi.Result()
+        res.Control, res.Traj = _dptr(ctrl), _dptr(traj)
+        self._check(self._lib.mppi_step_combine(self._h, arr, len(partials), C.byref(res)))
+        _store(self, res, ctrl, traj)
+
+    def comm_init(self, unique_id, rank, n_ranks):
+        """In-library NCCL: the softmin exchange becomes an all-gather inside the step graph."""
+        buf = (C.c_uint8 * capi.MPPI_COMM_ID_BYTES).from_buffer_copy(bytes(unique_id))
+        self._check(self._lib.mppi_comm_init(self._h, buf, rank, n_ranks))
+
+    def step_batched(self, x0s=None, Us=None):
+        """Config 5: B independent instances in one call. x0s (n_x, B), Us (N, m, B)."""
+        B, N = self._cfg.B, self._cfg.N
+        xp = up = None
+        if x0s is not None:
+            xa = np.ascontiguousarray(np.asarray(x0s, dtype=np.float64).T)
+            xp = _dptr(xa)
+        if Us is not None:
+            ua = np.ascontiguousarray(np.transpose(np.asarray(Us, dtype=np.float64), (2, 1, 0)))
+            up = _dptr(ua)
+        out = np.empty((B, 2, N))
+        costs = np.empty(B)
+        feas = np.empty(B, dtype=np.int32)
+        self._check(self._lib.mppi_step_batched(self._h, xp, up, _dptr(out), _dptr(costs),
+                                                feas.ctypes.data_as(C.POINTER(C.c_int32))))
+        return np.transpose(out, (2, 1, 0)), costs, feas
+
+
+def comm_unique_id():
+    """NCCL unique id (rank 0 creates it; ship it to the other ranks with any transport)."""
+    buf = (C.c_uint8 * capi.MPPI_COMM_ID_BYTES)()
+    lib = capi.load()
+    if lib.mppi_comm_unique_id(buf) != capi.MPPI_OK:
+        raise MPPIError(lib.mppi_last_error(None).decode())
+    return bytes(buf)
+
 
 def _fill(arr, vals):
     for i, v in enumerate(vals):

@@ -102,7 +102,7 @@ def test_reference_demo_dynamic_circles_with_cutoff(built, precision):
     mppi, ref = run_pair(args, kw, sc.CIRCLES, [], precision)
     check(mppi, ref, precision)
     # a state close to the first obstacle so that collisions and infeasible samples occur
-    args2 = (7, 2, 25.0, [42.0, 0.6, 0.1, 0.02, 0.05, 8.0, 0.01], [110, 0], 1500, sc.SIGMA, 20, 3.0, XL, XU, sc.CL, sc.CU)
+    args2 = (7, 2, 25.0, [40.0, -1.5, 0.0, 0.0, -0.05, 4.0, 0.0], [110, 0], 1500, sc.SIGMA, 20, 3.0, XL, XU, sc.CL, sc.CU)
     mppi, ref = run_pair(args2, kw, sc.CIRCLES, [], precision, Unom=warm_nominal(20))
     assert (ref["flags"] & capi.FLAG_COLLIDED).any() and (ref["flags"] & capi.FLAG_FEASIBLE).any()
     check(mppi, ref, precision)

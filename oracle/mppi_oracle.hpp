@@ -181,10 +181,13 @@ void get_rectangle_pts(const R* block, R* pts) {
 
 // SeparatingAxisTheorem, utils.jl:37-62.  true = a separating axis was found
 // among pts_base's edges.  n_base / n_other = number of columns.
+// gap (optional, guard-band bookkeeping only): best normalised separation over the
+// edges, >= 0 iff some edge separates; when requested every edge is scanned.
 template <class R>
 bool separating_axis_theorem(const R* pts_base, int n_base, const R* pts_other, int n_other,
-                             Margin<R>* mg) {
+                             R* gap = nullptr) {
   bool found = false;
+  R best = -std::numeric_limits<R>::infinity();
   for (int b = 0; b + 1 < n_base; ++b) {                                // :39
     const R bgx = pts_base[2 * b], bgy = pts_base[2 * b + 1];           // :41
     const R bvx = pts_base[2 * b + 2] - bgx, bvy = pts_base[2 * b + 3] - bgy;  // :42-44
@@ -199,26 +202,39 @@ bool separating_axis_theorem(const R* pts_base, int n_base, const R* pts_other, 
       const R d = (pts_other[2 * i] - bgx) * nx + (pts_other[2 * i + 1] - bgy) * ny;
       min_other = std::fmin(min_other, d); max_other = std::fmax(max_other, d);
     }
-    if (mg) { mg->see(max_other, min_base); mg->see(max_base, min_other); }
+    if (gap) {
+      const R sc = std::fmax(std::fmax(std::fabs(min_base), std::fabs(max_base)),
+                             std::fmax(std::fmax(std::fabs(min_other), std::fabs(max_other)), R(1)));
+      best = std::fmax(best, std::fmax(min_base - max_other, min_other - max_base) / sc);
+    }
     if ((max_other <= min_base) || (max_base <= min_other)) {           // :57
-      if (!mg) return true;                                             // :58
-      found = true;  // margin mode: keep scanning so every test is recorded
+      if (!gap) return true;                                            // :58
+      found = true;
     }
   }
+  if (gap) *gap = best;
   return found;                                                         // :61
 }
 
 // ConvexCollision, utils.jl:64-74.  true = collision-FREE; needs a separating
 // axis among pts1's edges AND among pts2's edges (stricter than textbook SAT).
+// Guard-band margin = how far the OUTCOME is from flipping.
 template <class R>
 bool convex_collision(const R* pts1, int n1, const R* pts2, int n2, Margin<R>* mg) {
   if (mg) {
-    const bool a = separating_axis_theorem(pts1, n1, pts2, n2, mg);
-    const bool b = separating_axis_theorem(pts2, n2, pts1, n1, mg);
+    R g1, g2;
+    const bool a = separating_axis_theorem(pts1, n1, pts2, n2, &g1);
+    const bool b = separating_axis_theorem(pts2, n2, pts1, n1, &g2);
+    R m;
+    if (a && b) m = std::fmin(g1, g2);                 // free: either direction failing flips it
+    else if (a) m = std::fabs(g2);                     // hit because of direction 2 only
+    else if (b) m = std::fabs(g1);
+    else m = std::fmax(std::fabs(g1), std::fabs(g2));  // both must flip
+    if (m < mg->v) mg->v = m;
     return a && b;
   }
-  if (separating_axis_theorem(pts1, n1, pts2, n2, mg)) {
-    return separating_axis_theorem(pts2, n2, pts1, n1, mg);
+  if (separating_axis_theorem(pts1, n1, pts2, n2)) {
+    return separating_axis_theorem(pts2, n2, pts1, n1);
   }
   return false;
 }

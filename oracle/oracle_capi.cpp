@@ -151,7 +151,7 @@ int oracle_rungekutta2(const mppi_config_t* cfg, const double* x, const double* 
 
 void oracle_get_rectangle_pts(const double* block, double* pts10) { get_rectangle_pts(block, pts10); }
 int oracle_sat(const double* base, int nb, const double* other, int no) {
-  return separating_axis_theorem<double>(base, nb, other, no, nullptr) ? 1 : 0;
+  return separating_axis_theorem<double>(base, nb, other, no) ? 1 : 0;
 }
 // ConvexCollision on point sets (2 x n col-major); 1 = collision-free
 int oracle_convex_collision(const double* p1, int n1, const double* p2, int n2) {

@@ -1,0 +1,260 @@
+"""GPU tests beyond supplied-noise parity: Philox mode (device noise replayed through the oracle),
+sample sharding (logical shards on one GPU), cut-off, DWA planner, batched instances, pose
+queries, plot export, error behaviour, and size-independent properties at BASELINE.json sizes."""
+import numpy as np
+import pytest
+
+import motionplanning_b200 as m
+import oracle_lib as orc
+from motionplanning_b200 import dist as mdist
+from motionplanning_b200 import scenarios as sc
+from test_gpu_parity import FP32_TOL, GUARD, check, warm_nominal
+
+capi = m.capi
+pytestmark = pytest.mark.gpu
+
+
+def make(args, kw, circles, blocks, Unom=None):
+    mppi = m.defineMPPI(*args, **kw)
+    if circles:
+        m.defineMPPIobs(mppi, circles)
+    if blocks:
+        m.defineMPPIblocks(mppi, blocks)
+    if Unom is not None:
+        m.defineMPPINominalControl(mppi, Unom)
+    return mppi
+
+
+@pytest.mark.parametrize("precision", [capi.FP64, capi.FP32])
+def test_philox_noise_replayed_through_oracle(built, precision):
+    """Config 2's mode at a size the oracle finishes quickly: in-kernel Philox noise is dumped
+    (mppi_get_noise) and replayed through the oracle's supplied-noise path."""
+    args, kw, circles, blocks = sc.config(1, K=8192)
+    kw = dict(kw, precision=precision, noise_mode=capi.NOISE_PHILOX)
+    U = warm_nominal(50)
+    mppi = make(args, kw, circles, blocks, U)
+    m.MPPIPlan(mppi)
+    eps = mppi.noise()
+    ref = orc.plan(orc.make_config(args, kw), circles, blocks, args[3], U, eps.astype(np.float64), capi.FP64,
+                   threads=8, want_margin=True)
+    check(mppi, ref, precision)
+    # distribution: eps ~ N(0, Sigma), Sigma a covariance (setup.jl:57)
+    flat = eps.reshape(-1, 2).astype(np.float64)
+    assert abs(flat.mean(0)).max() < 2e-3
+    np.testing.assert_allclose(np.cov(flat.T), sc.SIGMA, atol=1.5e-3)
+    # the device generator follows the oracle's Philox/Box-Muller statement up to libm rounding
+    host = orc.generate_noise(sc.SIGMA, sc.SEED, 0, 8192, 50, precision)
+    assert np.abs(host.astype(np.float64) - eps).max() < 5e-5
+
+
+def test_philox_determinism_iteration_and_seed(built):
+    args, kw, circles, blocks = sc.config(1, K=4096)
+    a = make(args, kw, circles, blocks)
+    b = make(args, kw, circles, blocks)
+    m.MPPIPlan(a), m.MPPIPlan(b)
+    assert np.array_equal(a.noise(), b.noise()) and np.array_equal(a.r.Control, b.r.Control)
+    e0 = a.noise()
+    m.MPPIPlan(a)
+    assert not np.array_equal(e0, a.noise())          # iteration counter advances the stream
+    host1 = orc.generate_noise(sc.SIGMA, sc.SEED, 1, 4096, 50, capi.FP32)
+    assert np.abs(host1 - a.noise()).max() < 5e-5
+    c = make(args, dict(kw, seed=12345), circles, blocks)
+    m.MPPIPlan(c)
+    assert not np.array_equal(e0, c.noise())
+
+
+@pytest.mark.parametrize("precision", [capi.FP64, capi.FP32])
+@pytest.mark.parametrize("G", [2, 4, 8])
+def test_logical_shards_match_unsharded(built, precision, G):
+    """G logical shards on one GPU (split-phase local / combine) == the unsharded step:
+    argmin / counts identical, U_new equal up to the rounding of the rescale."""
+    K = 8192
+    args, kw, circles, blocks = sc.config(1, K=K)
+    kw = dict(kw, precision=precision)
+    U = warm_nominal(50)
+    whole = make(args, kw, circles, blocks, U)
+    m.MPPIPlan(whole)
+    shards, partials = [], []
+    for g in range(G):
+        off, kl = mdist.shard_range(K, g, G)
+        s = make(args, dict(kw, k_offset=off, K_local=kl), circles, blocks, U)
+        partials.append(s.step_local())
+        shards.append(s)
+    # Philox counters use the global sample id: the shards drew exactly the unsharded noise
+    assert np.array_equal(np.concatenate([s.noise() for s in shards], axis=1), whole.noise())
+    assert np.array_equal(np.concatenate([s.p.costs for s in shards]), whole.p.costs)
+    for s in shards:
+        s.step_combine(partials)
+    tol = 1e-12 if precision == capi.FP64 else 2e-6
+    for s in shards:
+        assert s.r.argmin == whole.r.argmin and s.r.RolloutCount == whole.r.RolloutCount
+        assert s.r.FeasibleTrajCount == whole.r.FeasibleTrajCount
+        assert s.r.rho == whole.r.rho
+        assert s.r.eta == pytest.approx(whole.r.eta, rel=tol)
+        assert np.abs(s.r.Control - whole.r.Control).max() <= tol * max(np.abs(whole.r.Control).max(), 1)
+    # every rank folds the same partials in the same order: bitwise identical results
+    for s in shards[1:]:
+        assert np.array_equal(s.r.Control, shards[0].r.Control) and s.r.cost == shards[0].r.cost
+
+
+def test_partial_roundtrip_through_exchange_format(built):
+    args, kw, circles, blocks = sc.config(0)
+    s = make(args, kw, circles, blocks)
+    p = s.step_local()
+    q = mdist.array_to_partial(mdist.partial_to_array(p, 50), 50)
+    assert (q.rho, q.eta, q.argmin_global, q.rollouts, q.feasible) == (p.rho, p.eta, p.argmin_global, p.rollouts, p.feasible)
+    assert list(q.S[:100]) == list(p.S[:100])
+
+
+@pytest.mark.parametrize("precision", [capi.FP64, capi.FP32])
+def test_dwa_planner(built, precision):
+    """DWA mode (DynamicWindow/src/DWAUtils.jl:141-163, setup.jl:59-85): 31 x 41 constant-control grid,
+    no lambda term, obstacle penalty 10000*712.5, arg-min selection."""
+    CLd, CUd = [-0.3, -2.5], [0.3, 2.5]
+    g0, g1 = np.linspace(CLd[0], CUd[0], 31), np.linspace(CLd[1], CUd[1], 41)
+    cand = np.array([[a, b] for a in g0 for b in g1])
+    K = len(cand)
+    x0 = [38.0, -1.2, 0.0, 0.0, 0.0, 5.0, 0.0]
+    args = (7, 2, 25.0, x0, sc.GOAL, K, sc.SIGMA, 20, 3.0, sc.XL_DYN, sc.XU_DYN, CLd, CUd)
+    kw = dict(planner=capi.PLANNER_DWA, obstacle_penalty=10000.0 * 712.5, FeasibilityCount=K, precision=precision)
+    mppi = make(args, kw, sc.CIRCLES, [])
+    cf = np.asfortranarray(cand)
+    mppi._check(mppi._lib.mppi_set_candidates(mppi._h, cf.ctypes.data_as(m.mppi.C.POINTER(m.mppi.C.c_double)), K, 2))
+    m.MPPIPlan(mppi)
+    ref = orc.plan(orc.make_config(args, kw), sc.CIRCLES, [], x0, None, cand, capi.FP64, threads=8)
+    tol = 1e-9 if precision == capi.FP64 else FP32_TOL
+    rel = np.abs(mppi.p.costs - ref["costs"]) / np.abs(ref["costs"])
+    assert rel.max() <= tol
+    assert np.array_equal(mppi.p.flags, ref["flags"])
+    assert mppi.r.argmin == ref["argmin"]
+    assert np.array_equal(mppi.r.Control, ref["Control"])
+    assert np.abs(mppi.r.Traj - ref["Traj"]).max() <= (1e-9 if precision == capi.FP64 else 1e-3)
+    assert mppi.r.cost == pytest.approx(ref["cost"], rel=tol)
+
+
+def test_check_poses_matches_block_collision_check(built):
+    """mppi_check_poses == block_collision_check (hybrid_astar_utils.jl:193-201) per pose, incl. the
+    ConvexCollision quirk and headings outside [-pi, pi] (modπ)."""
+    cfg = capi.default_config()
+    rng = np.random.RandomState(11)
+    blocks = sc.PARKING_BLOCKS + sc.wall_blocks(16)
+    poses = np.stack([rng.uniform(-8, 100, 50000), rng.uniform(-10, 10, 50000), rng.uniform(-9, 9, 50000)], axis=1)
+    mppi = make(*sc.config(0)[:2], sc.CIRCLES, blocks)
+    hit = mppi.check_poses(poses)
+    ref, margin = orc.check_poses(cfg, sc.CIRCLES, blocks, poses)
+    ok = margin > 1e-9
+    assert ok.mean() > 0.999 and np.array_equal(hit[ok], ref[ok])
+    assert (ref > 0).any() and (ref == 0).any()
+    # the derived known-answer cases of CollisionDetection/main.jl:7-12 (free) and the quirk
+    one = make(*sc.config(0)[:2], [], [[0.0, -1.0, 0.0, 3.75, 1.0]])
+    assert one.check_poses([[5.5 - 1.5, 1.0, 0.0]])[0] == 0          # vehicle block [5.5, 1, 0, 1.5, 1]
+    unit = make(sc.config(0)[0], dict(sc.config(0)[1], veh_L=2.0, veh_W=2.0, veh_center_offset=0.0), [], [[0, 0, 0, 1, 1]])
+    assert unit.check_poses([[2.45, 0.0, np.pi / 4]])[0] == 1         # disjoint, yet ConvexCollision = false
+    assert unit.check_poses([[2.0, 0.0, 0.0]])[0] == 0                # touching counts as separated
+    assert unit.check_poses([[3.0, 0.0, np.pi / 4]])[0] == 0
+
+
+def test_batched_instances_match_single_instance_oracle(built):
+    """Config 5 shape at a small size: B instances with their own x0 / U_nom, Philox noise per
+    (instance, sample); every instance replayed through the oracle."""
+    B, K, N = 6, 512, 50
+    args, kw, circles, blocks = sc.config(4, K=K)
+    kw = dict(kw, B=B, precision=capi.FP64)
+    x0s = sc.jittered_x0(B)
+    Us = np.stack([warm_nominal(N, seed=b) for b in range(B)], axis=2)
+    mppi = make(args[:3] + (x0s,) + args[4:], kw, circles, blocks)
+    Uout, costs, feas = mppi.step_batched(x0s, Us)
+    dt = np.float64
+    eps = np.empty((B, N, K, 2), dtype=dt)
+    mppi._check(mppi._lib.mppi_get_noise(mppi._h, eps.ctypes.data_as(m.mppi.C.c_void_p)))
+    allc = mppi.p.costs.reshape(B, K)
+    for b in range(B):
+        ref = orc.plan(orc.make_config(args, dict(kw, B=1)), circles, blocks, x0s[:, b], Us[:, :, b], eps[b], capi.FP64, threads=8)
+        assert (np.abs(allc[b] - ref["costs"]) / np.abs(ref["costs"])).max() < 1e-9
+        assert np.abs(Uout[:, :, b] - ref["Control"]).max() < 1e-9
+        assert costs[b] == pytest.approx(ref["cost"], rel=1e-9) and bool(feas[b]) == ref["feasible"]
+    assert not np.array_equal(eps[0], eps[1])     # instances draw independent noise
+
+
+def test_sample_xy_export(built):
+    args, kw, circles, blocks = sc.config(0)
+    kw = dict(kw, precision=capi.FP64)
+    mppi = make(args, kw, circles, blocks)
+    m.MPPIPlan(mppi)
+    xy = mppi.p.sample_xy(stride=64)
+    assert xy.shape == (16, 51, 2)
+    eps = mppi.noise()
+    cfg = orc.make_config(args, kw)
+    for i in (0, 7, 15):
+        u = np.clip(eps[:, 64 * i, :], sc.CL, sc.CU)
+        ref = orc.rollout(cfg, circles, blocks, args[3], np.zeros((50, 2)), u)
+        assert np.abs(xy[i] - ref["Traj"][:, :2]).max() < 1e-4
+
+
+def test_error_behaviour(built):
+    """setup.jl:19-39 errors become MPPIError; state errors are reported, never crash."""
+    args, kw, circles, blocks = sc.config(0)
+    with pytest.raises(m.MPPIError, match="Length of XL"):
+        m.defineMPPI(*(args[:9] + ([0.0] * 4,) + args[10:]), **kw)
+    with pytest.raises(m.MPPIError, match="Controls"):
+        m.defineMPPI(*(args[:1] + (0,) + args[2:]), **kw)
+    mppi = make(args, dict(kw, noise_mode=capi.NOISE_SUPPLIED), circles, blocks)
+    with pytest.raises(m.MPPIError, match="needs the eps tensor"):
+        m.MPPIPlan(mppi)
+    with pytest.raises(m.MPPIError):
+        mppi.p.costs   # no step has run
+    with pytest.raises(m.MPPIError, match="must match number of states"):
+        m.ShiftInitialCondition(mppi, [0.0] * 7)
+    with pytest.raises(m.MPPIError):
+        m.defineMPPIobs(mppi, [[0.0, 0.0, 1.0]] * 65)
+    with pytest.raises(m.MPPIError, match="positive definite"):
+        m.defineMPPINominalControl(mppi, np.zeros((50, 2)), [[1.0, 2.0], [2.0, 1.0]])
+
+
+def test_closed_loop_device_resident_equals_host_loop(built):
+    """main.jl:59-62 (U_nom <- r.Control each iteration): the device-resident adopt path gives the
+    same controls as the host round trip."""
+    args, kw, circles, blocks = sc.config(1, K=4096)
+    a = make(args, kw, circles, blocks)
+    b = make(args, kw, circles, blocks)
+    m.MPPIPlan(a)
+    m.MPPIPlan(b)
+    for _ in range(4):
+        m.defineMPPINominalControl(a, a.r.Control)
+        m.MPPIPlan(a)
+        b.step_async(adopt=True)
+    b.sync()
+    b.fetch_result()
+    assert np.array_equal(a.r.Control, b.r.Control) and a.r.cost == b.r.cost
+    assert a.r.cost < 1e4 and a.r.Feasibility == "Feasible"
+
+
+@pytest.mark.parametrize("cfg_idx,K,N", [(1, 65536, 50), (2, 262144, 80), (3, 131072, 100)])
+def test_full_size_properties(built, cfg_idx, K, N):
+    """BASELINE.json sizes (cfg4 at the 8-GPU per-rank shard), checked through size-independent
+    properties: rho is the cost of the argmin sample and the minimum of all costs; eta equals the
+    softmin sum recomputed in float64 from the device costs; U_new equals the weighted mean recomputed
+    in float64 from the dumped noise; U_new stays inside [CL, CU]; counts match the flags."""
+    args, kw, circles, blocks = sc.config(cfg_idx, K=K, N=N)
+    U = warm_nominal(N)
+    mppi = make(args, kw, circles, blocks, U)
+    m.MPPIPlan(mppi)
+    costs, flags = mppi.p.costs, mppi.p.flags
+    assert mppi.r.rho == costs.min() and costs[mppi.r.argmin - 1] == mppi.r.rho
+    assert mppi.r.argmin - 1 == int(np.argmin(costs))
+    w = np.exp(-(costs - costs.min()) / sc.LAMBDA)
+    assert mppi.r.eta == pytest.approx(w.sum(), rel=2e-5)
+    assert mppi.r.FeasibleTrajCount == int((flags & capi.FLAG_FEASIBLE).sum())
+    assert mppi.r.RolloutCount == K + 1
+    eps = mppi.noise().astype(np.float64)
+    u = np.clip(U[:, None, :] + eps, sc.CL, sc.CU)
+    Uref = np.einsum("k,jkc->jc", w / w.sum(), u)
+    assert np.abs(mppi.r.Control - Uref).max() <= FP32_TOL * np.abs(Uref).max()
+    assert (mppi.r.Control >= np.array(sc.CL) - 1e-6).all() and (mppi.r.Control <= np.array(sc.CU) + 1e-6).all()
+    # spot parity: 256 samples spread over the shard replayed through the oracle
+    idx = np.linspace(0, K - 1, 256).astype(int)
+    sub = orc.plan(orc.make_config(args[:5] + (256,) + args[6:], dict(kw, FeasibilityCount=256)), circles, blocks,
+                   args[3], U, np.ascontiguousarray(eps[:, idx, :]), capi.FP64, threads=8, want_margin=True)
+    ok = sub["margins"] > GUARD
+    rel = np.abs(costs[idx] - sub["costs"]) / np.abs(sub["costs"])
+    assert rel[ok].max() <= FP32_TOL and np.array_equal(flags[idx][ok], sub["flags"][ok])

@@ -151,7 +151,8 @@ def test_check_poses_matches_block_collision_check(built):
     unit = make(sc.config(0)[0], dict(sc.config(0)[1], veh_L=2.0, veh_W=2.0, veh_center_offset=0.0), [], [[0, 0, 0, 1, 1]])
     assert unit.check_poses([[2.45, 0.0, np.pi / 4]])[0] == 1         # disjoint, yet ConvexCollision = false
     assert unit.check_poses([[2.0, 0.0, 0.0]])[0] == 0                # touching counts as separated
-    assert unit.check_poses([[3.0, 0.0, np.pi / 4]])[0] == 0
+    assert unit.check_poses([[3.0, 0.0, np.pi / 4]])[0] == 1                # still the quirk: 3/sqrt2 < 1 + sqrt2
+    assert unit.check_poses([[3.5, 0.0, np.pi / 4]])[0] == 0
 
 
 def test_batched_instances_match_single_instance_oracle(built):

@@ -128,7 +128,7 @@ def test_config3_parking_polygon_walls(built, precision):
     # a pose next to the right-hand wall block, so that SAT hits, misses and bound hits all occur
     x0 = [5.8, 0.5, np.pi / 2 + 0.15, 1.2, 0.1]
     args = args[:3] + (x0,) + args[4:]
-    mppi, ref = run_pair(args, kw, circles, blocks, precision, Unom=warm_nominal(80))
+    mppi, ref = run_pair(args, kw, circles, blocks, precision)
     f = ref["flags"]
     assert (f & capi.FLAG_COLLIDED).any() and (f & capi.FLAG_FEASIBLE).any() and (f & capi.FLAG_OOB).any()
     check(mppi, ref, precision)

@@ -1,0 +1,153 @@
+# MPPIB200.jl — `ccall` shim over libmppi_b200.so (include/mppi_b200.h).
+#
+# Drop-in for the MPPI step of congkaishen/MotionPlanning: replace
+#     include("src/MPPIUtils.jl")                       # OptimalControl/MPPI/main.jl:1
+# by
+#     include("/path/to/julia/MPPIB200.jl"); using .MPPIB200
+# and lines 29-30 and 59-63 of OptimalControl/MPPI/main.jl run unchanged:
+#     mppi = defineMPPI(numStates, numControls, lambda, X0, goal, SamplingNumber, Σ, N, T, XL, XU, CL, CU)
+#     defineMPPIobs!(mppi, [[50.0, 1, 2.5], [70.0, -1, 2.5], [90.0, 1, 2.5]])
+#     ShiftInitialCondition(mppi, states); defineMPPINominalControl!(mppi, NominalControls); MPPIPlan(mppi)
+#     mppi.r.Control, mppi.r.Feasibility, mppi.r.time, mppi.r.RolloutCount, mppi.r.Traj
+#
+# Julia is not installed in the build container, so this file is the syntax-reviewed twin of
+# motionplanning_b200/_capi.py + mppi.py (ctypes), which IS exercised by tests/ against the same
+# symbols.  The struct layouts below mirror include/mppi_b200.h field by field.
+module MPPIB200
+
+export defineMPPI, defineMPPIobs!, defineMPPIblocks!, defineMPPINominalControl!,
+       ShiftInitialCondition, MPPIPlan, MPPISearcher
+
+const LIB = get(ENV, "MPPI_B200_LIB", joinpath(@__DIR__, "..", "motionplanning_b200", "csrc", "libmppi_b200.so"))
+const MAX_NX = 8
+
+# mppi_config_t (include/mppi_b200.h) — isbits, same field order
+struct Config
+    struct_size::UInt32
+    model::Int32; n_x::Int32; m::Int32; K::Int32; N::Int32; B::Int32
+    precision::Int32; noise_mode::Int32; planner::Int32
+    feasibility_count::Int32; use_cuda_graph::Int32; device::Int32
+    k_offset::Int32; K_local::Int32; reserved0::Int32
+    seed::UInt64
+    T::Float64; lambda::Float64
+    Sigma::NTuple{4,Float64}
+    X0::NTuple{8,Float64}
+    goal::NTuple{2,Float64}
+    XL::NTuple{8,Float64}; XU::NTuple{8,Float64}
+    CL::NTuple{2,Float64}; CU::NTuple{2,Float64}
+    slack_penalty::Float64; obstacle_penalty::Float64; terminal_scale::Float64
+    la::Float64; lb::Float64; mass::Float64; Izz::Float64; g::Float64; mu::Float64
+    KFZF::Float64; KFZR::Float64; KFZX::Float64
+    tire::NTuple{6,Float64}
+    stage_w::NTuple{6,Float64}
+    veh_L::Float64; veh_W::Float64; veh_center_offset::Float64
+end
+
+# mppi_result_t
+mutable struct CResult
+    Control::Ptr{Float64}; Traj::Ptr{Float64}
+    cost::Float64
+    feasible::Int32; rollout_count::Int32; feasible_count::Int32; argmin_index::Int32
+    rho::Float64; eta::Float64; time_s::Float64
+    CResult() = new(C_NULL, C_NULL, 0.0, 0, 0, 0, 0, 0.0, 0.0, 0.0)
+end
+
+# the (s, p, r) shape of MPPISearcher (types.jl:46-50)
+mutable struct Setting                 # types.jl:10-31
+    numStates::Int; numControls::Int
+    X0::Vector{Float64}; XL::Vector{Float64}; XU::Vector{Float64}; CL::Vector{Float64}; CU::Vector{Float64}
+    dt::Float64; T::Float64; N::Int; goal::Vector{Float64}
+    obstacle_list::Vector{Vector{Float64}}
+    SamplingNumber::Int; FeasibilityCount::Int
+    NominalControl::Matrix{Float64}; Σ::Matrix{Float64}; lambda::Float64; SlackPenalty::Float64
+end
+mutable struct Result                  # types.jl:36-44
+    Traj::Matrix{Float64}; Control::Matrix{Float64}; Feasibility::Symbol
+    cost::Float64; time::Float64; FeasibleTrajCount::Int; RolloutCount::Int
+end
+mutable struct MPPISearcher
+    h::Ptr{Cvoid}
+    s::Setting
+    r::Result
+    cres::CResult
+end
+
+lasterr(h) = unsafe_string(ccall((:mppi_last_error, LIB), Cstring, (Ptr{Cvoid},), h))
+check(h, rc) = rc == 0 ? nothing : error(lasterr(h))     # same exception behaviour as setup.jl:19-39
+
+pad8(v) = ntuple(i -> i <= length(v) ? Float64(v[i]) : 0.0, 8)
+
+function defineMPPI(numStates, numControls, lambda, X0, goal, SamplingNumber, Σ, N, T, XL, XU, CL, CU;
+                    model = numStates == 7 ? 0 : 1, precision = 0, noise_mode = 1, seed = 0x5EED0001,
+                    device = 0, FeasibilityCount = 1300)
+    numControls > 0 || error("Controls ($numControls) must be > 0")                 # setup.jl:19-21
+    numStates > 0 || error("States ($numStates) must be > 0")                       # :22-24
+    length(X0) == numStates || error("Length of X0 ($(length(X0))) must match number of states ($numStates)")
+    length(XL) == numStates || error("Length of XL ($(length(XL))) must match number of states ($numStates)")
+    length(XU) == numStates || error("Length of XU ($(length(XU))) must match number of states ($numStates)")
+    length(CL) == numControls || error("Length of CL ($(length(CL))) must match number of controls ($numControls)")
+    length(CU) == numControls || error("Length of CU ($(length(CU))) must match number of controls ($numControls)")
+    d = Ref{Config}()
+    ccall((:mppi_config_default, LIB), Int32, (Ref{Config},), d)
+    c = d[]
+    cfg = Config(c.struct_size, model, numStates, numControls, SamplingNumber, N, 1, precision, noise_mode, 0,
+                 FeasibilityCount, 1, device, 0, 0, 0, seed, T, lambda,
+                 (Σ[1, 1], Σ[2, 1], Σ[1, 2], Σ[2, 2]), pad8(X0), (goal[1], goal[2]), pad8(XL), pad8(XU),
+                 (CL[1], CL[2]), (CU[1], CU[2]), c.slack_penalty, c.obstacle_penalty, c.terminal_scale,
+                 c.la, c.lb, c.mass, c.Izz, c.g, c.mu, c.KFZF, c.KFZR, c.KFZX, c.tire, c.stage_w,
+                 c.veh_L, c.veh_W, c.veh_center_offset)
+    hp = Ref{Ptr{Cvoid}}(C_NULL)
+    rc = ccall((:mppi_create, LIB), Int32, (Ref{Config}, Ref{Ptr{Cvoid}}), cfg, hp)
+    rc == 0 || error(lasterr(C_NULL))
+    s = Setting(numStates, numControls, Float64.(X0), Float64.(XL), Float64.(XU), Float64.(CL), Float64.(CU),
+                T / N, T, N, Float64.(goal), Vector{Vector{Float64}}(), SamplingNumber, FeasibilityCount,
+                zeros(N, numControls), Float64.(Σ), lambda, 1e5)                      # setup.jl:53-55
+    r = Result(zeros(N + 1, numStates), zeros(N, numControls), :InFeasible, 1e6, 0.0, 0, 0)
+    mppi = MPPISearcher(hp[], s, r, CResult())
+    finalizer(m -> ccall((:mppi_destroy, LIB), Int32, (Ptr{Cvoid},), m.h), mppi)
+    return mppi
+end
+
+function defineMPPIobs!(mppi::MPPISearcher, obstacle_list)                           # setup.jl:61-64
+    mppi.s.obstacle_list = obstacle_list
+    xyr = Float64[o[i] for i in 1:3, o in obstacle_list]                              # 3 x M_c col-major
+    check(mppi.h, ccall((:mppi_set_circles, LIB), Int32, (Ptr{Cvoid}, Ptr{Float64}, Int32), mppi.h, xyr, size(xyr, 2)))
+end
+
+# polygon walls [cx, cy, ψ, half_len, half_wid] (CollisionDetection/src/utils.jl:14-25)
+function defineMPPIblocks!(mppi::MPPISearcher, block_list)
+    b = Float64[o[i] for i in 1:5, o in block_list]
+    check(mppi.h, ccall((:mppi_set_blocks, LIB), Int32, (Ptr{Cvoid}, Ptr{Float64}, Int32), mppi.h, b, size(b, 2)))
+end
+
+function defineMPPINominalControl!(mppi::MPPISearcher, U::Matrix{Float64})            # setup.jl:70-73
+    mppi.s.NominalControl = U
+    check(mppi.h, ccall((:mppi_set_nominal, LIB), Int32, (Ptr{Cvoid}, Ptr{Float64}, Int32, Int32),
+                        mppi.h, U, size(U, 1), size(U, 2)))                           # Matrix{Float64} is already N x m col-major
+end
+function defineMPPINominalControl!(mppi::MPPISearcher, U::Matrix{Float64}, Σ)          # setup.jl:74-78
+    defineMPPINominalControl!(mppi, U)
+    mppi.s.Σ = Float64.(Σ)
+    check(mppi.h, ccall((:mppi_set_sigma_lambda, LIB), Int32, (Ptr{Cvoid}, Ptr{Float64}, Float64),
+                        mppi.h, mppi.s.Σ, mppi.s.lambda))
+end
+
+function ShiftInitialCondition(mppi::MPPISearcher, X0)                                 # MPPIUtils.jl:24-27
+    mppi.s.X0 = Float64.(X0)
+    check(mppi.h, ccall((:mppi_set_x0, LIB), Int32, (Ptr{Cvoid}, Ptr{Float64}, Int32), mppi.h, mppi.s.X0, length(X0)))
+end
+
+function MPPIPlan(mppi::MPPISearcher; noise = nothing)                                 # MPPIUtils.jl:169-203
+    r, c = mppi.r, mppi.cres
+    GC.@preserve r begin
+        c.Control = pointer(r.Control); c.Traj = pointer(r.Traj)                       # filled in place, zero-copy
+        np = noise === nothing ? C_NULL : pointer(noise)                               # Array{T,3}(m, K, N)
+        check(mppi.h, ccall((:mppi_step, LIB), Int32, (Ptr{Cvoid}, Ptr{Cvoid}, Ref{CResult}), mppi.h, np, c))
+    end
+    r.Feasibility = c.feasible != 0 ? :Feasible : :InFeasible                          # :195
+    r.cost = c.cost; r.RolloutCount = c.rollout_count; r.FeasibleTrajCount = c.feasible_count
+    r.time = c.time_s                                                                  # :199-200
+    return nothing
+end
+
+end # module

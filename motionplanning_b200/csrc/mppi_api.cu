@@ -76,6 +76,8 @@ static int validate(const mppi_config_t* c, std::string* why) {
   if (c->k_offset < 0 || c->k_offset + Kl > c->K) { *why = "sample shard [k_offset, k_offset+K_local) must lie inside [0, K)"; return MPPI_EINVAL; }
   const double det = c->Sigma[0] * c->Sigma[3] - c->Sigma[1] * c->Sigma[2];
   if (!(c->Sigma[0] > 0) || !(det > 0)) { *why = "Sigma must be positive definite"; return MPPI_EINVAL; }
+  for (int i = 0; i < c->n_x; ++i)
+    if (c->XL[i] > c->XU[i]) { snprintf(buf, sizeof buf, "XL[%d] (%g) must be <= XU[%d] (%g)", i, c->XL[i], i, c->XU[i]); *why = buf; return MPPI_EINVAL; }
   if (c->planner == MPPI_PLANNER_DWA && (Kl != c->K || c->B != 1)) { *why = "DWA planner runs unsharded, B = 1"; return MPPI_EINVAL; }
   return MPPI_OK;
 }
@@ -87,9 +89,9 @@ int32_t mppi_destroy(mppi_handle_t* h) {
   drop_graphs(h);
   if (h->comm && nccl_api().CommDestroy) nccl_api().CommDestroy(h->comm);
   void* dev[] = {h->d_in, h->d_eps, h->d_costs, h->d_flags, h->d_scratch, h->d_scratch_tmpl, h->d_iter, h->d_Spart,
-                 h->d_eta_part, h->d_partial, h->d_gathered, h->d_res, h->d_traj, h->d_cand};
+                 h->d_eta_part, h->d_partial, h->d_gathered, h->d_res, h->d_cand};
   for (void* p : dev) if (p) cudaFree(p);
-  void* host[] = {h->h_in, h->h_res, h->h_traj, h->h_partial, h->h_gathered};
+  void* host[] = {h->h_in, h->h_res, h->h_partial, h->h_gathered};
   for (void* p : host) if (p) cudaFreeHost(p);
   for (auto& e : h->ev) if (e) cudaEventDestroy(e);
   if (h->stream) cudaStreamDestroy(h->stream);
@@ -121,12 +123,13 @@ static int create_impl(mppi_handle* h) {
   MPPI_CUDA(h, cudaMalloc(&h->d_eta_part, B * h->ksplit * rs));
   MPPI_CUDA(h, cudaMalloc(&h->d_partial, B * h->plen * sizeof(double)));
   MPPI_CUDA(h, cudaMalloc(&h->d_gathered, 8 * B * h->plen * sizeof(double)));
-  MPPI_CUDA(h, cudaMalloc(&h->d_res, B * (RES_SCALARS + 2 * N) * sizeof(double)));
-  MPPI_CUDA(h, cudaMalloc(&h->d_traj, B * (N + 1) * c.n_x * sizeof(double)));
+  // results: [B][RES_SCALARS] scalars | [B][2N] U_new | [B][(N+1)*n_x] nominal trajectory, one D2H copy
+  MPPI_CUDA(h, cudaMalloc(&h->d_res, B * (RES_SCALARS + 2 * N + (N + 1) * c.n_x) * sizeof(double)));
+  h->d_traj = h->d_res + B * (RES_SCALARS + 2 * N);
   if (c.planner == MPPI_PLANNER_DWA) MPPI_CUDA(h, cudaMalloc(&h->d_cand, K * 2 * sizeof(double)));
   MPPI_CUDA(h, cudaMallocHost(&h->h_in, B * (MPPI_MAX_NX + 2 * N) * sizeof(double)));
-  MPPI_CUDA(h, cudaMallocHost(&h->h_res, B * (RES_SCALARS + 2 * N) * sizeof(double)));
-  MPPI_CUDA(h, cudaMallocHost(&h->h_traj, (N + 1) * c.n_x * sizeof(double)));
+  MPPI_CUDA(h, cudaMallocHost(&h->h_res, (B * (RES_SCALARS + 2 * N) + (N + 1) * c.n_x) * sizeof(double)));
+  h->h_traj = h->h_res + B * (RES_SCALARS + 2 * N);
   MPPI_CUDA(h, cudaMallocHost(&h->h_partial, B * h->plen * sizeof(double)));
   MPPI_CUDA(h, cudaMallocHost(&h->h_gathered, 8 * B * h->plen * sizeof(double)));
   // inputs: X0 from the config for every instance, zero nominal (setup.jl:55)
@@ -161,7 +164,7 @@ int32_t mppi_create(const mppi_config_t* cfg, mppi_handle_t** out) {
 }
 
 static int quiesce(mppi_handle* h) {   // pinned inputs are about to change: no step may be in flight
-  MPPI_CUDA(h, cudaStreamSynchronize(h->stream));
+  if (h->in_flight) { MPPI_CUDA(h, cudaStreamSynchronize(h->stream)); h->in_flight = false; }
   return MPPI_OK;
 }
 
@@ -176,7 +179,7 @@ int32_t mppi_set_x0(mppi_handle_t* h, const double* x0, int32_t n) {
   int rc = quiesce(h); if (rc) return rc;
   for (int b = 0; b < h->cfg.B; ++b)
     for (int i = 0; i < n; ++i) h->h_in[size_t(b) * MPPI_MAX_NX + i] = x0[size_t(b) * n + i];
-  MPPI_CUDA(h, cudaMemcpyAsync(h->d_in, h->h_in, size_t(h->cfg.B) * MPPI_MAX_NX * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  h->x0_dirty = true;   // uploaded by the next step's graph (one H2D node for x0 + U_nom)
   return MPPI_OK;
 }
 
@@ -187,7 +190,7 @@ int32_t mppi_set_nominal(mppi_handle_t* h, const double* U, int32_t N, int32_t m
   int rc = quiesce(h); if (rc) return rc;
   const size_t B = h->cfg.B, off = B * MPPI_MAX_NX, n = B * 2 * N;
   memcpy(h->h_in + off, U, n * sizeof(double));
-  MPPI_CUDA(h, cudaMemcpyAsync(h->d_in + off, h->h_in + off, n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  h->u_dirty = true;
   return MPPI_OK;
 }
 

@@ -40,7 +40,7 @@ struct StaticParams {
   R la, lb, inv_mass_num /*unused*/, mass, Izz, mu, KFZX;
   R FZF0, FZR0;               // KFZF*g, KFZR*g
   R tireB, tireC, tireD, tireE;  // B = tire[0]/mu, C = tire[1], D = tire[2], E = tire[3]
-  R Lwb;                      // la + lb
+  R Lwb, inv_Lwb;             // la + lb
   R w[6];                     // stage cost weights v2, r2, ax2, sr2, sa2, y2
   R veh_off, veh_hl, veh_hw;  // rectangle: centre offset, half length, half width
   R circ[MPPI_MAX_CIRCLES][3];  // x, y, r^2
@@ -94,6 +94,8 @@ template <> struct Math<float> {
   static __device__ __forceinline__ void sincos(float x, float* s, float* c) { __sincosf(x, s, c); }
   static __device__ __forceinline__ float tan(float x) { return __tanf(x); }
   static __device__ __forceinline__ float div(float a, float b) { return __fdividef(a, b); }
+  // division by a parameter whose reciprocal was taken on the host
+  static __device__ __forceinline__ float over(float a, float, float inv_b) { return a * inv_b; }
   static __device__ __forceinline__ float exp(float x) { return __expf(x); }
   static __device__ __forceinline__ float sin(float x) { return __sinf(x); }
   static __device__ __forceinline__ float fabs(float x) { return fabsf(x); }
@@ -125,6 +127,7 @@ template <> struct Math<double> {
   static __device__ __forceinline__ void sincos(double x, double* s, double* c) { ::sincos(x, s, c); }
   static __device__ __forceinline__ double tan(double x) { return ::tan(x); }
   static __device__ __forceinline__ double div(double a, double b) { return a / b; }
+  static __device__ __forceinline__ double over(double a, double b, double) { return a / b; }
   static __device__ __forceinline__ double exp(double x) { return ::exp(x); }
   static __device__ __forceinline__ double sin(double x) { return ::sin(x); }
   static __device__ __forceinline__ double atan(double x) { return ::atan(x); }

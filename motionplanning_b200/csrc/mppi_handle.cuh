@@ -65,12 +65,12 @@ struct mppi_handle {
   double* d_partial = nullptr;   // [B][plen]
   double* d_gathered = nullptr;  // [G][B][plen]
   double* d_res = nullptr;       // [B][RES_SCALARS] then [B][2N]
-  double* d_traj = nullptr;      // [B][(N+1)*n_x]
+  double* d_traj = nullptr;      // [B][(N+1)*n_x], inside the d_res allocation
   double* d_cand = nullptr;      // DWA candidates K x 2 col-major
   // pinned host mirrors
   double* h_in = nullptr;
   double* h_res = nullptr;
-  double* h_traj = nullptr;
+  double* h_traj = nullptr;      // inside the h_res allocation
   double* h_partial = nullptr;
   double* h_gathered = nullptr;
   // static params
@@ -87,6 +87,8 @@ struct mppi_handle {
   float us[4] = {0, 0, 0, 0};
   int64_t launches = 0;
   bool stepped = false;
+  bool x0_dirty = false, u_dirty = false;   // pinned x0 / U_nom changed since the last upload
+  bool in_flight = false;   // work enqueued on the stream and not yet synchronised
   bool have_candidates = false;
 };
 
@@ -126,12 +128,15 @@ void build_params(const mppi_handle* h, StaticParams<R>* p) {
   p->la = R(c.la); p->lb = R(c.lb); p->mass = R(c.mass); p->Izz = R(c.Izz); p->mu = R(c.mu); p->KFZX = R(c.KFZX);
   p->FZF0 = R(c.KFZF) * R(c.g); p->FZR0 = R(c.KFZR) * R(c.g);
   p->tireB = R(c.tire[0]) / R(c.mu); p->tireC = R(c.tire[1]); p->tireD = R(c.tire[2]); p->tireE = R(c.tire[3]);
-  p->Lwb = R(c.la) + R(c.lb);
+  p->Lwb = R(c.la) + R(c.lb); p->inv_Lwb = R(1) / p->Lwb;
   for (int i = 0; i < 6; ++i) p->w[i] = R(c.stage_w[i]);
   p->veh_off = R(c.veh_center_offset); p->veh_hl = R(c.veh_L) / R(2); p->veh_hw = R(c.veh_W) / R(2);
   for (int o = 0; o < p->n_circles; ++o) {
     const R r = R(h->circles[3 * o + 2]);
     p->circ[o][0] = R(h->circles[3 * o]); p->circ[o][1] = R(h->circles[3 * o + 1]); p->circ[o][2] = r * r;
+  }
+  for (int o = p->n_circles; o < ((p->n_circles + 3) & ~3) && o < MPPI_MAX_CIRCLES; ++o) {
+    p->circ[o][0] = R(0); p->circ[o][1] = R(0); p->circ[o][2] = R(-1);   // padding: d^2 <= -1 never holds
   }
   for (int b = 0; b < p->n_blocks; ++b) {
     const double* bl = &h->blocks[5 * b];

@@ -19,6 +19,9 @@ constexpr int CUTOFF_BS = 1024;
 template <class R> struct Vec2;
 template <> struct Vec2<float> { using type = float2; };
 template <> struct Vec2<double> { using type = double2; };
+template <class R> struct Vec4;
+template <> struct Vec4<float> { using type = float4; };
+template <> struct Vec4<double> { using type = double4; };
 
 __device__ __forceinline__ unsigned long long shfl_xor_u64(unsigned long long v, int m) {
   return __shfl_xor_sync(0xffffffffu, v, m);
@@ -91,43 +94,59 @@ rollout_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) 
     R stage = R(0);
     R2* eps = reinterpret_cast<R2*>(buf.eps) + size_t(b) * N * p.K_local + k;
     R cu0 = R(0), cu1 = R(0);
-    uint4 rnd = make_uint4(0, 0, 0, 0);
     unsigned int iter = 0;
     if (SRC == SRC_PHILOX) iter = *buf.iter;
     if (SRC == SRC_DWA) {
       cu0 = R(buf.cand[k]);
       cu1 = R(buf.cand[size_t(p.K_local) + k]);
     }
-    R2 e_next = R2{R(0), R(0)};
-    if (SRC == SRC_SUPPLIED) e_next = eps[0];
-    for (int j = 0; j < N; ++j) {
+    // one horizon step: PushInBounds, control cost, stage cost, Heun step, tests of x_{j+1}
+    auto advance = [&](int j, R2 e) {
       R u0, u1;
       if (SRC == SRC_DWA) {
         u0 = cu0; u1 = cu1;
       } else {
-        R2 e;
-        if (SRC == SRC_SUPPLIED) {
-          e = e_next;
-          if (j + 1 < N) e_next = eps[size_t(j + 1) * p.K_local];   // prefetch next step's noise
-        } else {
-          if ((j & 1) == 0) rnd = philox4x32_10(make_uint4(uint32_t(p.k_offset + k), uint32_t(j >> 1), iter, uint32_t(b)),
-                                                p.seed_lo, p.seed_hi);
-          float z0, z1;
-          box_muller((j & 1) ? rnd.z : rnd.x, (j & 1) ? rnd.w : rnd.y, &z0, &z1);
-          e.x = p.L00 * R(z0);                       // eps = chol(Sigma) * z   (MPPIUtils.jl:6)
-          e.y = p.L10 * R(z0) + p.L11 * R(z1);
-          eps[size_t(j) * p.K_local] = e;            // kept for the update kernel / oracle replay
-        }
-        const R n0 = sU[4 * j + 0], n1 = sU[4 * j + 1];
-        u0 = Math<R>::fmin(Math<R>::fmax(n0 + e.x, p.CL[0]), p.CU[0]);   // PushInBounds (:13-20)
-        u1 = Math<R>::fmin(Math<R>::fmax(n1 + e.y, p.CL[1]), p.CU[1]);
-        stage += sU[4 * j + 2] * (u0 - n0) + sU[4 * j + 3] * (u1 - n1);  // lambda*U_nom'*inv(Sigma)*(u-U_nom) (:45)
+        const typename Vec4<R>::type nu = reinterpret_cast<const typename Vec4<R>::type*>(sU)[j];   // u0, u1, g0, g1
+        u0 = Math<R>::fmin(Math<R>::fmax(nu.x + e.x, p.CL[0]), p.CU[0]);   // PushInBounds (:13-20)
+        u1 = Math<R>::fmin(Math<R>::fmax(nu.y + e.y, p.CL[1]), p.CU[1]);
+        stage += nu.z * (u0 - nu.x) + nu.w * (u1 - nu.y);                  // lambda*U_nom'*inv(Sigma)*(u-U_nom) (:45)
       }
       stage += veh.stage_cost(p, u0, u1);            // VehicleDynamics cost at the pre-step state
       veh.step(p, u0, u1);                           // Rungekutta2 (:76-90)
       hits += circle_hits(p, veh.s[0], veh.s[1]);    // x_{j+1}: ObstacleEvaluation
       hits += block_hits(p, veh.s[0], veh.s[1], veh.sn, veh.cs);
       viol += bound_violation<R, Model::NX>(p, veh.s);   // BoundEvaluation
+    };
+    if (SRC == SRC_PHILOX) {
+      // one Philox4x32-10 call feeds two horizon steps; eps = chol(Sigma) * z (MPPIUtils.jl:6)
+      // is kept for the update kernel / oracle replay
+      const uint32_t gk = uint32_t(p.k_offset + k);
+      for (int j = 0; j < N; j += 2) {
+        const uint4 rnd = philox4x32_10(make_uint4(gk, uint32_t(j >> 1), iter, uint32_t(b)), p.seed_lo, p.seed_hi);
+        float z0, z1;
+        box_muller(rnd.x, rnd.y, &z0, &z1);
+        R2 e;
+        e.x = p.L00 * R(z0);
+        e.y = p.L10 * R(z0) + p.L11 * R(z1);
+        eps[size_t(j) * p.K_local] = e;
+        advance(j, e);
+        if (j + 1 < N) {
+          box_muller(rnd.z, rnd.w, &z0, &z1);
+          e.x = p.L00 * R(z0);
+          e.y = p.L10 * R(z0) + p.L11 * R(z1);
+          eps[size_t(j + 1) * p.K_local] = e;
+          advance(j + 1, e);
+        }
+      }
+    } else if (SRC == SRC_SUPPLIED) {
+      R2 e_next = eps[0];
+      for (int j = 0; j < N; ++j) {
+        const R2 e = e_next;
+        if (j + 1 < N) e_next = eps[size_t(j + 1) * p.K_local];   // prefetch next step's noise
+        advance(j, e);
+      }
+    } else {
+      for (int j = 0; j < N; ++j) advance(j, R2{R(0), R(0)});
     }
     stage += veh.stage_cost(p, R(0), R(0));          // terminal slot: VehicleDynamics(x_N, [0,0]) (:49,:53)
     const R gx = veh.s[0] - p.goal[0], gy = veh.s[1] - p.goal[1];

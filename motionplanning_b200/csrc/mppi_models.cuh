@@ -25,7 +25,7 @@ struct Kin5 {
 #pragma unroll
     for (int i = 0; i < NX; ++i) s[i] = R(x0[i]);
     Math<R>::sincos(s[IPSI], &sn, &cs);
-    tn = Math<R>::div(Math<R>::tan(s[4]), p.Lwb);
+    tn = Math<R>::over(Math<R>::tan(s[4]), p.Lwb, p.inv_Lwb);
   }
   // stage cost of VehicleDynamics at (state, u): SURVEY 8(a) a6 = dynamic cost with v = r = 0
   __device__ __forceinline__ R stage_cost(const StaticParams<R>& p, R sr, R ax) const {
@@ -40,7 +40,7 @@ struct Kin5 {
     const R sat = s[4] + sr * p.dt;
     R st, ct;
     Math<R>::sincos(psit, &st, &ct);
-    const R tnt = Math<R>::div(Math<R>::tan(sat), p.Lwb);
+    const R tnt = Math<R>::over(Math<R>::tan(sat), p.Lwb, p.inv_Lwb);
     const R k2x = uxt * ct, k2y = uxt * st, k2p = uxt * tnt;
     // corrector x + dt*(k1+k2)/2
     s[0] = s[0] + p.half_dt * (k1x + k2x);
@@ -123,12 +123,31 @@ struct Dyn7 {
 // Obstacles.  Returns the number of obstacles hit by the pose (each hit costs
 // obs_pen and clears the constraint flag: MPPIUtils.jl:125-127).
 // ---------------------------------------------------------------------------
+// The circle table is padded on the host to a multiple of 4 with never-hit entries
+// (r^2 = -1), so the common small counts run as fully unrolled groups whose table
+// entries are immediate constant-bank operands (no per-circle load / loop overhead).
+template <class R, int Q>
+__device__ __forceinline__ int circle_hits_quads(const StaticParams<R>& p, R x, R y) {
+  int hits = 0;
+#pragma unroll
+  for (int o = 0; o < 4 * Q; ++o) {
+    const R dx = x - p.circ[o][0], dy = y - p.circ[o][1];
+    hits += (dx * dx + dy * dy <= p.circ[o][2]) ? 1 : 0;   // sum((s-o).^2) <= r^2
+  }
+  return hits;
+}
 template <class R>
 __device__ __forceinline__ int circle_hits(const StaticParams<R>& p, R x, R y) {
+  switch ((p.n_circles + 3) >> 2) {   // warp-uniform
+    case 0: return 0;
+    case 1: return circle_hits_quads<R, 1>(p, x, y);
+    case 2: return circle_hits_quads<R, 2>(p, x, y);
+    default: break;
+  }
   int hits = 0;
   for (int o = 0; o < p.n_circles; ++o) {
     const R dx = x - p.circ[o][0], dy = y - p.circ[o][1];
-    hits += (dx * dx + dy * dy <= p.circ[o][2]) ? 1 : 0;   // sum((s-o).^2) <= r^2
+    hits += (dx * dx + dy * dy <= p.circ[o][2]) ? 1 : 0;
   }
   return hits;
 }
@@ -161,14 +180,14 @@ __device__ __forceinline__ int block_hits(const StaticParams<R>& p, R x, R y, R 
 
 // BoundEvaluation (MPPIUtils.jl:135-151): sum of violations |x - XL|, |x - XU|
 // (strict inequalities; the slack factor is applied once at the end).
+// XL <= XU, so at most one side is violated: max(XL - s, s - XU, 0) equals the sum of
+// the two one-sided terms exactly (the other term is +0).
 template <class R, int NX>
 __device__ __forceinline__ R bound_violation(const StaticParams<R>& p, const R* s) {
   R acc = R(0);
 #pragma unroll
-  for (int i = 0; i < NX; ++i) {
-    acc += Math<R>::fmax(p.XL[i] - s[i], R(0));
-    acc += Math<R>::fmax(s[i] - p.XU[i], R(0));
-  }
+  for (int i = 0; i < NX; ++i)
+    acc += Math<R>::fmax(Math<R>::fmax(p.XL[i] - s[i], s[i] - p.XU[i]), R(0));
   return acc;
 }
 
@@ -192,7 +211,9 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1
 __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float* z0, float* z1) {
   const float u = __uint2float_rn(a) * 2.3283064365386963e-10f + 1.1641532182693481e-10f;
   const float th = __uint2float_rn(b) * 1.4629180792671596e-09f + (-3.1415926535897931f + 7.3145903963357981e-10f);
-  const float s = sqrtf(-1.3862943611198906f * __log2f(u));   // sqrt(-2 ln u) = sqrt(-2 ln2 * log2 u)
+  float lg, s;   // sqrt(-2 ln u) = sqrt(-2 ln2 * log2 u); u >= 2^-33 so the .ftz forms are exact-domain
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(u));
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(s) : "f"(-1.3862943611198906f * lg));
   float sn, cs;
   __sincosf(th, &sn, &cs);
   *z0 = s * sn;

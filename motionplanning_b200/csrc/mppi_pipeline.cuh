@@ -17,7 +17,9 @@ enum {
   V_NCCL = 64,       // in-library all-gather of the partials
   V_COMBINE = 128,   // finalize<PH_COMBINE> (+ nominal rollout)
   V_D2H_RES = 256,
-  V_FUSED_FINAL = 512  // finalize<PH_PARTIAL|PH_COMBINE> in one kernel (single rank)
+  V_FUSED_FINAL = 512,  // finalize<PH_PARTIAL|PH_COMBINE> in one kernel (single rank)
+  V_H2D_X0 = 1024,      // pinned x0 only -> device
+  V_H2D_U = 2048        // pinned U_nom only -> device
 };
 
 template <class R> const StaticParams<R>& params_of(const mppi_handle* h);
@@ -37,6 +39,10 @@ int enqueue_variant(mppi_handle* h, int v, bool timed) {
 
   if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[0], s));
   if (v & V_H2D_IN) MPPI_CUDA(h, cudaMemcpyAsync(h->d_in, h->h_in, in_bytes, cudaMemcpyHostToDevice, s));
+  if (v & V_H2D_X0) MPPI_CUDA(h, cudaMemcpyAsync(h->d_in, h->h_in, size_t(B) * MPPI_MAX_NX * sizeof(double), cudaMemcpyHostToDevice, s));
+  if (v & V_H2D_U)
+    MPPI_CUDA(h, cudaMemcpyAsync(h->d_in + size_t(B) * MPPI_MAX_NX, h->h_in + size_t(B) * MPPI_MAX_NX,
+                                 size_t(B) * 2 * N * sizeof(double), cudaMemcpyHostToDevice, s));
   if (v & V_ADOPT)
     MPPI_CUDA(h, cudaMemcpyAsync(h->d_in + size_t(B) * MPPI_MAX_NX, h->d_res + size_t(B) * RES_SCALARS,
                                  size_t(B) * 2 * N * sizeof(double), cudaMemcpyDeviceToDevice, s));
@@ -57,7 +63,7 @@ int enqueue_variant(mppi_handle* h, int v, bool timed) {
     }
     if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[2], s));
   }
-  const size_t smemF = size_t(N) * 6 * sizeof(R);
+  const size_t smemF = (size_t(N) * 6 + size_t(N + 1) * (Model::NX + 2 + 3)) * sizeof(R);
   if (v & V_FUSED_FINAL) {
     finalize_kernel<R, Model, SRC, PH_PARTIAL | PH_COMBINE><<<B, FINAL_BS, smemF, s>>>(p, buf);
     h->launches++;
@@ -82,9 +88,8 @@ int enqueue_variant(mppi_handle* h, int v, bool timed) {
   }
   if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[3], s));
   if (v & V_D2H_RES) {
-    MPPI_CUDA(h, cudaMemcpyAsync(h->h_res, h->d_res, res_bytes, cudaMemcpyDeviceToHost, s));
-    if (B == 1)
-      MPPI_CUDA(h, cudaMemcpyAsync(h->h_traj, h->d_traj, size_t(N + 1) * nx * sizeof(double), cudaMemcpyDeviceToHost, s));
+    const size_t traj_bytes = (B == 1) ? size_t(N + 1) * nx * sizeof(double) : 0;   // contiguous with the scalars
+    MPPI_CUDA(h, cudaMemcpyAsync(h->h_res, h->d_res, res_bytes + traj_bytes, cudaMemcpyDeviceToHost, s));
   }
   if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[4], s));
   MPPI_CUDA(h, cudaGetLastError());
@@ -125,12 +130,19 @@ inline int kernels_in(const mppi_handle* h, int v) {
   return n;
 }
 
+// pending host-side input changes -> the H2D node(s) the next step must carry
+inline int take_dirty(mppi_handle* h) {
+  const int v = (h->x0_dirty && h->u_dirty) ? V_H2D_IN : (h->x0_dirty ? V_H2D_X0 : (h->u_dirty ? V_H2D_U : 0));
+  h->x0_dirty = h->u_dirty = false;
+  return v;
+}
+
 // run a variant: graph replay (captured on first use) or eager when profiling / graphs are off
 inline int run_variant(mppi_handle* h, int v) {
   const bool use_graph = h->cfg.use_cuda_graph && !h->profiling;
   if (!use_graph) {
-    int rc = enqueue(h, v, h->profiling);
-    return rc;
+    h->in_flight = true;
+    return enqueue(h, v, h->profiling);
   }
   auto it = h->graphs.find(v);
   if (it == h->graphs.end()) {
@@ -154,6 +166,7 @@ inline int run_variant(mppi_handle* h, int v) {
   MPPI_CUDA(h, cudaGraphLaunch(it->second, h->stream));
   MPPI_CUDA(h, cudaEventRecord(h->ev[4], h->stream));
   h->launches += kernels_in(h, v);
+  h->in_flight = true;
   return MPPI_OK;
 }
 

@@ -158,17 +158,27 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
         part[PART_FEASIBLE] = double(sc.feasible_count);
       }
     } else {
-      for (int i = t; i < 2 * N; i += FINAL_BS) {   // i = c*N + j (col-major N x m)
-        const int c = i / N, j = i - c * N;
-        double s = 0.0;
-        for (int ks = 0; ks < buf.ksplit; ++ks) s += double(buf.Spart[((size_t(b) * buf.ksplit + ks) * N + j) * 2 + c]);
-        part[PART_HDR + i] = s;
+      // Fixed-order tree over the ksplit partials: one warp per output column (2N control
+      // sums + eta), lanes across ksplit, all loads of a warp's columns independent.
+      {
+        const int lane = t & 31, wid = t >> 5, ks_n = buf.ksplit;
+        const R* Sp = buf.Spart + size_t(b) * ks_n * N * 2;
+        const R* Ep = buf.eta_part + size_t(b) * ks_n;
+        for (int col = wid; col <= 2 * N; col += FINAL_BS / 32) {   // col = c*N + j; col == 2N: eta
+          double s = 0.0;
+          for (int ks = lane; ks < ks_n; ks += 32) {
+            if (col < 2 * N) { const int c = col / N, j = col - c * N; s += double(Sp[(size_t(ks) * N + j) * 2 + c]); }
+            else s += double(Ep[ks]);
+          }
+          s = warp_sum(s);
+          if (lane == 0) {
+            if (col < 2 * N) part[PART_HDR + col] = s;
+            else part[PART_ETA] = s;
+          }
+        }
       }
       if (t == 0) {
-        double eta = 0.0;
-        for (int ks = 0; ks < buf.ksplit; ++ks) eta += double(buf.eta_part[size_t(b) * buf.ksplit + ks]);
         part[PART_RHO] = double(key_cost(sc.rho_key, R(0)));
-        part[PART_ETA] = eta;
         // FP32 key carries the index unless the cut-off kernel wrote argmin explicitly
         const unsigned int arg = (sizeof(R) == 4 && sc.argmin == 0xFFFFFFFFu) ? (unsigned int)(sc.rho_key & 0xFFFFFFFFull) : sc.argmin;
         part[PART_ARGMIN] = double(arg) + double(p.k_offset);
@@ -238,31 +248,56 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
     }
   }
   __syncthreads();
+  // Final nominal rollout, TrajectoryRollout(MPPI, MPPICtrl) (MPPIUtils.jl:192).  Only the
+  // state recurrence is sequential: thread 0 integrates x_0..x_N into shared memory, then the
+  // N+1 states are costed / tested / exported in parallel and summed in horizon order.
+  constexpr int NX = Model::NX, ROW = Model::NX + 2;   // state, sin(heading), cos(heading)
+  R* sX = sNew + 2 * N;                 // [N+1][ROW]
+  R* sC = sX + (N + 1) * ROW;           // [N+1][3]: stage+control cost, bound violation, hits
   if (t == 0) {
-    // final nominal rollout, TrajectoryRollout(MPPI, MPPICtrl) (MPPIUtils.jl:192)
-    const int NX = Model::NX;
-    double* tr = buf.res_traj + size_t(b) * (N + 1) * NX;   // col-major (N+1) x n_x
     Model veh;
     veh.init(p, buf.x0 + size_t(b) * MPPI_MAX_NX);
-    const R gx0 = veh.s[0] - p.goal[0], gy0 = veh.s[1] - p.goal[1];
-    const R d0 = gx0 * gx0 + gy0 * gy0;
-    R stage = R(0), viol = R(0);
-    int hits = 0;
 #pragma unroll
-    for (int i = 0; i < NX; ++i) tr[size_t(i) * (N + 1)] = double(veh.s[i]);
+    for (int i = 0; i < NX; ++i) sX[i] = veh.s[i];
+    sX[NX] = veh.sn; sX[NX + 1] = veh.cs;
     for (int j = 0; j < N; ++j) {
-      const R u0 = sNew[2 * j], u1 = sNew[2 * j + 1];
-      if (SRC != SRC_DWA) stage += sU[4 * j + 2] * (u0 - sU[4 * j]) + sU[4 * j + 3] * (u1 - sU[4 * j + 1]);
-      stage += veh.stage_cost(p, u0, u1);
-      veh.step(p, u0, u1);
-      hits += circle_hits(p, veh.s[0], veh.s[1]);
-      hits += block_hits(p, veh.s[0], veh.s[1], veh.sn, veh.cs);
-      viol += bound_violation<R, Model::NX>(p, veh.s);
+      veh.step(p, sNew[2 * j], sNew[2 * j + 1]);
+      R* row = sX + (j + 1) * ROW;
 #pragma unroll
-      for (int i = 0; i < NX; ++i) tr[size_t(i) * (N + 1) + j + 1] = double(veh.s[i]);
+      for (int i = 0; i < NX; ++i) row[i] = veh.s[i];
+      row[NX] = veh.sn; row[NX + 1] = veh.cs;
     }
-    stage += veh.stage_cost(p, R(0), R(0));
-    const R gx = veh.s[0] - p.goal[0], gy = veh.s[1] - p.goal[1];
+  }
+  __syncthreads();
+  double* tr = buf.res_traj + size_t(b) * (N + 1) * NX;   // col-major (N+1) x n_x
+  for (int j = t; j <= N; j += FINAL_BS) {
+    const R* row = sX + j * ROW;
+    Model veh;
+#pragma unroll
+    for (int i = 0; i < NX; ++i) { veh.s[i] = row[i]; tr[size_t(i) * (N + 1) + j] = double(row[i]); }
+    R c = R(0), v = R(0);
+    int hits = 0;
+    if (j < N) {
+      const R u0 = sNew[2 * j], u1 = sNew[2 * j + 1];
+      if (SRC != SRC_DWA) c = sU[4 * j + 2] * (u0 - sU[4 * j]) + sU[4 * j + 3] * (u1 - sU[4 * j + 1]);
+      c += veh.stage_cost(p, u0, u1);
+    } else {
+      c = veh.stage_cost(p, R(0), R(0));   // terminal slot (:49,:53)
+    }
+    if (j > 0) {   // x_0 is never tested (:40-41)
+      hits = circle_hits(p, row[0], row[1]) + block_hits(p, row[0], row[1], row[NX], row[NX + 1]);
+      v = bound_violation<R, NX>(p, row);
+    }
+    sC[3 * j] = c; sC[3 * j + 1] = v; sC[3 * j + 2] = R(hits);
+  }
+  __syncthreads();
+  if (t == 0) {
+    const R gx0 = sX[0] - p.goal[0], gy0 = sX[1] - p.goal[1];
+    const R d0 = gx0 * gx0 + gy0 * gy0;
+    R stage = R(0), viol = R(0), fh = R(0);
+    for (int j = 0; j <= N; ++j) { stage += sC[3 * j]; viol += sC[3 * j + 1]; fh += sC[3 * j + 2]; }
+    const int hits = int(fh);
+    const R gx = sX[N * ROW] - p.goal[0], gy = sX[N * ROW + 1] - p.goal[1];
     const R term = Math<R>::div(gx * gx + gy * gy, d0) * p.term_scale;
     const R cost = stage + p.slack * viol + p.obs_pen * R(hits) + term;
     double* rs = buf.res_scalars + size_t(b) * RES_SCALARS;

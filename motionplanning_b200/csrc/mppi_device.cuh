@@ -84,6 +84,42 @@ struct Buffers {
 };
 
 // ---------------------------------------------------------------------------
+// Hot parameters held in per-thread registers for the horizon loop.
+// sm_100 ALU instructions take no constant-bank operands: every use of a kernel
+// parameter inside the loop costs an LDCU (uniform load) issue slot, and ptxas
+// re-issues them every iteration (~25 of 243 slots per step in profiles/r01a).
+// The block therefore stages the hot parameters ONCE in shared memory and every
+// thread copies them to registers before its horizon loop; a value that arrived
+// through LDS cannot be rematerialised from the constant bank.
+// Same field names as StaticParams so the model code is generic over both.
+// ---------------------------------------------------------------------------
+constexpr int HOT_CIRCLES = 8;   // circles (2 quads) that can ride in registers
+
+template <class R, int NX>
+struct HotParams {
+  R dt, half_dt, Lwb, inv_Lwb;
+  R XL[NX], XU[NX], CL[2], CU[2], w[6];
+  R la, lb, mass, Izz, mu, KFZX, FZF0, FZR0, tireB, tireC, tireD, tireE;
+  R L00, L10, L11;
+  R circ[HOT_CIRCLES][3];
+  uint32_t key[20];   // Philox round keys
+  __device__ __forceinline__ void fill(const StaticParams<R>& p) {
+    dt = p.dt; half_dt = p.half_dt; Lwb = p.Lwb; inv_Lwb = p.inv_Lwb;
+    for (int i = 0; i < NX; ++i) { XL[i] = p.XL[i]; XU[i] = p.XU[i]; }
+    for (int i = 0; i < 2; ++i) { CL[i] = p.CL[i]; CU[i] = p.CU[i]; }
+    for (int i = 0; i < 6; ++i) w[i] = p.w[i];
+    la = p.la; lb = p.lb; mass = p.mass; Izz = p.Izz; mu = p.mu; KFZX = p.KFZX;
+    FZF0 = p.FZF0; FZR0 = p.FZR0;
+    tireB = p.tireB; tireC = p.tireC; tireD = p.tireD; tireE = p.tireE;
+    L00 = p.L00; L10 = p.L10; L11 = p.L11;
+    for (int o = 0; o < HOT_CIRCLES; ++o)
+      for (int c = 0; c < 3; ++c) circ[o][c] = p.circ[o][c];
+    uint32_t k0 = p.seed_lo, k1 = p.seed_hi;
+    for (int r = 0; r < 10; ++r) { key[2 * r] = k0; key[2 * r + 1] = k1; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+  }
+};
+
+// ---------------------------------------------------------------------------
 // math traits
 // ---------------------------------------------------------------------------
 template <class R> struct Math;

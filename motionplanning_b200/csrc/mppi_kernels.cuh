@@ -57,18 +57,99 @@ __device__ __forceinline__ double key_cost(unsigned long long key, double) { ret
 // Schedule (MPPIUtils.jl:39-53): states x_1..x_N are each tested once against
 // obstacles and bounds (x_0 never is); stage cost is taken at the pre-step state.
 // ---------------------------------------------------------------------------
+// Per-sample accumulators of the rollout (registers).
+template <class R>
+struct RolloutAcc {
+  R stage = R(0);   // stage + control cost (MPPIUtils.jl:45, vehicledynamics.jl:52)
+  R viol = R(0);    // sum of bound violations (slack applied once at the end)
+  int hits = 0;     // obstacle hits
+};
+
+// The horizon loop for one sample, specialised on the number of circle quads held in
+// registers (NQ >= 0) or reading the circle table (NQ < 0).
+template <class R, class Model, int SRC, int NQ>
+__device__ __forceinline__ void rollout_horizon(const StaticParams<R>& p, const Buffers<R>& buf, Model& veh,
+                                                RolloutAcc<R>& acc, const HotParams<R, Model::NX>* sHot,
+                                                const R* sU, int b, int k) {
+  using R2 = typename Vec2<R>::type;
+  using R4 = typename Vec4<R>::type;
+  const int N = p.N;
+  const HotParams<R, Model::NX> hp = *sHot;   // smem -> registers (unused fields are dead)
+  const bool walls = p.n_blocks > 0;
+  const size_t estride = size_t(p.K_local);
+  R2* eps = reinterpret_cast<R2*>(buf.eps) + size_t(b) * N * estride + k;
+  const R4* nu_p = reinterpret_cast<const R4*>(sU);
+  R cu0 = R(0), cu1 = R(0);
+  if (SRC == SRC_DWA) {
+    cu0 = R(buf.cand[k]);
+    cu1 = R(buf.cand[estride + k]);
+  }
+  // one horizon step: PushInBounds, control cost, stage cost, Heun step, tests of x_{j+1}
+  auto advance = [&](R4 nu, R2 e) {
+    R u0, u1;
+    if (SRC == SRC_DWA) {
+      u0 = cu0; u1 = cu1;
+    } else {
+      u0 = Math<R>::fmin(Math<R>::fmax(nu.x + e.x, hp.CL[0]), hp.CU[0]);   // PushInBounds (:13-20)
+      u1 = Math<R>::fmin(Math<R>::fmax(nu.y + e.y, hp.CL[1]), hp.CU[1]);
+      acc.stage += nu.z * (u0 - nu.x) + nu.w * (u1 - nu.y);                // lambda*U_nom'*inv(Sigma)*(u-U_nom) (:45)
+    }
+    acc.stage += veh.stage_cost(hp, u0, u1);       // VehicleDynamics cost at the pre-step state
+    veh.step(hp, u0, u1);                          // Rungekutta2 (:76-90)
+    if (NQ >= 0) acc.hits += circle_hits_regs<R, (NQ > 0 ? NQ : 0)>(hp, veh.s[0], veh.s[1]);   // x_{j+1}: ObstacleEvaluation
+    else acc.hits += circle_hits(p, veh.s[0], veh.s[1]);
+    if (walls) acc.hits += block_hits(p, veh.s[0], veh.s[1], veh.sn, veh.cs);
+    acc.viol += bound_violation<R, Model::NX>(hp, veh.s);                 // BoundEvaluation
+  };
+  if (SRC == SRC_PHILOX) {
+    // one Philox4x32-10 call feeds two horizon steps; eps = chol(Sigma) * z (MPPIUtils.jl:6)
+    // is kept for the update kernel / oracle replay
+    const R L00 = hp.L00, L10 = hp.L10, L11 = hp.L11;
+    const uint32_t gk = uint32_t(p.k_offset + k), iter = *buf.iter;
+    for (int j = 0; j < N; j += 2) {
+      const uint4 rnd = philox4x32_10(make_uint4(gk, uint32_t(j >> 1), iter, uint32_t(b)), hp.key);
+      float z0, z1;
+      box_muller(rnd.x, rnd.y, &z0, &z1);
+      R2 e;
+      e.x = L00 * R(z0);
+      e.y = L10 * R(z0) + L11 * R(z1);
+      *eps = e;
+      advance(nu_p[j], e);
+      if (j + 1 < N) {
+        box_muller(rnd.z, rnd.w, &z0, &z1);
+        e.x = L00 * R(z0);
+        e.y = L10 * R(z0) + L11 * R(z1);
+        eps[estride] = e;
+        advance(nu_p[j + 1], e);
+      }
+      eps += 2 * estride;
+    }
+  } else if (SRC == SRC_SUPPLIED) {
+    R2 e_next = *eps;
+    for (int j = 0; j < N; ++j) {
+      const R2 e = e_next;
+      eps += estride;
+      if (j + 1 < N) e_next = *eps;   // prefetch next step's noise
+      advance(nu_p[j], e);
+    }
+  } else {
+    for (int j = 0; j < N; ++j) advance(R4{R(0), R(0), R(0), R(0)}, R2{R(0), R(0)});
+  }
+}
+
 template <class R, class Model, int SRC>
 __global__ void __launch_bounds__(ROLLOUT_BS)
 rollout_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) {
-  using R2 = typename Vec2<R>::type;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   R* sU = reinterpret_cast<R*>(smem_raw);  // [N][4]: u0, u1, g0, g1
   __shared__ unsigned long long s_key[ROLLOUT_BS / 32];
   __shared__ int s_feas[ROLLOUT_BS / 32];
+  __shared__ __align__(16) HotParams<R, Model::NX> sHot;
 
   const int b = blockIdx.y;
   const int N = p.N;
   const int k = blockIdx.x * ROLLOUT_BS + threadIdx.x;
+  if (threadIdx.x == ROLLOUT_BS - 1) sHot.fill(p);
   const bool active = k < p.K_local;
   const double* Ub = buf.U + size_t(b) * 2 * N;
   if (SRC != SRC_DWA) {
@@ -79,88 +160,36 @@ rollout_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) 
       sU[4 * j + 2] = p.G00 * u0 + p.G01 * u1;
       sU[4 * j + 3] = p.G10 * u0 + p.G11 * u1;
     }
-    __syncthreads();
   }
+  __syncthreads();
 
   R cost = R(0);
-  int hits = 0;
-  R viol = R(0);
+  RolloutAcc<R> acc;
   if (active) {
     const double* x0 = buf.x0 + size_t(b) * MPPI_MAX_NX;
     Model veh;
     veh.init(p, x0);
     const R gx0 = veh.s[0] - p.goal[0], gy0 = veh.s[1] - p.goal[1];
     const R d0 = gx0 * gx0 + gy0 * gy0;
-    R stage = R(0);
-    R2* eps = reinterpret_cast<R2*>(buf.eps) + size_t(b) * N * p.K_local + k;
-    R cu0 = R(0), cu1 = R(0);
-    unsigned int iter = 0;
-    if (SRC == SRC_PHILOX) iter = *buf.iter;
-    if (SRC == SRC_DWA) {
-      cu0 = R(buf.cand[k]);
-      cu1 = R(buf.cand[size_t(p.K_local) + k]);
-    }
-    // one horizon step: PushInBounds, control cost, stage cost, Heun step, tests of x_{j+1}
-    auto advance = [&](int j, R2 e) {
-      R u0, u1;
-      if (SRC == SRC_DWA) {
-        u0 = cu0; u1 = cu1;
-      } else {
-        const typename Vec4<R>::type nu = reinterpret_cast<const typename Vec4<R>::type*>(sU)[j];   // u0, u1, g0, g1
-        u0 = Math<R>::fmin(Math<R>::fmax(nu.x + e.x, p.CL[0]), p.CU[0]);   // PushInBounds (:13-20)
-        u1 = Math<R>::fmin(Math<R>::fmax(nu.y + e.y, p.CL[1]), p.CU[1]);
-        stage += nu.z * (u0 - nu.x) + nu.w * (u1 - nu.y);                  // lambda*U_nom'*inv(Sigma)*(u-U_nom) (:45)
-      }
-      stage += veh.stage_cost(p, u0, u1);            // VehicleDynamics cost at the pre-step state
-      veh.step(p, u0, u1);                           // Rungekutta2 (:76-90)
-      hits += circle_hits(p, veh.s[0], veh.s[1]);    // x_{j+1}: ObstacleEvaluation
-      hits += block_hits(p, veh.s[0], veh.s[1], veh.sn, veh.cs);
-      viol += bound_violation<R, Model::NX>(p, veh.s);   // BoundEvaluation
-    };
-    if (SRC == SRC_PHILOX) {
-      // one Philox4x32-10 call feeds two horizon steps; eps = chol(Sigma) * z (MPPIUtils.jl:6)
-      // is kept for the update kernel / oracle replay
-      const uint32_t gk = uint32_t(p.k_offset + k);
-      for (int j = 0; j < N; j += 2) {
-        const uint4 rnd = philox4x32_10(make_uint4(gk, uint32_t(j >> 1), iter, uint32_t(b)), p.seed_lo, p.seed_hi);
-        float z0, z1;
-        box_muller(rnd.x, rnd.y, &z0, &z1);
-        R2 e;
-        e.x = p.L00 * R(z0);
-        e.y = p.L10 * R(z0) + p.L11 * R(z1);
-        eps[size_t(j) * p.K_local] = e;
-        advance(j, e);
-        if (j + 1 < N) {
-          box_muller(rnd.z, rnd.w, &z0, &z1);
-          e.x = p.L00 * R(z0);
-          e.y = p.L10 * R(z0) + p.L11 * R(z1);
-          eps[size_t(j + 1) * p.K_local] = e;
-          advance(j + 1, e);
-        }
-      }
-    } else if (SRC == SRC_SUPPLIED) {
-      R2 e_next = eps[0];
-      for (int j = 0; j < N; ++j) {
-        const R2 e = e_next;
-        if (j + 1 < N) e_next = eps[size_t(j + 1) * p.K_local];   // prefetch next step's noise
-        advance(j, e);
-      }
-    } else {
-      for (int j = 0; j < N; ++j) advance(j, R2{R(0), R(0)});
-    }
-    stage += veh.stage_cost(p, R(0), R(0));          // terminal slot: VehicleDynamics(x_N, [0,0]) (:49,:53)
+    const int nq = (p.n_circles + 3) >> 2;   // warp-uniform: the whole horizon loop is specialised
+    if (sizeof(R) == 8) rollout_horizon<R, Model, SRC, -1>(p, buf, veh, acc, &sHot, sU, b, k);
+    else if (nq == 0) rollout_horizon<R, Model, SRC, 0>(p, buf, veh, acc, &sHot, sU, b, k);
+    else if (nq == 1) rollout_horizon<R, Model, SRC, 1>(p, buf, veh, acc, &sHot, sU, b, k);
+    else if (nq == 2) rollout_horizon<R, Model, SRC, 2>(p, buf, veh, acc, &sHot, sU, b, k);
+    else rollout_horizon<R, Model, SRC, -1>(p, buf, veh, acc, &sHot, sU, b, k);
+    acc.stage += veh.stage_cost(p, R(0), R(0));      // terminal slot: VehicleDynamics(x_N, [0,0]) (:49,:53)
     const R gx = veh.s[0] - p.goal[0], gy = veh.s[1] - p.goal[1];
     const R term = Math<R>::div(gx * gx + gy * gy, d0) * p.term_scale;   // (:54)
-    cost = stage + p.slack * viol + p.obs_pen * R(hits) + term;
+    cost = acc.stage + p.slack * acc.viol + p.obs_pen * R(acc.hits) + term;
     buf.costs[size_t(b) * p.K_local + k] = cost;
     buf.flags[size_t(b) * p.K_local + k] =
-        uint8_t(((hits == 0 && !(viol > R(0))) ? MPPI_FLAG_FEASIBLE : 0) | (hits ? MPPI_FLAG_COLLIDED : 0) |
-                ((viol > R(0)) ? MPPI_FLAG_OOB : 0));
+        uint8_t(((acc.hits == 0 && !(acc.viol > R(0))) ? MPPI_FLAG_FEASIBLE : 0) | (acc.hits ? MPPI_FLAG_COLLIDED : 0) |
+                ((acc.viol > R(0)) ? MPPI_FLAG_OOB : 0));
   }
   // block epilogue: (min cost, first index) and feasible count -> one atomic each
   unsigned long long key = active ? make_key(cost, (unsigned int)k) : 0xFFFFFFFFFFFFFFFFull;
   key = warp_min_u64(key);
-  const unsigned feas_mask = __ballot_sync(0xffffffffu, active && hits == 0 && !(viol > R(0)));
+  const unsigned feas_mask = __ballot_sync(0xffffffffu, active && acc.hits == 0 && !(acc.viol > R(0)));
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   if (lane == 0) { s_key[wid] = key; s_feas[wid] = __popc(feas_mask); }
   __syncthreads();

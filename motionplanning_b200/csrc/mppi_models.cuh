@@ -28,10 +28,12 @@ struct Kin5 {
     tn = Math<R>::over(Math<R>::tan(s[4]), p.Lwb, p.inv_Lwb);
   }
   // stage cost of VehicleDynamics at (state, u): SURVEY 8(a) a6 = dynamic cost with v = r = 0
-  __device__ __forceinline__ R stage_cost(const StaticParams<R>& p, R sr, R ax) const {
+  template <class P>
+  __device__ __forceinline__ R stage_cost(const P& p, R sr, R ax) const {
     return p.w[2] * (ax * ax) + p.w[3] * (sr * sr) + p.w[4] * (s[4] * s[4]) + p.w[5] * (s[1] * s[1]);
   }
-  __device__ __forceinline__ void step(const StaticParams<R>& p, R sr, R ax) {
+  template <class P>
+  __device__ __forceinline__ void step(const P& p, R sr, R ax) {
     // k1 at (s, u)
     const R k1x = s[3] * cs, k1y = s[3] * sn, k1p = s[3] * tn;   // ux cosψ, ux sinψ, ux/L tan(sa)
     // predictor x + k1*dt
@@ -70,18 +72,21 @@ struct Dyn7 {
     for (int i = 0; i < NX; ++i) s[i] = R(x0[i]);
     Math<R>::sincos(s[IPSI], &sn, &cs);
   }
-  __device__ __forceinline__ R stage_cost(const StaticParams<R>& p, R sr, R ax) const {  // :52
+  template <class P>
+  __device__ __forceinline__ R stage_cost(const P& p, R sr, R ax) const {  // :52
     return s[2] * s[2] * p.w[0] + p.w[1] * (s[3] * s[3]) + p.w[2] * (ax * ax) + p.w[3] * (sr * sr) +
            p.w[4] * (s[6] * s[6]) + p.w[5] * (s[1] * s[1]);
   }
   // lateral tyre force (:35-38): mu*FZ*D*sin(C*atan(X - E*(X - atan X))), X = B*alpha
-  static __device__ __forceinline__ R tyre(const StaticParams<R>& p, R FZ, R alpha) {
+  template <class P>
+  static __device__ __forceinline__ R tyre(const P& p, R FZ, R alpha) {
     const R X = p.tireB * alpha;
     const R inner = X - p.tireE * (X - Math<R>::atan(X));
     return p.mu * FZ * p.tireD * Math<R>::sin(p.tireC * Math<R>::atan(inner));
   }
   // derivatives of (v, r) and the planar velocity at state q with heading sin/cos (sq, cq)
-  static __device__ __forceinline__ void deriv(const StaticParams<R>& p, R v, R r, R ux, R sa, R sq, R cq,
+  template <class P>
+  static __device__ __forceinline__ void deriv(const P& p, R v, R r, R ux, R sa, R sq, R cq,
                                                R ax, R* dx, R* dy, R* dv, R* dr) {
     const R t = ax - r * v;
     const R FZF = R(2) * (p.FZF0 - t * p.KFZX);                              // :30
@@ -97,7 +102,8 @@ struct Dyn7 {
     *dv = Math<R>::div(FY1 + FY2, p.mass) - r * uxc;                         // :46
     *dr = Math<R>::div(FY1 * p.la - FY2 * p.lb, p.Izz);                      // :47
   }
-  __device__ __forceinline__ void step(const StaticParams<R>& p, R sr, R ax) {
+  template <class P>
+  __device__ __forceinline__ void step(const P& p, R sr, R ax) {
     R k1x, k1y, k1v, k1r;
     deriv(p, s[2], s[3], s[5], s[6], sn, cs, ax, &k1x, &k1y, &k1v, &k1r);
     const R k1p = s[3];                                                      // dpsi = r (:45)
@@ -136,6 +142,18 @@ __device__ __forceinline__ int circle_hits_quads(const StaticParams<R>& p, R x, 
   }
   return hits;
 }
+// the first 4*Q circles of a register-resident table (horizon loop of the rollout kernel)
+template <class R, int Q, class P>
+__device__ __forceinline__ int circle_hits_regs(const P& hp, R px, R py) {
+  int h = 0;
+#pragma unroll
+  for (int o = 0; o < 4 * Q; ++o) {
+    const R dx = px - hp.circ[o][0], dy = py - hp.circ[o][1];
+    h += (dx * dx + dy * dy <= hp.circ[o][2]) ? 1 : 0;
+  }
+  return h;
+}
+
 template <class R>
 __device__ __forceinline__ int circle_hits(const StaticParams<R>& p, R x, R y) {
   switch ((p.n_circles + 3) >> 2) {   // warp-uniform
@@ -182,8 +200,8 @@ __device__ __forceinline__ int block_hits(const StaticParams<R>& p, R x, R y, R 
 // (strict inequalities; the slack factor is applied once at the end).
 // XL <= XU, so at most one side is violated: max(XL - s, s - XU, 0) equals the sum of
 // the two one-sided terms exactly (the other term is +0).
-template <class R, int NX>
-__device__ __forceinline__ R bound_violation(const StaticParams<R>& p, const R* s) {
+template <class R, int NX, class P>
+__device__ __forceinline__ R bound_violation(const P& p, const R* s) {
   R acc = R(0);
 #pragma unroll
   for (int i = 0; i < NX; ++i)
@@ -203,6 +221,18 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1
     c = make_uint4(hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0);
     k0 += 0x9E3779B9u;
     k1 += 0xBB67AE85u;
+  }
+  return c;
+}
+
+// same function with the 10 round keys precomputed (warp-uniform and identical for every
+// call of a launch; 20 UIADD3 issue slots per call otherwise)
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, const uint32_t* key) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(hi1 ^ c.y ^ key[2 * r], lo1, hi0 ^ c.w ^ key[2 * r + 1], lo0);
   }
   return c;
 }

@@ -212,7 +212,11 @@ int32_t mppi_comm_init(mppi_handle_t* h, const uint8_t id[MPPI_COMM_ID_BYTES], i
 /* timings of the last step in microseconds (CUDA events on the handle's stream):
  * [0] rollout, [1] softmin+update, [2] combine+nominal rollout, [3] whole device step */
 int32_t mppi_get_timings(mppi_handle_t* h, float us[4]);
-/* toggle per-kernel event timing (disables graph replay for that step) */
+/* SM-clock stamps (clock64) at the phase boundaries of the last finalize kernel, instance 0:
+ * [0] entry, [1] partials reduced, [2] ranks combined, [3] U_new ready, [4] nominal state
+ * recurrence done, [5] states costed, [6] result written.  Diagnostics only. */
+int32_t mppi_get_phase_clocks(mppi_handle_t* h, uint64_t clocks[16]);
+/* toggle per-kernel event timing (eager launches bracketed by events; no graph replay) */
 int32_t mppi_set_profiling(mppi_handle_t* h, int32_t on);
 /* number of kernels the library launched on this handle so far */
 int64_t mppi_launch_count(const mppi_handle_t* h);

@@ -104,6 +104,7 @@ SIGNATURES = {
     "mppi_comm_unique_id": (_i, [_P(C.c_uint8)]),
     "mppi_comm_init": (_i, [_H, _P(C.c_uint8), _i, _i]),
     "mppi_get_timings": (_i, [_H, _P(C.c_float)]),
+    "mppi_get_phase_clocks": (_i, [_H, _P(C.c_uint64)]),
     "mppi_set_profiling": (_i, [_H, _i]),
     "mppi_launch_count": (C.c_int64, [_H]),
     "mppi_check_poses": (_i, [_H, _P(_d), _i, _P(_i)]),

@@ -89,7 +89,7 @@ int32_t mppi_destroy(mppi_handle_t* h) {
   drop_graphs(h);
   if (h->comm && nccl_api().CommDestroy) nccl_api().CommDestroy(h->comm);
   void* dev[] = {h->d_in, h->d_eps, h->d_costs, h->d_flags, h->d_scratch, h->d_scratch_tmpl, h->d_iter, h->d_Spart,
-                 h->d_eta_part, h->d_partial, h->d_gathered, h->d_res, h->d_cand};
+                 h->d_eta_part, h->d_partial, h->d_gathered, h->d_res, h->d_cand, h->d_dbg};
   for (void* p : dev) if (p) cudaFree(p);
   void* host[] = {h->h_in, h->h_res, h->h_partial, h->h_gathered};
   for (void* p : host) if (p) cudaFreeHost(p);
@@ -127,6 +127,8 @@ static int create_impl(mppi_handle* h) {
   MPPI_CUDA(h, cudaMalloc(&h->d_res, B * (RES_SCALARS + 2 * N + (N + 1) * c.n_x) * sizeof(double)));
   h->d_traj = h->d_res + B * (RES_SCALARS + 2 * N);
   if (c.planner == MPPI_PLANNER_DWA) MPPI_CUDA(h, cudaMalloc(&h->d_cand, K * 2 * sizeof(double)));
+  MPPI_CUDA(h, cudaMalloc(&h->d_dbg, 16 * sizeof(unsigned long long)));
+  MPPI_CUDA(h, cudaMemset(h->d_dbg, 0, 16 * sizeof(unsigned long long)));
   MPPI_CUDA(h, cudaMallocHost(&h->h_in, B * (MPPI_MAX_NX + 2 * N) * sizeof(double)));
   MPPI_CUDA(h, cudaMallocHost(&h->h_res, (B * (RES_SCALARS + 2 * N) + (N + 1) * c.n_x) * sizeof(double)));
   h->h_traj = h->h_res + B * (RES_SCALARS + 2 * N);

@@ -79,6 +79,7 @@ struct Buffers {
   double* res_control;  // [B][2*N]  col-major N x m
   double* res_traj;     // [B][(N+1)*n_x] col-major (N+1) x n_x
   const double* cand;   // DWA: [K][2] col-major K x m candidates
+  unsigned long long* dbg;  // [16] SM-clock stamps at the phase boundaries of finalize (instance 0)
   int ksplit;
   int n_ranks;
 };

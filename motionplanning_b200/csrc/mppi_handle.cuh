@@ -67,6 +67,7 @@ struct mppi_handle {
   double* d_res = nullptr;       // [B][RES_SCALARS] then [B][2N]
   double* d_traj = nullptr;      // [B][(N+1)*n_x], inside the d_res allocation
   double* d_cand = nullptr;      // DWA candidates K x 2 col-major
+  unsigned long long* d_dbg = nullptr;   // [16] finalize phase clocks
   // pinned host mirrors
   double* h_in = nullptr;
   double* h_res = nullptr;
@@ -83,7 +84,7 @@ struct mppi_handle {
   int rank = 0, n_ranks = 1;
   // profiling
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
-  bool profiling = false;
+  int profiling = 0;   // 0 off | 1 eager launches bracketed by events | 2 graph replay with event-record nodes
   float us[4] = {0, 0, 0, 0};
   int64_t launches = 0;
   bool stepped = false;
@@ -171,6 +172,7 @@ Buffers<R> make_buffers(const mppi_handle* h) {
   b.res_control = h->d_res + size_t(B) * RES_SCALARS;
   b.res_traj = h->d_traj;
   b.cand = h->d_cand;
+  b.dbg = h->d_dbg;
   b.ksplit = h->ksplit;
   b.n_ranks = h->n_ranks;
   return b;

@@ -10,7 +10,7 @@
 namespace mppi {
 
 enum { SRC_SUPPLIED = 0, SRC_PHILOX = 1, SRC_DWA = 2 };
-constexpr int ROLLOUT_BS = 128;
+constexpr int ROLLOUT_BS = 64;   // 65,536 samples = 1024 CTAs = 6.9 per SM: one balanced wave on 148 SMs
 constexpr int UPDATE_BS = 256;
 constexpr int UPDATE_JG = 4;
 constexpr int FINAL_BS = 256;

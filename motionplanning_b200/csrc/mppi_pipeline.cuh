@@ -27,7 +27,7 @@ template <> inline const StaticParams<float>& params_of<float>(const mppi_handle
 template <> inline const StaticParams<double>& params_of<double>(const mppi_handle* h) { return h->pd; }
 
 template <class R, class Model, int SRC>
-int enqueue_variant(mppi_handle* h, int v, bool timed) {
+int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all events, 2 = inner boundaries only (graph nodes)
   const StaticParams<R>& p = params_of<R>(h);
   Buffers<R> buf = make_buffers<R>(h);
   if (v & V_FUSED_FINAL) { buf.gathered = buf.partial; buf.n_ranks = 1; }   // single rank: combine reads its own partial
@@ -37,7 +37,7 @@ int enqueue_variant(mppi_handle* h, int v, bool timed) {
   const size_t res_bytes = size_t(B) * (RES_SCALARS + 2 * N) * sizeof(double);
   const size_t smemU = size_t(N) * 4 * sizeof(R);
 
-  if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[0], s));
+  if (timed == 1) MPPI_CUDA(h, cudaEventRecord(h->ev[0], s));
   if (v & V_H2D_IN) MPPI_CUDA(h, cudaMemcpyAsync(h->d_in, h->h_in, in_bytes, cudaMemcpyHostToDevice, s));
   if (v & V_H2D_X0) MPPI_CUDA(h, cudaMemcpyAsync(h->d_in, h->h_in, size_t(B) * MPPI_MAX_NX * sizeof(double), cudaMemcpyHostToDevice, s));
   if (v & V_H2D_U)
@@ -91,7 +91,7 @@ int enqueue_variant(mppi_handle* h, int v, bool timed) {
     const size_t traj_bytes = (B == 1) ? size_t(N + 1) * nx * sizeof(double) : 0;   // contiguous with the scalars
     MPPI_CUDA(h, cudaMemcpyAsync(h->h_res, h->d_res, res_bytes + traj_bytes, cudaMemcpyDeviceToHost, s));
   }
-  if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[4], s));
+  if (timed == 1) MPPI_CUDA(h, cudaEventRecord(h->ev[4], s));
   MPPI_CUDA(h, cudaGetLastError());
   return MPPI_OK;
 }
@@ -102,7 +102,7 @@ inline int source_of(const mppi_handle* h) {
 }
 
 template <class R, class Model>
-int enqueue_src(mppi_handle* h, int v, bool timed) {
+int enqueue_src(mppi_handle* h, int v, int timed) {
   switch (source_of(h)) {
     case SRC_PHILOX: return enqueue_variant<R, Model, SRC_PHILOX>(h, v, timed);
     case SRC_DWA: return enqueue_variant<R, Model, SRC_DWA>(h, v, timed);
@@ -110,11 +110,11 @@ int enqueue_src(mppi_handle* h, int v, bool timed) {
   }
 }
 template <class R>
-int enqueue_model(mppi_handle* h, int v, bool timed) {
+int enqueue_model(mppi_handle* h, int v, int timed) {
   if (h->cfg.model == MPPI_MODEL_DYNAMIC7) return enqueue_src<R, Dyn7<R>>(h, v, timed);
   return enqueue_src<R, Kin5<R>>(h, v, timed);
 }
-inline int enqueue(mppi_handle* h, int v, bool timed) {
+inline int enqueue(mppi_handle* h, int v, int timed) {
   if (h->cfg.precision == MPPI_FP64) return enqueue_model<double>(h, v, timed);
   return enqueue_model<float>(h, v, timed);
 }
@@ -139,17 +139,19 @@ inline int take_dirty(mppi_handle* h) {
 
 // run a variant: graph replay (captured on first use) or eager when profiling / graphs are off
 inline int run_variant(mppi_handle* h, int v) {
-  const bool use_graph = h->cfg.use_cuda_graph && !h->profiling;
+  const bool use_graph = h->cfg.use_cuda_graph && h->profiling != 1;
   if (!use_graph) {
     h->in_flight = true;
-    return enqueue(h, v, h->profiling);
+    return enqueue(h, v & 0xFFFF, h->profiling ? 1 : 0);
   }
+  const bool inner = h->profiling == 2;
+  if (inner) v |= 1 << 24;   // graphs with event-record nodes are cached separately
   auto it = h->graphs.find(v);
   if (it == h->graphs.end()) {
     cudaGraph_t g = nullptr;
     const int64_t before = h->launches;
     MPPI_CUDA(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
-    int rc = enqueue(h, v, false);
+    int rc = enqueue(h, v & 0xFFFF, inner ? 2 : 0);
     cudaError_t e = cudaStreamEndCapture(h->stream, &g);
     h->launches = before;
     if (rc != MPPI_OK) { if (g) cudaGraphDestroy(g); return rc; }
@@ -165,7 +167,7 @@ inline int run_variant(mppi_handle* h, int v) {
   MPPI_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
   MPPI_CUDA(h, cudaGraphLaunch(it->second, h->stream));
   MPPI_CUDA(h, cudaEventRecord(h->ev[4], h->stream));
-  h->launches += kernels_in(h, v);
+  h->launches += kernels_in(h, v & 0xFFFF);
   h->in_flight = true;
   return MPPI_OK;
 }

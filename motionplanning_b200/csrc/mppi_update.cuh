@@ -123,6 +123,7 @@ __global__ void __launch_bounds__(UPDATE_BS) update_kernel(const __grid_constant
 // DWA (DWAUtils.jl:152-158): U_new = the arg-min candidate, replicated over the horizon.
 // ---------------------------------------------------------------------------
 enum { PH_PARTIAL = 1, PH_COMBINE = 2 };
+#define MPPI_STAMP(i) do { if (t == 0 && b == 0) buf.dbg[i] = clock64(); } while (0)
 
 template <class R, class Model, int SRC, int PHASES>
 __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) {
@@ -134,6 +135,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
   const int b = blockIdx.x, N = p.N, t = threadIdx.x;
   const int plen = PART_HDR + 2 * N;
   double* part = buf.partial + size_t(b) * plen;
+  MPPI_STAMP(0);
   const Scratch sc = buf.scratch[b];
 
   if (PHASES & PH_PARTIAL) {
@@ -164,16 +166,31 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
         const int lane = t & 31, wid = t >> 5, ks_n = buf.ksplit;
         const R* Sp = buf.Spart + size_t(b) * ks_n * N * 2;
         const R* Ep = buf.eta_part + size_t(b) * ks_n;
-        for (int col = wid; col <= 2 * N; col += FINAL_BS / 32) {   // col = c*N + j; col == 2N: eta
-          double s = 0.0;
-          for (int ks = lane; ks < ks_n; ks += 32) {
-            if (col < 2 * N) { const int c = col / N, j = col - c * N; s += double(Sp[(size_t(ks) * N + j) * 2 + c]); }
-            else s += double(Ep[ks]);
+        constexpr int NW = FINAL_BS / 32, CB = 16;   // CB columns per warp in flight (independent loads + trees)
+        for (int col0 = wid; col0 <= 2 * N; col0 += NW * CB) {   // col = c*N + j; col == 2N: eta
+          double s[CB];
+#pragma unroll
+          for (int u = 0; u < CB; ++u) {
+            const int col = col0 + u * NW;
+            // ksplit <= 64: two predicated loads per lane, no loop, so the CB columns' loads overlap
+            const bool eta_col = (col == 2 * N);
+            const int c = col >= N ? 1 : 0, j = col - c * N;
+            R v0 = R(0), v1 = R(0);
+            if (col <= 2 * N) {
+              if (lane < ks_n) v0 = eta_col ? Ep[lane] : Sp[(size_t(lane) * N + j) * 2 + c];
+              if (lane + 32 < ks_n) v1 = eta_col ? Ep[lane + 32] : Sp[(size_t(lane + 32) * N + j) * 2 + c];
+            }
+            s[u] = double(v0) + double(v1);
           }
-          s = warp_sum(s);
+#pragma unroll
+          for (int u = 0; u < CB; ++u) s[u] = warp_sum(s[u]);
           if (lane == 0) {
-            if (col < 2 * N) part[PART_HDR + col] = s;
-            else part[PART_ETA] = s;
+#pragma unroll
+            for (int u = 0; u < CB; ++u) {
+              const int col = col0 + u * NW;
+              if (col < 2 * N) part[PART_HDR + col] = s[u];
+              else if (col == 2 * N) part[PART_ETA] = s[u];
+            }
           }
         }
       }
@@ -188,6 +205,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
     }
     __syncthreads();   // block-scope visibility of `part` for the combine phase (G == 1)
   }
+  MPPI_STAMP(1);
   if (!(PHASES & PH_COMBINE)) return;
 
   const int G = buf.n_ranks;
@@ -217,6 +235,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
     rs[RES_RHO] = rho;
     rs[RES_ETA] = eta;
   }
+  MPPI_STAMP(2);
   // stage old nominal + g for the nominal rollout's control-cost term (evaluated
   // against the OLD U_nom: MPPIUtils.jl:192 runs before main.jl:62 replaces it)
   const double* Ub = buf.U + size_t(b) * 2 * N;
@@ -248,6 +267,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
     }
   }
   __syncthreads();
+  MPPI_STAMP(3);
   // Final nominal rollout, TrajectoryRollout(MPPI, MPPICtrl) (MPPIUtils.jl:192).  Only the
   // state recurrence is sequential: thread 0 integrates x_0..x_N into shared memory, then the
   // N+1 states are costed / tested / exported in parallel and summed in horizon order.
@@ -269,6 +289,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
     }
   }
   __syncthreads();
+  MPPI_STAMP(4);
   double* tr = buf.res_traj + size_t(b) * (N + 1) * NX;   // col-major (N+1) x n_x
   for (int j = t; j <= N; j += FINAL_BS) {
     const R* row = sX + j * ROW;
@@ -291,6 +312,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
     sC[3 * j] = c; sC[3 * j + 1] = v; sC[3 * j + 2] = R(hits);
   }
   __syncthreads();
+  MPPI_STAMP(5);
   if (t == 0) {
     const R gx0 = sX[0] - p.goal[0], gy0 = sX[1] - p.goal[1];
     const R d0 = gx0 * gx0 + gy0 * gy0;
@@ -305,6 +327,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
     rs[RES_COST] = double(cost);
     rs[RES_FEASIBLE] = feas ? 1.0 : 0.0;
     rs[RES_FLAGS] = double((feas ? MPPI_FLAG_FEASIBLE : 0) | (hits ? MPPI_FLAG_COLLIDED : 0) | ((viol > R(0)) ? MPPI_FLAG_OOB : 0));
+    MPPI_STAMP(6);
     if (b == 0) *buf.iter += 1;   // next step draws fresh Philox noise
   }
 }

@@ -149,6 +149,12 @@ class MPPISearcher:  # types.jl:46-50
         self._check(self._lib.mppi_get_timings(self._h, us))
         return list(us)
 
+    def phase_clocks(self):
+        """clock64 stamps at the phase boundaries of the last finalize kernel (diagnostics)."""
+        ck = (C.c_uint64 * 16)()
+        self._check(self._lib.mppi_get_phase_clocks(self._h, ck))
+        return list(ck)
+
     def launch_count(self):
         return int(self._lib.mppi_launch_count(self._h))
 
@@ -172,7 +178,7 @@ class MPPISearcher:  # types.jl:46-50
         _store(self, res, ctrl, traj)
 
     def set_profiling(self, on):
-        self._check(self._lib.mppi_set_profiling(self._h, 1 if on else 0))
+        self._check(self._lib.mppi_set_profiling(self._h, int(on)))
 
     def measure_fp32_peak(self):
         v = C.c_double(0)

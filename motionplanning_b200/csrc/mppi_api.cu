@@ -89,9 +89,9 @@ int32_t mppi_destroy(mppi_handle_t* h) {
   drop_graphs(h);
   if (h->comm && nccl_api().CommDestroy) nccl_api().CommDestroy(h->comm);
   void* dev[] = {h->d_in, h->d_eps, h->d_costs, h->d_flags, h->d_scratch, h->d_scratch_tmpl, h->d_iter, h->d_Spart,
-                 h->d_eta_part, h->d_partial, h->d_gathered, h->d_res, h->d_cand, h->d_dbg};
+                 h->d_eta_part, h->d_partial, h->d_gathered, h->d_res, h->d_cand, h->d_dbg, h->d_seq};
   for (void* p : dev) if (p) cudaFree(p);
-  void* host[] = {h->h_in, h->h_res, h->h_partial, h->h_gathered};
+  void* host[] = {h->h_in, h->h_res, h->h_partial, h->h_gathered, h->h_seq};
   for (void* p : host) if (p) cudaFreeHost(p);
   for (auto& e : h->ev) if (e) cudaEventDestroy(e);
   if (h->stream) cudaStreamDestroy(h->stream);
@@ -129,8 +129,14 @@ static int create_impl(mppi_handle* h) {
   if (c.planner == MPPI_PLANNER_DWA) MPPI_CUDA(h, cudaMalloc(&h->d_cand, K * 2 * sizeof(double)));
   MPPI_CUDA(h, cudaMalloc(&h->d_dbg, 16 * sizeof(unsigned long long)));
   MPPI_CUDA(h, cudaMemset(h->d_dbg, 0, 16 * sizeof(unsigned long long)));
-  MPPI_CUDA(h, cudaMallocHost(&h->h_in, B * (MPPI_MAX_NX + 2 * N) * sizeof(double)));
-  MPPI_CUDA(h, cudaMallocHost(&h->h_res, (B * (RES_SCALARS + 2 * N) + (N + 1) * c.n_x) * sizeof(double)));
+  // inputs and results are MAPPED pinned memory: for B == 1 the step's kernels read / write them
+  // directly over PCIe (no memcpy nodes in the step graph) and the host spins on h_seq
+  MPPI_CUDA(h, cudaHostAlloc(&h->h_in, B * (MPPI_MAX_NX + 2 * N) * sizeof(double), cudaHostAllocMapped));
+  MPPI_CUDA(h, cudaHostAlloc(&h->h_seq, sizeof(unsigned long long), cudaHostAllocMapped));
+  *h->h_seq = 0;
+  MPPI_CUDA(h, cudaMalloc(&h->d_seq, sizeof(unsigned long long)));
+  MPPI_CUDA(h, cudaMemset(h->d_seq, 0, sizeof(unsigned long long)));
+  MPPI_CUDA(h, cudaHostAlloc(&h->h_res, (B * (RES_SCALARS + 2 * N) + (N + 1) * c.n_x) * sizeof(double), cudaHostAllocMapped));
   h->h_traj = h->h_res + B * (RES_SCALARS + 2 * N);
   MPPI_CUDA(h, cudaMallocHost(&h->h_partial, B * h->plen * sizeof(double)));
   MPPI_CUDA(h, cudaMallocHost(&h->h_gathered, 8 * B * h->plen * sizeof(double)));
@@ -142,6 +148,7 @@ static int create_impl(mppi_handle* h) {
   std::vector<Scratch> tmpl(B);
   for (auto& s : tmpl) { s.rho_key = ~0ull; s.argmin = ~0u; s.feasible_count = 0; s.k_eff = h->K_local; s.pad = 0; }
   MPPI_CUDA(h, cudaMemcpy(h->d_scratch_tmpl, tmpl.data(), B * sizeof(Scratch), cudaMemcpyHostToDevice));
+  MPPI_CUDA(h, cudaMemcpy(h->d_scratch, tmpl.data(), B * sizeof(Scratch), cudaMemcpyHostToDevice));
   MPPI_CUDA(h, cudaMemset(h->d_iter, 0, sizeof(unsigned int)));
   MPPI_CUDA(h, cudaMemset(h->d_res, 0, B * (RES_SCALARS + 2 * N) * sizeof(double)));
   rebuild_params(h);
@@ -165,8 +172,12 @@ int32_t mppi_create(const mppi_config_t* cfg, mppi_handle_t** out) {
   return MPPI_OK;
 }
 
-static int quiesce(mppi_handle* h) {   // pinned inputs are about to change: no step may be in flight
-  if (h->in_flight) { MPPI_CUDA(h, cudaStreamSynchronize(h->stream)); h->in_flight = false; }
+static int quiesce(mppi_handle* h) {   // configuration is about to change: the stream must be idle
+  if (h->in_flight) { MPPI_CUDA(h, cudaStreamSynchronize(h->stream)); h->in_flight = h->inputs_busy = false; }
+  return MPPI_OK;
+}
+static int quiesce_inputs(mppi_handle* h) {   // pinned inputs are about to change: no step may still read them
+  if (h->inputs_busy) { MPPI_CUDA(h, cudaStreamSynchronize(h->stream)); h->in_flight = h->inputs_busy = false; }
   return MPPI_OK;
 }
 
@@ -178,7 +189,7 @@ int32_t mppi_set_x0(mppi_handle_t* h, const double* x0, int32_t n) {
     snprintf(buf, sizeof buf, "Length of X0 (%d) must match number of states (%d)", n, h->cfg.n_x);
     return fail(h, MPPI_EINVAL, buf);
   }
-  int rc = quiesce(h); if (rc) return rc;
+  int rc = quiesce_inputs(h); if (rc) return rc;
   for (int b = 0; b < h->cfg.B; ++b)
     for (int i = 0; i < n; ++i) h->h_in[size_t(b) * MPPI_MAX_NX + i] = x0[size_t(b) * n + i];
   h->x0_dirty = true;   // uploaded by the next step's graph (one H2D node for x0 + U_nom)
@@ -189,7 +200,7 @@ int32_t mppi_set_nominal(mppi_handle_t* h, const double* U, int32_t N, int32_t m
   H_CHECK(h);
   if (!U) return fail(h, MPPI_EINVAL, "null U");
   if (N != h->cfg.N || m != h->cfg.m) return fail(h, MPPI_EINVAL, "NominalControl must be N x numControls");
-  int rc = quiesce(h); if (rc) return rc;
+  int rc = quiesce_inputs(h); if (rc) return rc;
   const size_t B = h->cfg.B, off = B * MPPI_MAX_NX, n = B * 2 * N;
   memcpy(h->h_in + off, U, n * sizeof(double));
   h->u_dirty = true;

@@ -47,7 +47,7 @@ struct StaticParams {
   R blk[MPPI_MAX_BLOCKS][6];    // cx, cy, cos(psi), sin(psi), half_len, half_wid
 };
 
-// per-instance scratch, reset from a template by one D2D copy at the head of a step
+// per-instance scratch; initialised at create and re-armed by finalize once it has been consumed
 struct Scratch {
   unsigned long long rho_key;  // atomicMin: FP32 (ordered cost bits << 32 | local k); FP64 ordered cost bits
   unsigned int argmin;         // FP64 path / cut-off path: min local k with cost == rho
@@ -79,6 +79,9 @@ struct Buffers {
   double* res_control;  // [B][2*N]  col-major N x m
   double* res_traj;     // [B][(N+1)*n_x] col-major (N+1) x n_x
   const double* cand;   // DWA: [K][2] col-major K x m candidates
+  double* host_res;         // mapped pinned host mirror of the result block (B == 1), or nullptr
+  unsigned long long* seq;  // device count of completed steps
+  volatile unsigned long long* host_seq;  // mapped pinned host copy of *seq: the completion flag the host spins on
   unsigned long long* dbg;  // [16] SM-clock stamps at the phase boundaries of finalize (instance 0)
   int ksplit;
   int n_ranks;

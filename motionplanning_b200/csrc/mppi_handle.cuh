@@ -68,6 +68,9 @@ struct mppi_handle {
   double* d_traj = nullptr;      // [B][(N+1)*n_x], inside the d_res allocation
   double* d_cand = nullptr;      // DWA candidates K x 2 col-major
   unsigned long long* d_dbg = nullptr;   // [16] finalize phase clocks
+  unsigned long long* d_seq = nullptr;   // completed-step counter
+  unsigned long long* h_seq = nullptr;   // mapped pinned: completion flag written by finalize
+  unsigned long long seq_launched = 0;   // steps (finalize<COMBINE>) enqueued so far
   // pinned host mirrors
   double* h_in = nullptr;
   double* h_res = nullptr;
@@ -88,8 +91,10 @@ struct mppi_handle {
   float us[4] = {0, 0, 0, 0};
   int64_t launches = 0;
   bool stepped = false;
+  bool timings_pending = false;   // events of the last step not yet read back
   bool x0_dirty = false, u_dirty = false;   // pinned x0 / U_nom changed since the last upload
   bool in_flight = false;   // work enqueued on the stream and not yet synchronised
+  bool inputs_busy = false; // a step that reads the pinned input block may not have consumed it yet
   bool have_candidates = false;
 };
 
@@ -173,6 +178,9 @@ Buffers<R> make_buffers(const mppi_handle* h) {
   b.res_traj = h->d_traj;
   b.cand = h->d_cand;
   b.dbg = h->d_dbg;
+  b.host_res = nullptr;
+  b.seq = h->d_seq;
+  b.host_seq = h->h_seq;
   b.ksplit = h->ksplit;
   b.n_ranks = h->n_ranks;
   return b;

@@ -57,6 +57,12 @@ __device__ __forceinline__ double key_cost(unsigned long long key, double) { ret
 // Schedule (MPPIUtils.jl:39-53): states x_1..x_N are each tested once against
 // obstacles and bounds (x_0 never is); stage cost is taken at the pre-step state.
 // ---------------------------------------------------------------------------
+// Step prologue for B == 1: pull the caller's x0 / U_nom (mapped pinned host memory, read over
+// PCIe by one small CTA) into the device input block.  Replaces an H2D memcpy node in the graph.
+__global__ void __launch_bounds__(128) begin_kernel(const double* __restrict__ host_in, double* __restrict__ dev_in, int first, int count) {
+  for (int i = threadIdx.x; i < count; i += 128) dev_in[first + i] = host_in[first + i];
+}
+
 // Per-sample accumulators of the rollout (registers).
 template <class R>
 struct RolloutAcc {

@@ -19,7 +19,8 @@ enum {
   V_D2H_RES = 256,
   V_FUSED_FINAL = 512,  // finalize<PH_PARTIAL|PH_COMBINE> in one kernel (single rank)
   V_H2D_X0 = 1024,      // pinned x0 only -> device
-  V_H2D_U = 2048        // pinned U_nom only -> device
+  V_H2D_U = 2048,       // pinned U_nom only -> device
+  V_HOST_RES = 4096     // B == 1: finalize writes the result block to mapped host memory (no D2H node)
 };
 
 template <class R> const StaticParams<R>& params_of(const mppi_handle* h);
@@ -33,21 +34,27 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   if (v & V_FUSED_FINAL) { buf.gathered = buf.partial; buf.n_ranks = 1; }   // single rank: combine reads its own partial
   const int B = h->cfg.B, N = h->cfg.N, K = h->K_local, nx = h->cfg.n_x;
   cudaStream_t s = h->stream;
+  if ((v & V_HOST_RES) && B == 1) buf.host_res = h->h_res;
   const size_t in_bytes = size_t(B) * (MPPI_MAX_NX + 2 * N) * sizeof(double);
   const size_t res_bytes = size_t(B) * (RES_SCALARS + 2 * N) * sizeof(double);
   const size_t smemU = size_t(N) * 4 * sizeof(R);
 
   if (timed == 1) MPPI_CUDA(h, cudaEventRecord(h->ev[0], s));
-  if (v & V_H2D_IN) MPPI_CUDA(h, cudaMemcpyAsync(h->d_in, h->h_in, in_bytes, cudaMemcpyHostToDevice, s));
-  if (v & V_H2D_X0) MPPI_CUDA(h, cudaMemcpyAsync(h->d_in, h->h_in, size_t(B) * MPPI_MAX_NX * sizeof(double), cudaMemcpyHostToDevice, s));
-  if (v & V_H2D_U)
-    MPPI_CUDA(h, cudaMemcpyAsync(h->d_in + size_t(B) * MPPI_MAX_NX, h->h_in + size_t(B) * MPPI_MAX_NX,
-                                 size_t(B) * 2 * N * sizeof(double), cudaMemcpyHostToDevice, s));
+  if (v & (V_H2D_IN | V_H2D_X0 | V_H2D_U)) {
+    const int nx0 = B * MPPI_MAX_NX, nU = B * 2 * N;
+    const int first = (v & V_H2D_U) ? nx0 : 0;
+    const int count = (v & V_H2D_IN) ? nx0 + nU : ((v & V_H2D_X0) ? nx0 : nU);
+    if (B == 1) {   // one small kernel reading the mapped host block: cheaper than a memcpy node
+      begin_kernel<<<1, 128, 0, s>>>(h->h_in, h->d_in, first, count);
+      h->launches++;
+    } else {
+      MPPI_CUDA(h, cudaMemcpyAsync(h->d_in + first, h->h_in + first, size_t(count) * sizeof(double), cudaMemcpyHostToDevice, s));
+    }
+  }
   if (v & V_ADOPT)
     MPPI_CUDA(h, cudaMemcpyAsync(h->d_in + size_t(B) * MPPI_MAX_NX, h->d_res + size_t(B) * RES_SCALARS,
                                  size_t(B) * 2 * N * sizeof(double), cudaMemcpyDeviceToDevice, s));
   if (v & V_LOCAL) {
-    MPPI_CUDA(h, cudaMemcpyAsync(h->d_scratch, h->d_scratch_tmpl, size_t(B) * sizeof(Scratch), cudaMemcpyDeviceToDevice, s));
     dim3 grid((K + ROLLOUT_BS - 1) / ROLLOUT_BS, B);
     rollout_kernel<R, Model, SRC><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
     h->launches++;
@@ -123,6 +130,7 @@ inline int enqueue(mppi_handle* h, int v, int timed) {
 inline int kernels_in(const mppi_handle* h, int v) {
   int n = 0;
   const bool dwa = h->cfg.planner == MPPI_PLANNER_DWA;
+  if ((v & (V_H2D_IN | V_H2D_X0 | V_H2D_U)) && h->cfg.B == 1) n++;
   if (v & V_LOCAL) n += 1 + ((h->cutoff && !dwa) ? 1 : 0) + (dwa ? 0 : 1);
   if (v & V_FUSED_FINAL) n++;
   if (v & V_PARTIAL) n++;
@@ -137,11 +145,36 @@ inline int take_dirty(mppi_handle* h) {
   return v;
 }
 
+// Wait for the step whose finalize carries sequence number seq_launched.  B == 1: spin on the
+// mapped completion flag (the result block is already in host memory when it flips), checking
+// the stream now and then so that a faulted launch cannot hang the caller.  Otherwise: stream sync.
+inline int wait_step(mppi_handle* h, bool flag_ok) {
+  if (flag_ok && h->cfg.B == 1) {
+    volatile unsigned long long* f = h->h_seq;
+    for (unsigned spins = 1;; ++spins) {
+      if (*f >= h->seq_launched) { h->timings_pending = true; h->inputs_busy = false; return MPPI_OK; }
+      if ((spins & 0x3FFF) == 0) {
+        const cudaError_t e = cudaStreamQuery(h->stream);
+        if (e == cudaSuccess) break;          // everything retired: fall through to the sync below
+        if (e != cudaErrorNotReady) { h->err = std::string("step failed: ") + cudaGetErrorString(e); return MPPI_ECUDA; }
+      }
+#if defined(__x86_64__)
+      __builtin_ia32_pause();
+#endif
+    }
+  }
+  MPPI_CUDA(h, cudaStreamSynchronize(h->stream));
+  h->in_flight = h->inputs_busy = false;
+  h->timings_pending = true;
+  return MPPI_OK;
+}
+
 // run a variant: graph replay (captured on first use) or eager when profiling / graphs are off
 inline int run_variant(mppi_handle* h, int v) {
   const bool use_graph = h->cfg.use_cuda_graph && h->profiling != 1;
   if (!use_graph) {
-    h->in_flight = true;
+    h->in_flight = h->inputs_busy = true;
+    if (v & (V_COMBINE | V_FUSED_FINAL)) h->seq_launched++;
     return enqueue(h, v & 0xFFFF, h->profiling ? 1 : 0);
   }
   const bool inner = h->profiling == 2;
@@ -168,7 +201,8 @@ inline int run_variant(mppi_handle* h, int v) {
   MPPI_CUDA(h, cudaGraphLaunch(it->second, h->stream));
   MPPI_CUDA(h, cudaEventRecord(h->ev[4], h->stream));
   h->launches += kernels_in(h, v & 0xFFFF);
-  h->in_flight = true;
+  if (v & (V_COMBINE | V_FUSED_FINAL)) h->seq_launched++;
+  h->in_flight = h->inputs_busy = true;
   return MPPI_OK;
 }
 

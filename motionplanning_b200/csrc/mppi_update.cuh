@@ -204,6 +204,11 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
       }
     }
     __syncthreads();   // block-scope visibility of `part` for the combine phase (G == 1)
+    if (t == 0) {      // this phase is the last consumer of the scratch: re-arm it for the next step
+      Scratch fresh;
+      fresh.rho_key = ~0ull; fresh.argmin = ~0u; fresh.feasible_count = 0; fresh.k_eff = p.K_local; fresh.pad = 0;
+      buf.scratch[b] = fresh;
+    }
   }
   MPPI_STAMP(1);
   if (!(PHASES & PH_COMBINE)) return;
@@ -329,6 +334,22 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
     rs[RES_FLAGS] = double((feas ? MPPI_FLAG_FEASIBLE : 0) | (hits ? MPPI_FLAG_COLLIDED : 0) | ((viol > R(0)) ? MPPI_FLAG_OOB : 0));
     MPPI_STAMP(6);
     if (b == 0) *buf.iter += 1;   // next step draws fresh Philox noise
+  }
+  if (p.B == 1) {
+    // Results go straight to the caller-visible mapped host block (posted PCIe writes, no D2H
+    // memcpy node); the host spins on host_seq instead of a stream synchronise.
+    __syncthreads();
+    if (buf.host_res) {
+      const int n_res = RES_SCALARS + 2 * N + (N + 1) * NX;   // scalars | U_new | nominal trajectory, contiguous
+      for (int i = t; i < n_res; i += FINAL_BS) buf.host_res[i] = buf.res_scalars[i];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (t == 0) {
+      const unsigned long long done = *buf.seq + 1ull;
+      *buf.seq = done;
+      *buf.host_seq = done;
+    }
   }
 }
 

@@ -16,3 +16,20 @@ for mode in (0,1):
         mp.step_async(); mp.sync(); ts.append(mp.timings_us())
     print('mode',mode,np.median(np.array(ts[5:]),axis=0))
 ck=mp.phase_clocks(); print('finalize phase cycles', [ck[i+1]-ck[i] for i in range(6)], 'total', ck[6]-ck[0])
+
+# ---- host-side cost of the three reference-facing calls (main.jl:59-61) ----
+import time
+mp.set_profiling(0)
+x = np.array(mp.s.X0, dtype=np.float64); U = np.array(mp.r.Control, copy=True)
+T = {k: [] for k in ("shift", "nominal", "plan", "raw_step")}
+for i in range(300):
+    t0 = time.perf_counter(); m.ShiftInitialCondition(mp, x)
+    t1 = time.perf_counter(); m.defineMPPINominalControl(mp, U)
+    t2 = time.perf_counter(); m.MPPIPlan(mp)
+    t3 = time.perf_counter()
+    T["shift"].append(t1 - t0); T["nominal"].append(t2 - t1); T["plan"].append(t3 - t2)
+import ctypes as C
+res = capi.Result()
+for i in range(300):
+    t0 = time.perf_counter(); mp._lib.mppi_step(mp._h, None, C.byref(res)); T["raw_step"].append(time.perf_counter() - t0)
+print({k: round(float(np.median(v[50:])) * 1e6, 2) for k, v in T.items()}, "device us", mp.timings_us()[3])

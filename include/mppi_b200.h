@@ -216,7 +216,10 @@ int32_t mppi_get_timings(mppi_handle_t* h, float us[4]);
  * [0] entry, [1] partials reduced, [2] ranks combined, [3] U_new ready, [4] nominal state
  * recurrence done, [5] states costed, [6] result written.  Diagnostics only. */
 int32_t mppi_get_phase_clocks(mppi_handle_t* h, uint64_t clocks[16]);
-/* toggle per-kernel event timing (eager launches bracketed by events; no graph replay) */
+/* per-kernel timing: 0 off; 1 eager launches bracketed by CUDA events (no graph replay);
+ * 2 graph replay in which every kernel stamps %globaltimer (ns) at its first CTA's start and last
+ * CTA's end into the phase-clock block: clocks[8+2i], clocks[9+2i] for i = rollout, update,
+ * finalize.  Re-arm with mppi_set_profiling(h, 2) before each traced step. */
 int32_t mppi_set_profiling(mppi_handle_t* h, int32_t on);
 /* number of kernels the library launched on this handle so far */
 int64_t mppi_launch_count(const mppi_handle_t* h);

@@ -85,6 +85,7 @@ struct Buffers {
   unsigned long long* dbg;  // [16] SM-clock stamps at the phase boundaries of finalize (instance 0)
   int ksplit;
   int n_ranks;
+  int trace;            // 1: kernels stamp %globaltimer at first-CTA start / last-CTA end into dbg[8..]
 };
 
 // ---------------------------------------------------------------------------
@@ -126,6 +127,19 @@ struct HotParams {
 // ---------------------------------------------------------------------------
 // math traits
 // ---------------------------------------------------------------------------
+// kernel span tracing (profiling mode 2): dbg[8 + 2*slot] = min start, dbg[9 + 2*slot] = max end, in ns
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void trace_begin(unsigned long long* dbg, int trace, int slot) {
+  if (trace && threadIdx.x == 0) atomicMin(&dbg[8 + 2 * slot], globaltimer_ns());
+}
+__device__ __forceinline__ void trace_end(unsigned long long* dbg, int trace, int slot) {
+  if (trace && threadIdx.x == 0) atomicMax(&dbg[9 + 2 * slot], globaltimer_ns());
+}
+
 template <class R> struct Math;
 
 template <> struct Math<float> {

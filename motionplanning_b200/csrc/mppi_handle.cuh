@@ -87,7 +87,7 @@ struct mppi_handle {
   int rank = 0, n_ranks = 1;
   // profiling
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
-  int profiling = 0;   // 0 off | 1 eager launches bracketed by events | 2 graph replay with event-record nodes
+  int profiling = 0;   // 0 off | 1 eager launches bracketed by events | 2 graph replay, kernels stamp %globaltimer
   float us[4] = {0, 0, 0, 0};
   int64_t launches = 0;
   bool stepped = false;
@@ -183,6 +183,7 @@ Buffers<R> make_buffers(const mppi_handle* h) {
   b.host_seq = h->h_seq;
   b.ksplit = h->ksplit;
   b.n_ranks = h->n_ranks;
+  b.trace = h->profiling == 2 ? 1 : 0;
   return b;
 }
 

@@ -155,6 +155,7 @@ rollout_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) 
   const int b = blockIdx.y;
   const int N = p.N;
   const int k = blockIdx.x * ROLLOUT_BS + threadIdx.x;
+  trace_begin(buf.dbg, buf.trace, 0);
   if (threadIdx.x == ROLLOUT_BS - 1) sHot.fill(p);
   const bool active = k < p.K_local;
   const double* Ub = buf.U + size_t(b) * 2 * N;
@@ -206,6 +207,7 @@ rollout_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) 
     atomicMin(&buf.scratch[b].rho_key, key);
     if (f) atomicAdd(&buf.scratch[b].feasible_count, f);
   }
+  trace_end(buf.dbg, buf.trace, 0);
 }
 
 // ---------------------------------------------------------------------------

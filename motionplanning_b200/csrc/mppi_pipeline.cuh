@@ -177,8 +177,8 @@ inline int run_variant(mppi_handle* h, int v) {
     if (v & (V_COMBINE | V_FUSED_FINAL)) h->seq_launched++;
     return enqueue(h, v & 0xFFFF, h->profiling ? 1 : 0);
   }
-  const bool inner = h->profiling == 2;
-  if (inner) v |= 1 << 24;   // graphs with event-record nodes are cached separately
+  const bool inner = false;
+  if (h->profiling == 2) v |= 1 << 24;   // graphs whose kernels trace %globaltimer are cached separately
   auto it = h->graphs.find(v);
   if (it == h->graphs.end()) {
     cudaGraph_t g = nullptr;

@@ -36,6 +36,7 @@ template <class R>
 __global__ void __launch_bounds__(UPDATE_BS) update_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) {
   __shared__ R s_red[UPDATE_BS / 32][2 * UPDATE_JG + 1];
   const int b = blockIdx.z, N = p.N, K = p.K_local;
+  trace_begin(buf.dbg, buf.trace, 1);
   const int j0 = blockIdx.y * UPDATE_JG;
   const Scratch sc = buf.scratch[b];
   const int keff = sc.k_eff;
@@ -111,6 +112,7 @@ __global__ void __launch_bounds__(UPDATE_BS) update_kernel(const __grid_constant
       if (j < N) buf.Spart[((size_t(b) * gridDim.x + blockIdx.x) * N + j) * 2 + (threadIdx.x & 1)] = s;
     }
   }
+  trace_end(buf.dbg, buf.trace, 1);
 }
 
 // ---------------------------------------------------------------------------
@@ -136,6 +138,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
   const int plen = PART_HDR + 2 * N;
   double* part = buf.partial + size_t(b) * plen;
   MPPI_STAMP(0);
+  trace_begin(buf.dbg, buf.trace, 2);
   const Scratch sc = buf.scratch[b];
 
   if (PHASES & PH_PARTIAL) {
@@ -351,6 +354,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
       *buf.host_seq = done;
     }
   }
+  trace_end(buf.dbg, buf.trace, 2);
 }
 
 }  // namespace mppi

@@ -15,6 +15,13 @@ for mode in (0,1):
     for _ in range(30):
         mp.step_async(); mp.sync(); ts.append(mp.timings_us())
     print('mode',mode,np.median(np.array(ts[5:]),axis=0))
+mp.set_profiling(2); mp.step_async(); mp.sync()   # first traced replay captures the graph
+spans=[]
+for _ in range(20):
+    mp.set_profiling(2); mp.step_async(); mp.sync(); c=mp.phase_clocks()
+    t0=c[8]; spans.append([(c[8+2*i]-t0, c[9+2*i]-t0) for i in range(3)])
+print('in-graph spans ns (start,end) rollout/update/finalize, median:', np.median(np.array(spans),axis=0).tolist())
+mp.set_profiling(0)
 ck=mp.phase_clocks(); print('finalize phase cycles', [ck[i+1]-ck[i] for i in range(6)], 'total', ck[6]-ck[0])
 
 # ---- host-side cost of the three reference-facing calls (main.jl:59-61) ----

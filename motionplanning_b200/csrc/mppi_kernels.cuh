@@ -112,21 +112,28 @@ __device__ __forceinline__ void rollout_horizon(const StaticParams<R>& p, const 
     // is kept for the update kernel / oracle replay
     const R L00 = hp.L00, L10 = hp.L10, L11 = hp.L11;
     const uint32_t gk = uint32_t(p.k_offset + k), iter = *buf.iter;
-    for (int j = 0; j < N; j += 2) {
+    // software pipeline: the noise of pair j+2 is generated while pair j integrates, so the
+    // integer Philox rounds and the MUFU work of Box-Muller fill the FP32 recurrence's issue gaps
+    auto draw = [&](int j, R2& ea, R2& eb) {
       const uint4 rnd = philox4x32_10(make_uint4(gk, uint32_t(j >> 1), iter, uint32_t(b)), hp.key);
       float z0, z1;
       box_muller(rnd.x, rnd.y, &z0, &z1);
-      R2 e;
-      e.x = L00 * R(z0);
-      e.y = L10 * R(z0) + L11 * R(z1);
-      *eps = e;
-      advance(nu_p[j], e);
+      ea.x = L00 * R(z0);
+      ea.y = L10 * R(z0) + L11 * R(z1);
+      box_muller(rnd.z, rnd.w, &z0, &z1);
+      eb.x = L00 * R(z0);
+      eb.y = L10 * R(z0) + L11 * R(z1);
+    };
+    R2 na, nb;
+    draw(0, na, nb);
+    for (int j = 0; j < N; j += 2) {
+      const R2 ea = na, eb = nb;
+      if (j + 2 < N) draw(j + 2, na, nb);
+      *eps = ea;
+      advance(nu_p[j], ea);
       if (j + 1 < N) {
-        box_muller(rnd.z, rnd.w, &z0, &z1);
-        e.x = L00 * R(z0);
-        e.y = L10 * R(z0) + L11 * R(z1);
-        eps[estride] = e;
-        advance(nu_p[j + 1], e);
+        eps[estride] = eb;
+        advance(nu_p[j + 1], eb);
       }
       eps += 2 * estride;
     }

@@ -18,6 +18,13 @@
 
 namespace mppi {
 
+template <class R> struct Vec2;
+template <> struct Vec2<float> { using type = float2; };
+template <> struct Vec2<double> { using type = double2; };
+template <class R> struct Vec4;
+template <> struct Vec4<float> { using type = float4; };
+template <> struct Vec4<double> { using type = double4; };
+
 // ---------------------------------------------------------------------------
 // Static parameters: passed BY VALUE as a __grid_constant__ kernel argument, so
 // every field is a constant-bank operand (no load instruction, warp-uniform).
@@ -44,7 +51,8 @@ struct StaticParams {
   R w[6];                     // stage cost weights v2, r2, ax2, sr2, sa2, y2
   R veh_off, veh_hl, veh_hw;  // rectangle: centre offset, half length, half width
   R circ[MPPI_MAX_CIRCLES][3];  // x, y, r^2
-  R blk[MPPI_MAX_BLOCKS][6];    // cx, cy, cos(psi), sin(psi), half_len, half_wid
+  R blk_all[4];                 // bounding circle of ALL walls: cx, cy, broad-phase d^2, pad
+  R blk[MPPI_MAX_BLOCKS][8];    // cx, cy, cos(psi), sin(psi), half_len, half_wid, broad-phase d^2, pad
 };
 
 // per-instance scratch; initialised at create and re-armed by finalize once it has been consumed
@@ -106,6 +114,8 @@ struct HotParams {
   R XL[NX], XU[NX], CL[2], CU[2], w[6];
   R la, lb, mass, Izz, mu, KFZX, FZF0, FZR0, tireB, tireC, tireD, tireE;
   R L00, L10, L11;
+  R veh_off, veh_hl, veh_hw;
+  R blk_all[4];
   R circ[HOT_CIRCLES][3];
   uint32_t key[20];   // Philox round keys
   __device__ __forceinline__ void fill(const StaticParams<R>& p) {
@@ -117,6 +127,8 @@ struct HotParams {
     FZF0 = p.FZF0; FZR0 = p.FZR0;
     tireB = p.tireB; tireC = p.tireC; tireD = p.tireD; tireE = p.tireE;
     L00 = p.L00; L10 = p.L10; L11 = p.L11;
+    veh_off = p.veh_off; veh_hl = p.veh_hl; veh_hw = p.veh_hw;
+    for (int i = 0; i < 4; ++i) blk_all[i] = p.blk_all[i];
     for (int o = 0; o < HOT_CIRCLES; ++o)
       for (int c = 0; c < 3; ++c) circ[o][c] = p.circ[o][c];
     uint32_t k0 = p.seed_lo, k1 = p.seed_hi;
@@ -151,6 +163,7 @@ template <> struct Math<float> {
   // division by a parameter whose reciprocal was taken on the host
   static __device__ __forceinline__ float over(float a, float, float inv_b) { return a * inv_b; }
   static __device__ __forceinline__ float exp(float x) { return __expf(x); }
+  static __device__ __forceinline__ float fma(float a, float b, float c) { return fmaf(a, b, c); }
   static __device__ __forceinline__ float sin(float x) { return __sinf(x); }
   static __device__ __forceinline__ float fabs(float x) { return fabsf(x); }
   static __device__ __forceinline__ float fmax(float a, float b) { return fmaxf(a, b); }
@@ -175,14 +188,35 @@ template <> struct Math<float> {
     r = big ? (1.57079632679f - r) : r;
     return copysignf(r, x);
   }
+  // atan(n/d) with ONE reciprocal: reduce on max(|n|,|d|) directly instead of dividing first and
+  // taking a second reciprocal when |n/d| > 1.  Sign = sign(n) xor sign(d), as for atan(n/d).
+  static __device__ __forceinline__ float atan_ratio(float n, float d) {
+    const float an = fabsf(n), ad = fabsf(d);
+    const bool big = an > ad;
+    const float z = __fdividef(fminf(an, ad), fmaxf(an, ad));
+    const float z2 = z * z;
+    float p = -0.004054558929055929f;
+    p = fmaf(p, z2, 0.021862929686903954f);
+    p = fmaf(p, z2, -0.05591228976845741f);
+    p = fmaf(p, z2, 0.09642194956541061f);
+    p = fmaf(p, z2, -0.1390862911939621f);
+    p = fmaf(p, z2, 0.19946566224098206f);
+    p = fmaf(p, z2, -0.33329859375953674f);
+    p = fmaf(p, z2, 0.9999993443489075f);
+    float r = p * z;
+    r = big ? (1.57079632679f - r) : r;
+    return __uint_as_float(__float_as_uint(r) | ((__float_as_uint(n) ^ __float_as_uint(d)) & 0x80000000u));
+  }
 };
 
 template <> struct Math<double> {
+  static __device__ __forceinline__ double atan_ratio(double n, double d) { return ::atan(n / d); }
   static __device__ __forceinline__ void sincos(double x, double* s, double* c) { ::sincos(x, s, c); }
   static __device__ __forceinline__ double tan(double x) { return ::tan(x); }
   static __device__ __forceinline__ double div(double a, double b) { return a / b; }
   static __device__ __forceinline__ double over(double a, double b, double) { return a / b; }
   static __device__ __forceinline__ double exp(double x) { return ::exp(x); }
+  static __device__ __forceinline__ double fma(double a, double b, double c) { return ::fma(a, b, c); }
   static __device__ __forceinline__ double sin(double x) { return ::sin(x); }
   static __device__ __forceinline__ double atan(double x) { return ::atan(x); }
   static __device__ __forceinline__ double fabs(double x) { return ::fabs(x); }

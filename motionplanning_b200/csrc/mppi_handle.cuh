@@ -4,6 +4,7 @@
 #include <dlfcn.h>
 #include <nccl.h>   // declarations only; symbols are resolved with dlsym at mppi_comm_init
 
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -144,11 +145,27 @@ void build_params(const mppi_handle* h, StaticParams<R>* p) {
   for (int o = p->n_circles; o < ((p->n_circles + 3) & ~3) && o < MPPI_MAX_CIRCLES; ++o) {
     p->circ[o][0] = R(0); p->circ[o][1] = R(0); p->circ[o][2] = R(-1);   // padding: d^2 <= -1 never holds
   }
+  {  // one bounding circle around every wall: a single test per pose culls the whole table
+    double cx = 0, cy = 0, Rc = 0;
+    for (int b = 0; b < p->n_blocks; ++b) { cx += h->blocks[5 * b] / p->n_blocks; cy += h->blocks[5 * b + 1] / p->n_blocks; }
+    for (int b = 0; b < p->n_blocks; ++b) {
+      const double* bl = &h->blocks[5 * b];
+      Rc = std::max(Rc, std::hypot(bl[0] - cx, bl[1] - cy) + std::hypot(bl[3], bl[4]));
+    }
+    const double Rv = std::hypot(c.veh_L / 2, c.veh_W / 2);
+    p->blk_all[0] = R(cx); p->blk_all[1] = R(cy); p->blk_all[2] = R(2.0 * (Rv + Rc) * (Rv + Rc) * (1.0 + 1e-5)); p->blk_all[3] = R(0);
+  }
   for (int b = 0; b < p->n_blocks; ++b) {
     const double* bl = &h->blocks[5 * b];
     p->blk[b][0] = R(bl[0]); p->blk[b][1] = R(bl[1]);
     p->blk[b][2] = R(std::cos(bl[2])); p->blk[b][3] = R(std::sin(bl[2]));
     p->blk[b][4] = R(bl[3]); p->blk[b][5] = R(bl[4]);
+    // broad phase: with centre distance d, max(|d.n1|, |d.n2|) >= d/sqrt(2) for either rectangle's
+    // orthonormal axes and every projection radius is <= the bounding-circle radius, so
+    // d^2 >= 2 (R_veh + R_wall)^2 guarantees a separating axis among BOTH axis pairs (= free
+    // under the reference's ConvexCollision semantics).  1e-5 covers the FP32 rounding of d^2.
+    const double Rv = std::hypot(c.veh_L / 2, c.veh_W / 2), Rw = std::hypot(bl[3], bl[4]);
+    p->blk[b][6] = R(2.0 * (Rv + Rw) * (Rv + Rw) * (1.0 + 1e-5)); p->blk[b][7] = R(0);
   }
 }
 

@@ -16,12 +16,6 @@ constexpr int UPDATE_JG = 4;
 constexpr int FINAL_BS = 256;
 constexpr int CUTOFF_BS = 1024;
 
-template <class R> struct Vec2;
-template <> struct Vec2<float> { using type = float2; };
-template <> struct Vec2<double> { using type = double2; };
-template <class R> struct Vec4;
-template <> struct Vec4<float> { using type = float4; };
-template <> struct Vec4<double> { using type = double4; };
 
 __device__ __forceinline__ unsigned long long shfl_xor_u64(unsigned long long v, int m) {
   return __shfl_xor_sync(0xffffffffu, v, m);
@@ -76,7 +70,7 @@ struct RolloutAcc {
 template <class R, class Model, int SRC, int NQ>
 __device__ __forceinline__ void rollout_horizon(const StaticParams<R>& p, const Buffers<R>& buf, Model& veh,
                                                 RolloutAcc<R>& acc, const HotParams<R, Model::NX>* sHot,
-                                                const R* sU, int b, int k) {
+                                                const R* sU, const R* sBlk, int b, int k) {
   using R2 = typename Vec2<R>::type;
   using R4 = typename Vec4<R>::type;
   const int N = p.N;
@@ -104,7 +98,7 @@ __device__ __forceinline__ void rollout_horizon(const StaticParams<R>& p, const 
     veh.step(hp, u0, u1);                          // Rungekutta2 (:76-90)
     if (NQ >= 0) acc.hits += circle_hits_regs<R, (NQ > 0 ? NQ : 0)>(hp, veh.s[0], veh.s[1]);   // x_{j+1}: ObstacleEvaluation
     else acc.hits += circle_hits(p, veh.s[0], veh.s[1]);
-    if (walls) acc.hits += block_hits(p, veh.s[0], veh.s[1], veh.sn, veh.cs);
+    if (walls) acc.hits += block_hits<R>(hp, hp.blk_all, sBlk, p.n_blocks, veh.s[0], veh.s[1], veh.sn, veh.cs);
     acc.viol += bound_violation<R, Model::NX>(hp, veh.s);                 // BoundEvaluation
   };
   if (SRC == SRC_PHILOX) {
@@ -155,6 +149,7 @@ __global__ void __launch_bounds__(ROLLOUT_BS)
 rollout_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   R* sU = reinterpret_cast<R*>(smem_raw);  // [N][4]: u0, u1, g0, g1
+  R* sBlk = sU + 4 * p.N;                  // [n_blocks][8]: wall table
   __shared__ unsigned long long s_key[ROLLOUT_BS / 32];
   __shared__ int s_feas[ROLLOUT_BS / 32];
   __shared__ __align__(16) HotParams<R, Model::NX> sHot;
@@ -164,6 +159,7 @@ rollout_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) 
   const int k = blockIdx.x * ROLLOUT_BS + threadIdx.x;
   trace_begin(buf.dbg, buf.trace, 0);
   if (threadIdx.x == ROLLOUT_BS - 1) sHot.fill(p);
+  for (int i = threadIdx.x; i < 8 * p.n_blocks; i += ROLLOUT_BS) sBlk[i] = (&p.blk[0][0])[i];
   const bool active = k < p.K_local;
   const double* Ub = buf.U + size_t(b) * 2 * N;
   if (SRC != SRC_DWA) {
@@ -186,11 +182,11 @@ rollout_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) 
     const R gx0 = veh.s[0] - p.goal[0], gy0 = veh.s[1] - p.goal[1];
     const R d0 = gx0 * gx0 + gy0 * gy0;
     const int nq = (p.n_circles + 3) >> 2;   // warp-uniform: the whole horizon loop is specialised
-    if (sizeof(R) == 8) rollout_horizon<R, Model, SRC, -1>(p, buf, veh, acc, &sHot, sU, b, k);
-    else if (nq == 0) rollout_horizon<R, Model, SRC, 0>(p, buf, veh, acc, &sHot, sU, b, k);
-    else if (nq == 1) rollout_horizon<R, Model, SRC, 1>(p, buf, veh, acc, &sHot, sU, b, k);
-    else if (nq == 2) rollout_horizon<R, Model, SRC, 2>(p, buf, veh, acc, &sHot, sU, b, k);
-    else rollout_horizon<R, Model, SRC, -1>(p, buf, veh, acc, &sHot, sU, b, k);
+    if (sizeof(R) == 8) rollout_horizon<R, Model, SRC, -1>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
+    else if (nq == 0) rollout_horizon<R, Model, SRC, 0>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
+    else if (nq == 1) rollout_horizon<R, Model, SRC, 1>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
+    else if (nq == 2) rollout_horizon<R, Model, SRC, 2>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
+    else rollout_horizon<R, Model, SRC, -1>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
     acc.stage += veh.stage_cost(p, R(0), R(0));      // terminal slot: VehicleDynamics(x_N, [0,0]) (:49,:53)
     const R gx = veh.s[0] - p.goal[0], gy = veh.s[1] - p.goal[1];
     const R term = Math<R>::div(gx * gx + gy * gy, d0) * p.term_scale;   // (:54)

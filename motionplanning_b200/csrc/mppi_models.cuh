@@ -92,8 +92,8 @@ struct Dyn7 {
     const R FZF = R(2) * (p.FZF0 - t * p.KFZX);                              // :30
     const R FZR = R(2) * (p.FZR0 + t * p.KFZX);                              // :31
     const R den = ux + R(0.01);
-    const R alpha_f = Math<R>::atan(Math<R>::div(v + p.la * r, den)) - sa;   // :32
-    const R alpha_r = Math<R>::atan(Math<R>::div(v - p.lb * r, den));        // :33
+    const R alpha_f = Math<R>::atan_ratio(v + p.la * r, den) - sa;           // :32
+    const R alpha_r = Math<R>::atan_ratio(v - p.lb * r, den);                // :33
     const R FY1 = tyre(p, FZF, alpha_f);
     const R FY2 = tyre(p, FZR, alpha_r);
     const R uxc = ux <= R(0) ? R(0) : ux;                                    // :40-42
@@ -178,22 +178,54 @@ __device__ __forceinline__ int circle_hits(const StaticParams<R>& p, R x, R y) {
 // 4 x 10 x 2 projections collapse to 4 dot products and 4 interval tests.
 // Vehicle rectangle (hybrid_astar_utils.jl:193): centre = (x, y) + off*(cosψ, sinψ),
 // half extents (hl, hw); modπ(ψ) leaves cosψ/sinψ unchanged.
-template <class R>
-__device__ __forceinline__ int block_hits(const StaticParams<R>& p, R x, R y, R sn, R cs) {
+// Broad phase voted across the warp (samples of a warp share x0 and differ only by noise, so
+// whole warps skip): one bounding circle around all walls, then per wall when there are many;
+// then the exact test.
+// `tbl` is the wall table [n][8] (cx, cy, cosΨ, sinΨ, half_len, half_wid, broad-phase d², pad):
+// the kernel parameter itself, or — in the rollout kernel — a shared-memory copy read as two
+// broadcast 128-bit loads per wall (a parameter table indexed by a loop counter costs an LDC
+// with register index per field).  V carries veh_off / veh_hl / veh_hw (StaticParams or HotParams).
+template <class R, class V>
+__device__ __forceinline__ int block_hits(const V& veh, const R* all4, const R* tbl, int n_blocks, R x, R y, R sn, R cs) {
+  using R4 = typename Vec4<R>::type;
   int hits = 0;
-  const R vx = x + p.veh_off * cs, vy = y + p.veh_off * sn;
-  for (int b = 0; b < p.n_blocks; ++b) {
-    const R C = p.blk[b][2], S = p.blk[b][3], wl = p.blk[b][4], ww = p.blk[b][5];
-    const R dx = vx - p.blk[b][0], dy = vy - p.blk[b][1];
-    const R ac = Math<R>::fabs(cs * C + sn * S);   // |cos(ψ-Ψ)|
-    const R as = Math<R>::fabs(sn * C - cs * S);   // |sin(ψ-Ψ)|
-    const bool sepW = (Math<R>::fabs(dx * C + dy * S) >= wl + (p.veh_hl * ac + p.veh_hw * as)) ||
-                      (Math<R>::fabs(dy * C - dx * S) >= ww + (p.veh_hl * as + p.veh_hw * ac));
-    const bool sepV = (Math<R>::fabs(dx * cs + dy * sn) >= p.veh_hl + (wl * ac + ww * as)) ||
-                      (Math<R>::fabs(dy * cs - dx * sn) >= p.veh_hw + (wl * as + ww * ac));
-    hits += (sepW && sepV) ? 0 : 1;   // !ConvexCollision => hit (hybrid_astar_utils.jl:198)
+  const R vx = Math<R>::fma(veh.veh_off, cs, x), vy = Math<R>::fma(veh.veh_off, sn, y);
+  const unsigned mask = __activemask();
+  {
+    const R ax = vx - all4[0], ay = vy - all4[1];
+    if (__ballot_sync(mask, Math<R>::fma(ax, ax, ay * ay) < all4[2]) == 0u) return 0;   // far from every wall
+  }
+  // exact rectangle-rectangle test against wall b
+  auto exact = [&](const R4 w0, const R4 w1, R dx, R dy) {
+    const R C = w0.z, S = w0.w, wl = w1.x, ww = w1.y;
+    const R ac = Math<R>::fabs(Math<R>::fma(cs, C, sn * S));    // |cos(ψ-Ψ)|
+    const R as = Math<R>::fabs(Math<R>::fma(sn, C, -(cs * S))); // |sin(ψ-Ψ)|
+    const bool sepW = (Math<R>::fabs(Math<R>::fma(dx, C, dy * S)) >= Math<R>::fma(veh.veh_hl, ac, Math<R>::fma(veh.veh_hw, as, wl))) ||
+                      (Math<R>::fabs(Math<R>::fma(dy, C, -(dx * S))) >= Math<R>::fma(veh.veh_hl, as, Math<R>::fma(veh.veh_hw, ac, ww)));
+    const bool sepV = (Math<R>::fabs(Math<R>::fma(dx, cs, dy * sn)) >= Math<R>::fma(wl, ac, Math<R>::fma(ww, as, veh.veh_hl))) ||
+                      (Math<R>::fabs(Math<R>::fma(dy, cs, -(dx * sn))) >= Math<R>::fma(wl, as, Math<R>::fma(ww, ac, veh.veh_hw)));
+    return (sepW && sepV) ? 0 : 1;   // !ConvexCollision => hit (hybrid_astar_utils.jl:198)
+  };
+  const R4* t4 = reinterpret_cast<const R4*>(tbl);
+  if (n_blocks <= 4) {   // few walls: straight loop the compiler can unroll and software-pipeline
+#pragma unroll 4
+    for (int b = 0; b < n_blocks; ++b) {
+      const R4 w0 = t4[2 * b], w1 = t4[2 * b + 1];
+      hits += exact(w0, w1, vx - w0.x, vy - w0.y);
+    }
+  } else {               // many walls: per-wall bounding-circle vote first
+    for (int b = 0; b < n_blocks; ++b) {
+      const R4 w0 = t4[2 * b], w1 = t4[2 * b + 1];
+      const R dx = vx - w0.x, dy = vy - w0.y;
+      if (__ballot_sync(mask, Math<R>::fma(dx, dx, dy * dy) < w1.z) == 0u) continue;   // provably free for every lane
+      hits += exact(w0, w1, dx, dy);
+    }
   }
   return hits;
+}
+template <class R>
+__device__ __forceinline__ int block_hits(const StaticParams<R>& p, R x, R y, R sn, R cs) {
+  return block_hits<R>(p, p.blk_all, &p.blk[0][0], p.n_blocks, x, y, sn, cs);
 }
 
 // BoundEvaluation (MPPIUtils.jl:135-151): sum of violations |x - XL|, |x - XU|

@@ -37,7 +37,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   if ((v & V_HOST_RES) && B == 1) buf.host_res = h->h_res;
   const size_t in_bytes = size_t(B) * (MPPI_MAX_NX + 2 * N) * sizeof(double);
   const size_t res_bytes = size_t(B) * (RES_SCALARS + 2 * N) * sizeof(double);
-  const size_t smemU = size_t(N) * 4 * sizeof(R);
+  const size_t smemU = (size_t(N) * 4 + size_t(8) * p.n_blocks) * sizeof(R);   // nominal + wall table
 
   if (timed == 1) MPPI_CUDA(h, cudaEventRecord(h->ev[0], s));
   if (v & (V_H2D_IN | V_H2D_X0 | V_H2D_U)) {

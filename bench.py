@@ -44,6 +44,8 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", type=int, default=1, help="index into BASELINE.json configs (default 1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: softmin all-gather in-kernel over NVLink peer memory (default) or in-library NCCL")
     return ap.parse_args()
 
 
@@ -224,8 +226,17 @@ def run_ours(a, rank, world, local_rank):
         m.defineMPPIobs(mppi, circles)
     if blocks:
         m.defineMPPIblocks(mppi, blocks)
+    exchange = "none"
     if world > 1 and not batched:
-        mdist.init_library_comm(mppi)
+        exchange = a.exchange
+        if exchange == "peer":
+            try:
+                mdist.init_peer_exchange(mppi)
+            except Exception as e:  # no peer access between these devices: NCCL carries the exchange
+                print(f"[rank {rank}] peer exchange unavailable ({e}); using NCCL", file=sys.stderr)
+                exchange = "nccl"
+        if exchange == "nccl":
+            mdist.init_library_comm(mppi)
 
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")   # > 126 MB L2
 
@@ -248,23 +259,30 @@ def run_ours(a, rank, world, local_rank):
     mppi.sync()
     mppi.adopt_nominal()
 
-    # ---- device-resident timing: one graph launch per iteration, CUDA events on the
-    #      library's stream, L2 flushed between iterations ----
+    # ---- device-resident timing: one graph launch per iteration, CUDA events on the LIBRARY's
+    #      stream, L2 flushed (256 MiB write on the same stream) before every timed iteration.
+    #      Everything is enqueued asynchronously, so host jitter never enters the timed spans and
+    #      the ranks of a sharded run stay in lockstep through the step's own exchange. ----
+    lib_stream = torch.cuda.ExternalStream(mppi.stream(), device=torch.device("cuda", local_rank))
     for _ in range(max(a.warmup, 3)):
         mppi.step_async(adopt=False)
     mppi.sync()
     clocks = ClockSampler(local_rank)
     launches0 = mppi.launch_count()
+    ev0 = [torch.cuda.Event(enable_timing=True) for _ in range(a.steps)]
+    ev1 = [torch.cuda.Event(enable_timing=True) for _ in range(a.steps)]
     barrier()
     clocks.start()
-    dev_us = []
-    for _ in range(a.steps):
-        l2_flush()
+    for i in range(a.steps):
+        with torch.cuda.stream(lib_stream):
+            flush.zero_()
+        ev0[i].record(lib_stream)
         mppi.step_async(adopt=False)
-        mppi.sync()
-        dev_us.append(mppi.timings_us()[3])
+        ev1[i].record(lib_stream)
+    mppi.sync()
     barrier()
     clocks.stop_flag = True
+    dev_us = [ev0[i].elapsed_time(ev1[i]) * 1e3 for i in range(a.steps)]
     launches = mppi.launch_count() - launches0
     total_s = float(np.sum(dev_us)) * 1e-6
     if world > 1:
@@ -327,10 +345,11 @@ def run_ours(a, rank, world, local_rank):
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOADS[a.config], "K_total": K if not batched else K, "K_per_gpu": kl, "N": N,
                        "instances": B * (world if batched else 1), "noise": "philox4x32-10 in-kernel",
-                       "parallelism": f"samples sharded x{world}, one NCCL all-gather per step" if world > 1 and not batched
+                       "parallelism": (f"samples sharded x{world}, softmin all-gather in the finalize kernel over NVLink peer memory"
+                                       if exchange == "peer" else f"samples sharded x{world}, one NCCL all-gather per step") if world > 1 and not batched
                        else ("instances sharded, no collective" if batched and world > 1 else "1 GPU"),
                        "l2": "flushed between timed iterations (256 MiB write)",
-                       "timing": "CUDA events on the library stream around one graph launch per iteration, summed"},
+                       "timing": "CUDA events on the library stream around one graph launch per iteration (flush + step enqueued asynchronously), summed, max over ranks"},
             "latency_us": {"device_median": float(np.median(dev_us)), "device_p99": float(np.percentile(dev_us, 99)),
                            "e2e_median": float(np.median(e2e_s) * 1e6), "e2e_p99": float(np.percentile(e2e_s, 99) * 1e6)},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

@@ -209,9 +209,23 @@ int32_t mppi_comm_unique_id(uint8_t id[MPPI_COMM_ID_BYTES]);
 int32_t mppi_comm_init(mppi_handle_t* h, const uint8_t id[MPPI_COMM_ID_BYTES], int32_t rank,
                        int32_t n_ranks);
 
+/* Peer-memory exchange (preferred on NVLink boxes): every rank exports a CUDA-IPC handle of its
+ * exchange window, the handles are all-gathered by any transport, and mppi_peer_init maps the
+ * peers' windows.  mppi_step then does the softmin all-gather INSIDE the finalize kernel with
+ * NVLink stores + flags (one store latency; no collective library on the data path).  Ranks
+ * must call mppi_step in lockstep, as with any collective; a rank that waits > 2 s fails the
+ * step with MPPI_ENCCL. */
+#define MPPI_PEER_HANDLE_BYTES 64
+int32_t mppi_peer_export(mppi_handle_t* h, uint8_t handle[MPPI_PEER_HANDLE_BYTES]);
+int32_t mppi_peer_init(mppi_handle_t* h, const uint8_t* handles /* n_ranks x 64, rank order */,
+                       int32_t rank, int32_t n_ranks);
+
 /* timings of the last step in microseconds (CUDA events on the handle's stream):
  * [0] rollout, [1] softmin+update, [2] combine+nominal rollout, [3] whole device step */
 int32_t mppi_get_timings(mppi_handle_t* h, float us[4]);
+/* the CUDA stream (cudaStream_t) every step of this handle is enqueued on, so that callers can
+ * order their own work or record their own events against it */
+int32_t mppi_get_stream(mppi_handle_t* h, void** stream);
 /* SM-clock stamps (clock64) at the phase boundaries of the last finalize kernel, instance 0:
  * [0] entry, [1] partials reduced, [2] ranks combined, [3] U_new ready, [4] nominal state
  * recurrence done, [5] states costed, [6] result written.  Diagnostics only. */

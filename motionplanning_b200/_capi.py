@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libmppi_b200.so")
 MPPI_MAX_NX = 8
 MPPI_MAX_N = 256
 MPPI_COMM_ID_BYTES = 128
+MPPI_PEER_HANDLE_BYTES = 64
 
 MPPI_OK, MPPI_EINVAL, MPPI_ECUDA, MPPI_ENCCL, MPPI_ENOMEM, MPPI_ESTATE = range(6)
 MODEL_DYNAMIC7, MODEL_KINEMATIC5 = 0, 1
@@ -103,7 +104,10 @@ SIGNATURES = {
     "mppi_step_combine": (_i, [_H, _P(Partial), _i, _P(Result)]),
     "mppi_comm_unique_id": (_i, [_P(C.c_uint8)]),
     "mppi_comm_init": (_i, [_H, _P(C.c_uint8), _i, _i]),
+    "mppi_peer_export": (_i, [_H, _P(C.c_uint8)]),
+    "mppi_peer_init": (_i, [_H, _P(C.c_uint8), _i, _i]),
     "mppi_get_timings": (_i, [_H, _P(C.c_float)]),
+    "mppi_get_stream": (_i, [_H, _P(C.c_void_p)]),
     "mppi_get_phase_clocks": (_i, [_H, _P(C.c_uint64)]),
     "mppi_set_profiling": (_i, [_H, _i]),
     "mppi_launch_count": (C.c_int64, [_H]),

@@ -88,6 +88,10 @@ int32_t mppi_destroy(mppi_handle_t* h) {
   if (h->stream) cudaStreamSynchronize(h->stream);
   drop_graphs(h);
   if (h->comm && nccl_api().CommDestroy) nccl_api().CommDestroy(h->comm);
+  for (int g = 0; g < 8; ++g)
+    if (h->peer_ptr[g] && h->peer_ptr[g] != h->d_window) cudaIpcCloseMemHandle(h->peer_ptr[g]);
+  if (h->d_window) cudaFree(h->d_window);
+  if (h->d_peers) cudaFree(h->d_peers);
   void* dev[] = {h->d_in, h->d_eps, h->d_costs, h->d_flags, h->d_scratch, h->d_scratch_tmpl, h->d_iter, h->d_Spart,
                  h->d_eta_part, h->d_partial, h->d_gathered, h->d_res, h->d_cand, h->d_dbg, h->d_seq};
   for (void* p : dev) if (p) cudaFree(p);
@@ -121,7 +125,7 @@ static int create_impl(mppi_handle* h) {
   MPPI_CUDA(h, cudaMalloc(&h->d_iter, sizeof(unsigned int)));
   MPPI_CUDA(h, cudaMalloc(&h->d_Spart, B * h->ksplit * N * 2 * rs));
   MPPI_CUDA(h, cudaMalloc(&h->d_eta_part, B * h->ksplit * rs));
-  MPPI_CUDA(h, cudaMalloc(&h->d_partial, B * h->plen * sizeof(double)));
+  MPPI_CUDA(h, cudaMalloc(&h->d_partial, (B + 8) * h->plen * sizeof(double)));   // + room for the peers' copies (in-kernel exchange)
   MPPI_CUDA(h, cudaMalloc(&h->d_gathered, 8 * B * h->plen * sizeof(double)));
   // results: [B][RES_SCALARS] scalars | [B][2N] U_new | [B][(N+1)*n_x] nominal trajectory, one D2H copy
   MPPI_CUDA(h, cudaMalloc(&h->d_res, B * (RES_SCALARS + 2 * N + (N + 1) * c.n_x) * sizeof(double)));

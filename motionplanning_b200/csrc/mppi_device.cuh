@@ -70,6 +70,31 @@ enum { PART_RHO = 0, PART_ETA = 1, PART_ARGMIN = 2, PART_ROLLOUTS = 3, PART_FEAS
 enum { RES_COST = 0, RES_FEASIBLE = 1, RES_ROLLOUTS = 2, RES_FEASCOUNT = 3, RES_ARGMIN = 4, RES_RHO = 5,
        RES_ETA = 6, RES_FLAGS = 7, RES_SCALARS = 8 };
 
+// Exchange window of one rank for the in-kernel softmin all-gather over NVLink peer memory
+// (B == 1), low-latency "LL" protocol: every double travels as one 16-byte line
+// {lo32, flag, hi32, flag} written with a single vector store, flag = step number, so data and
+// arrival notice are the same transaction — no fence, no separate flag write: one NVLink store
+// latency end to end.  Rank r stores its partial into slot [parity][r] of EVERY rank's window;
+// a rank polls its own window until every line carries this step's flag.  Two parities: a rank
+// can be at most one step ahead of the slowest.
+constexpr int PEER_MAX_RANKS = 8;
+constexpr int PEER_PLEN = 8 + 2 * MPPI_MAX_N;   // PART_HDR + 2 N at the largest horizon
+struct PeerWindow {
+  uint4 line[2][PEER_MAX_RANKS][PEER_PLEN];
+  unsigned long long timeout;   // set to the step number when a wait gave up
+};
+__device__ __forceinline__ void ll_store(uint4* dst, double v, uint32_t flag) {
+  const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "r"(uint32_t(b)), "r"(flag), "r"(uint32_t(b >> 32)), "r"(flag) : "memory");
+}
+__device__ __forceinline__ bool ll_try_load(const uint4* src, uint32_t flag, double* v) {
+  uint4 l;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(l.x), "=r"(l.y), "=r"(l.z), "=r"(l.w) : "l"(src) : "memory");
+  if (l.y != flag || l.w != flag) return false;
+  *v = __longlong_as_double((long long)(((unsigned long long)l.z << 32) | l.x));
+  return true;
+}
+
 template <class R>
 struct Buffers {
   const double* x0;     // [B][MPPI_MAX_NX]
@@ -93,6 +118,8 @@ struct Buffers {
   unsigned long long* dbg;  // [16] SM-clock stamps at the phase boundaries of finalize (instance 0)
   int ksplit;
   int n_ranks;
+  int rank;
+  PeerWindow* const* peers;   // [n_ranks] exchange windows of all ranks (own + IPC-mapped peers), or nullptr
   int trace;            // 1: kernels stamp %globaltimer at first-CTA start / last-CTA end into dbg[8..]
 };
 

@@ -86,6 +86,10 @@ struct mppi_handle {
   // multi-GPU
   ncclComm_t comm = nullptr;
   int rank = 0, n_ranks = 1;
+  mppi::PeerWindow* d_window = nullptr;          // this rank's exchange window (cudaMalloc: IPC-exportable)
+  mppi::PeerWindow* peer_ptr[8] = {nullptr};     // all ranks' windows as seen from this device
+  mppi::PeerWindow** d_peers = nullptr;          // device copy of peer_ptr
+  bool p2p = false;                              // exchange in-kernel over peer memory instead of NCCL
   // profiling
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
   int profiling = 0;   // 0 off | 1 eager launches bracketed by events | 2 graph replay, kernels stamp %globaltimer
@@ -200,6 +204,8 @@ Buffers<R> make_buffers(const mppi_handle* h) {
   b.host_seq = h->h_seq;
   b.ksplit = h->ksplit;
   b.n_ranks = h->n_ranks;
+  b.rank = h->rank;
+  b.peers = h->p2p ? h->d_peers : nullptr;
   b.trace = h->profiling == 2 ? 1 : 0;
   return b;
 }

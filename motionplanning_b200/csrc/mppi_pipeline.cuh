@@ -20,7 +20,8 @@ enum {
   V_FUSED_FINAL = 512,  // finalize<PH_PARTIAL|PH_COMBINE> in one kernel (single rank)
   V_H2D_X0 = 1024,      // pinned x0 only -> device
   V_H2D_U = 2048,       // pinned U_nom only -> device
-  V_HOST_RES = 4096     // B == 1: finalize writes the result block to mapped host memory (no D2H node)
+  V_HOST_RES = 4096,    // B == 1: finalize writes the result block to mapped host memory (no D2H node)
+  V_XFINAL = 8192       // finalize<PARTIAL|XCHG|COMBINE>: softmin all-gather in-kernel over NVLink peer memory
 };
 
 template <class R> const StaticParams<R>& params_of(const mppi_handle* h);
@@ -73,6 +74,10 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   const size_t smemF = (size_t(N) * 6 + size_t(N + 1) * (Model::NX + 2 + 3)) * sizeof(R);
   if (v & V_FUSED_FINAL) {
     finalize_kernel<R, Model, SRC, PH_PARTIAL | PH_COMBINE><<<B, FINAL_BS, smemF, s>>>(p, buf);
+    h->launches++;
+  }
+  if (v & V_XFINAL) {
+    finalize_kernel<R, Model, SRC, PH_PARTIAL | PH_XCHG | PH_COMBINE><<<B, FINAL_BS, smemF, s>>>(p, buf);
     h->launches++;
   }
   if (v & V_PARTIAL) {
@@ -133,6 +138,7 @@ inline int kernels_in(const mppi_handle* h, int v) {
   if ((v & (V_H2D_IN | V_H2D_X0 | V_H2D_U)) && h->cfg.B == 1) n++;
   if (v & V_LOCAL) n += 1 + ((h->cutoff && !dwa) ? 1 : 0) + (dwa ? 0 : 1);
   if (v & V_FUSED_FINAL) n++;
+  if (v & V_XFINAL) n++;
   if (v & V_PARTIAL) n++;
   if (v & V_COMBINE) n++;
   return n;
@@ -174,7 +180,7 @@ inline int run_variant(mppi_handle* h, int v) {
   const bool use_graph = h->cfg.use_cuda_graph && h->profiling != 1;
   if (!use_graph) {
     h->in_flight = h->inputs_busy = true;
-    if (v & (V_COMBINE | V_FUSED_FINAL)) h->seq_launched++;
+    if (v & (V_COMBINE | V_FUSED_FINAL | V_XFINAL)) h->seq_launched++;
     return enqueue(h, v & 0xFFFF, h->profiling ? 1 : 0);
   }
   const bool inner = false;
@@ -201,7 +207,7 @@ inline int run_variant(mppi_handle* h, int v) {
   MPPI_CUDA(h, cudaGraphLaunch(it->second, h->stream));
   MPPI_CUDA(h, cudaEventRecord(h->ev[4], h->stream));
   h->launches += kernels_in(h, v & 0xFFFF);
-  if (v & (V_COMBINE | V_FUSED_FINAL)) h->seq_launched++;
+  if (v & (V_COMBINE | V_FUSED_FINAL | V_XFINAL)) h->seq_launched++;
   h->in_flight = h->inputs_busy = true;
   return MPPI_OK;
 }

@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(UPDATE_BS) update_kernel(const __grid_constant
 //               then the final nominal rollout (MPPIUtils.jl:192-198) on thread 0.
 // DWA (DWAUtils.jl:152-158): U_new = the arg-min candidate, replicated over the horizon.
 // ---------------------------------------------------------------------------
-enum { PH_PARTIAL = 1, PH_COMBINE = 2 };
+enum { PH_PARTIAL = 1, PH_COMBINE = 2, PH_XCHG = 4 };
 #define MPPI_STAMP(i) do { if (t == 0 && b == 0) buf.dbg[i] = clock64(); } while (0)
 
 template <class R, class Model, int SRC, int PHASES>
@@ -218,28 +218,59 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
 
   const int G = buf.n_ranks;
   const double* gat = buf.gathered;   // [G][B][plen]
+  size_t gstride = size_t(p.B) * plen;
+  bool xchg_timeout = false;
+  if (PHASES & PH_XCHG) {
+    // In-kernel all-gather over NVLink peer memory (B == 1), LL protocol (see PeerWindow).
+    const int me = buf.rank;
+    const unsigned long long step = *buf.seq + 1ull;   // ranks step in lockstep, so this agrees everywhere
+    const int par = int(step & 1ull);
+    const uint32_t flag = uint32_t(step);
+    for (int i = t; i < plen; i += FINAL_BS) {
+      const double v = part[i];
+      for (int g = 0; g < G; ++g) ll_store(&buf.peers[g]->line[par][me][i], v, flag);
+    }
+    __shared__ int s_timeout;
+    if (t == 0) s_timeout = 0;
+    __syncthreads();
+    double* mine = buf.partial + size_t(plen);   // scratch behind this rank's partial: [G][plen] received copies
+    const unsigned long long t0 = globaltimer_ns();
+    for (int i = t; i < G * plen; i += FINAL_BS) {
+      const int g = i / plen, e = i - g * plen;
+      const uint4* src = &buf.peers[me]->line[par][g][e];
+      double v = 0.0;
+      while (!ll_try_load(src, flag, &v)) {
+        if (globaltimer_ns() - t0 > 2000000000ull) { s_timeout = 1; buf.peers[me]->timeout = step; break; }
+      }
+      mine[i] = v;
+    }
+    __syncthreads();
+    xchg_timeout = s_timeout != 0;
+    gat = mine;
+    gstride = plen;
+  }
   if (t == 0) {
     // global rho = isless-min over ranks (NaN last); ties -> lowest rank == lowest global index
     int best = 0;
-    double rho = gat[(size_t(0) * p.B + b) * plen + PART_RHO];
+    double rho = __ldcg(gat + b * plen + PART_RHO);
     for (int g = 1; g < G; ++g) {
-      const double r = gat[(size_t(g) * p.B + b) * plen + PART_RHO];
+      const double r = __ldcg(gat + g * gstride + b * plen + PART_RHO);
       if (r < rho || (r == r && rho != rho)) { rho = r; best = g; }
     }
     double eta = 0.0, rollouts = 0.0, feas = 0.0;
     for (int g = 0; g < G; ++g) {
-      const double* pg = gat + (size_t(g) * p.B + b) * plen;
-      const double sc_g = (G == 1) ? 1.0 : exp(-(pg[PART_RHO] - rho) / double(p.lambda));
+      const double* pg = gat + g * gstride + b * plen;
+      const double sc_g = (G == 1) ? 1.0 : exp(-(__ldcg(pg + PART_RHO) - rho) / double(p.lambda));
       s_scale[g] = sc_g;
-      eta += pg[PART_ETA] * sc_g;
-      rollouts += pg[PART_ROLLOUTS];
-      feas += pg[PART_FEASIBLE];
+      eta += __ldcg(pg + PART_ETA) * sc_g;
+      rollouts += __ldcg(pg + PART_ROLLOUTS);
+      feas += __ldcg(pg + PART_FEASIBLE);
     }
     s_hdr[0] = eta;
     double* rs = buf.res_scalars + size_t(b) * RES_SCALARS;
-    rs[RES_ROLLOUTS] = rollouts + 1.0;   // RolloutCount starts at 1 (MPPIUtils.jl:171,197)
+    rs[RES_ROLLOUTS] = xchg_timeout ? -1.0 : rollouts + 1.0;   // RolloutCount starts at 1 (MPPIUtils.jl:171,197); -1: exchange timed out
     rs[RES_FEASCOUNT] = feas;
-    rs[RES_ARGMIN] = gat[(size_t(best) * p.B + b) * plen + PART_ARGMIN] + 1.0;   // 1-based like Julia
+    rs[RES_ARGMIN] = __ldcg(gat + best * gstride + b * plen + PART_ARGMIN) + 1.0;   // 1-based like Julia
     rs[RES_RHO] = rho;
     rs[RES_ETA] = eta;
   }
@@ -268,7 +299,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
     for (int i = t; i < 2 * N; i += FINAL_BS) {
       const int c = i / N, j = i - c * N;
       double s = 0.0;
-      for (int g = 0; g < G; ++g) s += gat[(size_t(g) * p.B + b) * plen + PART_HDR + i] * s_scale[g];
+      for (int g = 0; g < G; ++g) s += __ldcg(gat + g * gstride + b * plen + PART_HDR + i) * s_scale[g];
       const double u = s / eta;
       rc[i] = u;
       sNew[2 * j + c] = R(u);

@@ -73,3 +73,18 @@ def init_library_comm(mppi, group=None):
         buf = buf.cuda()
     dist.broadcast(buf, src=0, group=group)
     mppi.comm_init(bytes(buf.cpu().numpy().tobytes()), rank, world)
+
+
+def init_peer_exchange(mppi, group=None):
+    """Peer-memory exchange: all-gather the CUDA-IPC handles of the ranks' exchange windows over
+    torch.distributed (plumbing) and map them; the per-step exchange then runs in-kernel."""
+    import torch
+    import torch.distributed as dist
+
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    mine = torch.tensor(list(mppi.peer_export()), dtype=torch.uint8)
+    if dist.get_backend(group) == "nccl":
+        mine = mine.cuda()
+    out = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(out, mine, group=group)
+    mppi.peer_init([bytes(t.cpu().numpy().tobytes()) for t in out], rank, world)

@@ -149,6 +149,12 @@ class MPPISearcher:  # types.jl:46-50
         self._check(self._lib.mppi_get_timings(self._h, us))
         return list(us)
 
+    def stream(self):
+        """cudaStream_t (as int) the handle's steps are enqueued on."""
+        st = C.c_void_p()
+        self._check(self._lib.mppi_get_stream(self._h, C.byref(st)))
+        return st.value or 0
+
     def phase_clocks(self):
         """clock64 stamps at the phase boundaries of the last finalize kernel (diagnostics)."""
         ck = (C.c_uint64 * 16)()
@@ -220,6 +226,19 @@ class MPPISearcher:  # types.jl:46-50
         """In-library NCCL: the softmin exchange becomes an all-gather inside the step graph."""
         buf = (C.c_uint8 * capi.MPPI_COMM_ID_BYTES).from_buffer_copy(bytes(unique_id))
         self._check(self._lib.mppi_comm_init(self._h, buf, rank, n_ranks))
+
+    def peer_export(self):
+        """CUDA-IPC handle (bytes) of this rank's exchange window."""
+        buf = (C.c_uint8 * capi.MPPI_PEER_HANDLE_BYTES)()
+        self._check(self._lib.mppi_peer_export(self._h, buf))
+        return bytes(buf)
+
+    def peer_init(self, handles, rank, n_ranks):
+        """Map all ranks' exchange windows: the softmin all-gather then runs inside the finalize
+        kernel over NVLink peer memory."""
+        blob = b"".join(handles)
+        buf = (C.c_uint8 * len(blob)).from_buffer_copy(blob)
+        self._check(self._lib.mppi_peer_init(self._h, buf, rank, n_ranks))
 
     def step_batched(self, x0s=None, Us=None):
         """Config 5: B independent instances in one call. x0s (n_x, B), Us (N, m, B)."""

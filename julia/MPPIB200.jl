@@ -27,7 +27,7 @@ struct Config
     model::Int32; n_x::Int32; m::Int32; K::Int32; N::Int32; B::Int32
     precision::Int32; noise_mode::Int32; planner::Int32
     feasibility_count::Int32; use_cuda_graph::Int32; device::Int32
-    k_offset::Int32; K_local::Int32; reserved0::Int32
+    k_offset::Int32; K_local::Int32; rollout_variant::Int32
     seed::UInt64
     T::Float64; lambda::Float64
     Sigma::NTuple{4,Float64}

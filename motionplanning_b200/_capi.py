@@ -34,7 +34,7 @@ class Config(C.Structure):
         ("model", _i), ("n_x", _i), ("m", _i), ("K", _i), ("N", _i), ("B", _i),
         ("precision", _i), ("noise_mode", _i), ("planner", _i),
         ("feasibility_count", _i), ("use_cuda_graph", _i), ("device", _i),
-        ("k_offset", _i), ("K_local", _i), ("reserved0", _i),
+        ("k_offset", _i), ("K_local", _i), ("rollout_variant", _i),
         ("seed", C.c_uint64),
         ("T", _d), ("lambda_", _d),
         ("Sigma", _d * 4),

@@ -1,9 +1,15 @@
 // mppi_api.cu — extern "C" entry points declared in include/mppi_b200.h.
 // Each function cites the reference interface it replaces in the header.
+#include <cstdlib>
+
 #include "mppi_extra.cuh"
 #include "mppi_pipeline.cuh"
 
 using namespace mppi;
+
+#ifndef MPPI_PACK_MIN_SAMPLES
+#define MPPI_PACK_MIN_SAMPLES 131072
+#endif
 
 #define H_CHECK(h)            \
   if (!(h)) return MPPI_EINVAL; \
@@ -116,6 +122,14 @@ static int create_impl(mppi_handle* h) {
   int ks = (h->K_local + 2047) / 2048;
   h->ksplit = ks < 1 ? 1 : (ks > 64 ? 64 : ks);
   h->cutoff = c.feasibility_count < c.K;
+  {
+    int variant = c.rollout_variant;
+    if (const char* e = getenv("MPPI_ROLLOUT_VARIANT")) variant = atoi(e);
+    const bool can_pack = c.precision == MPPI_FP32 && (h->K_local % 2) == 0;
+    // auto: packing halves the warps, so it needs enough samples to keep every SM sub-partition busy
+    const long long samples = (long long)h->K_local * c.B;
+    h->packed = can_pack && (variant == 2 || (variant == 0 && samples >= MPPI_PACK_MIN_SAMPLES));
+  }
   MPPI_CUDA(h, cudaMalloc(&h->d_in, B * (MPPI_MAX_NX + 2 * N) * sizeof(double)));
   if (c.planner == MPPI_PLANNER_MPPI) MPPI_CUDA(h, cudaMalloc(&h->d_eps, B * N * K * 2 * rs));
   MPPI_CUDA(h, cudaMalloc(&h->d_costs, B * K * rs));

@@ -44,7 +44,7 @@ struct StaticParams {
   R CL[2], CU[2];
   R slack, obs_pen, term_scale;
   // vehicle (vehicledynamics.jl:2-18), pre-folded where the folding is exact
-  R la, lb, inv_mass_num /*unused*/, mass, Izz, mu, KFZX;
+  R la, lb, mass, inv_mass, Izz, inv_Izz, mu, KFZX;
   R FZF0, FZR0;               // KFZF*g, KFZR*g
   R tireB, tireC, tireD, tireE;  // B = tire[0]/mu, C = tire[1], D = tire[2], E = tire[3]
   R Lwb, inv_Lwb;             // la + lb
@@ -139,7 +139,7 @@ template <class R, int NX>
 struct HotParams {
   R dt, half_dt, Lwb, inv_Lwb;
   R XL[NX], XU[NX], CL[2], CU[2], w[6];
-  R la, lb, mass, Izz, mu, KFZX, FZF0, FZR0, tireB, tireC, tireD, tireE;
+  R la, lb, mass, inv_mass, Izz, inv_Izz, mu, KFZX, FZF0, FZR0, tireB, tireC, tireD, tireE;
   R L00, L10, L11;
   R veh_off, veh_hl, veh_hw;
   R blk_all[4];
@@ -150,7 +150,7 @@ struct HotParams {
     for (int i = 0; i < NX; ++i) { XL[i] = p.XL[i]; XU[i] = p.XU[i]; }
     for (int i = 0; i < 2; ++i) { CL[i] = p.CL[i]; CU[i] = p.CU[i]; }
     for (int i = 0; i < 6; ++i) w[i] = p.w[i];
-    la = p.la; lb = p.lb; mass = p.mass; Izz = p.Izz; mu = p.mu; KFZX = p.KFZX;
+    la = p.la; lb = p.lb; mass = p.mass; inv_mass = p.inv_mass; Izz = p.Izz; inv_Izz = p.inv_Izz; mu = p.mu; KFZX = p.KFZX;
     FZF0 = p.FZF0; FZR0 = p.FZR0;
     tireB = p.tireB; tireC = p.tireC; tireD = p.tireD; tireE = p.tireE;
     L00 = p.L00; L10 = p.L10; L11 = p.L11;
@@ -182,6 +182,20 @@ __device__ __forceinline__ void trace_end(unsigned long long* dbg, int trace, in
 template <class R> struct Math;
 
 template <> struct Math<float> {
+  using S = float;                 // scalar type of parameters / buffers
+  static constexpr int LANES = 1;  // samples carried per thread
+  using Mask = bool;
+  using Count = int;
+  static __device__ __forceinline__ bool lt(float a, float b) { return a < b; }
+  static __device__ __forceinline__ bool le(float a, float b) { return a <= b; }
+  static __device__ __forceinline__ bool ge(float a, float b) { return a >= b; }
+  static __device__ __forceinline__ bool gt(float a, float b) { return a > b; }
+  static __device__ __forceinline__ int count(bool m) { return m ? 1 : 0; }
+  static __device__ __forceinline__ bool any(bool m) { return m; }
+  static __device__ __forceinline__ float lane(float v, int) { return v; }
+  static __device__ __forceinline__ int lane(int c, int) { return c; }
+  static __device__ __forceinline__ float to_real(int c) { return float(c); }
+  static __device__ __forceinline__ float make2(float a, float) { return a; }
   // Fast path: MUFU-based intrinsics.  |abs err| of sin/cos.approx <= 2^-21.4 on
   // [-pi, pi]; well inside the 1e-4 relative cost tolerance of FP32 mode.
   static __device__ __forceinline__ void sincos(float x, float* s, float* c) { __sincosf(x, s, c); }
@@ -237,6 +251,20 @@ template <> struct Math<float> {
 };
 
 template <> struct Math<double> {
+  using S = double;
+  static constexpr int LANES = 1;
+  using Mask = bool;
+  using Count = int;
+  static __device__ __forceinline__ bool lt(double a, double b) { return a < b; }
+  static __device__ __forceinline__ bool le(double a, double b) { return a <= b; }
+  static __device__ __forceinline__ bool ge(double a, double b) { return a >= b; }
+  static __device__ __forceinline__ bool gt(double a, double b) { return a > b; }
+  static __device__ __forceinline__ int count(bool m) { return m ? 1 : 0; }
+  static __device__ __forceinline__ bool any(bool m) { return m; }
+  static __device__ __forceinline__ double lane(double v, int) { return v; }
+  static __device__ __forceinline__ int lane(int c, int) { return c; }
+  static __device__ __forceinline__ double to_real(int c) { return double(c); }
+  static __device__ __forceinline__ double make2(double a, double) { return a; }
   static __device__ __forceinline__ double atan_ratio(double n, double d) { return ::atan(n / d); }
   static __device__ __forceinline__ void sincos(double x, double* s, double* c) { ::sincos(x, s, c); }
   static __device__ __forceinline__ double tan(double x) { return ::tan(x); }
@@ -250,5 +278,9 @@ template <> struct Math<double> {
   static __device__ __forceinline__ double fmax(double a, double b) { return ::fmax(a, b); }
   static __device__ __forceinline__ double fmin(double a, double b) { return ::fmin(a, b); }
 };
+
+// mask combinators usable with bool and with the packed two-lane mask
+__device__ __forceinline__ bool m_and(bool a, bool b) { return a && b; }
+__device__ __forceinline__ bool m_or(bool a, bool b) { return a || b; }
 
 }  // namespace mppi

@@ -52,6 +52,7 @@ struct mppi_handle {
   cudaStream_t stream = nullptr;
   int K_local = 0, ksplit = 1, plen = 0;
   bool cutoff = false;
+  bool packed = false;   // rollout carries two samples per thread as f32x2 (FP32, even K_local)
   std::vector<double> circles, blocks;   // host copies (3 x Mc, 5 x Mp col-major)
   // device
   double* d_in = nullptr;        // [B][8] x0 then [B][2N] U  (d_x0 = d_in, d_U = d_in + 8B)
@@ -136,7 +137,7 @@ void build_params(const mppi_handle* h, StaticParams<R>* p) {
   for (int i = 0; i < 2; ++i) { p->goal[i] = R(c.goal[i]); p->CL[i] = R(c.CL[i]); p->CU[i] = R(c.CU[i]); }
   for (int i = 0; i < MPPI_MAX_NX; ++i) { p->XL[i] = R(c.XL[i]); p->XU[i] = R(c.XU[i]); }
   p->slack = R(c.slack_penalty); p->obs_pen = R(c.obstacle_penalty); p->term_scale = R(c.terminal_scale);
-  p->la = R(c.la); p->lb = R(c.lb); p->mass = R(c.mass); p->Izz = R(c.Izz); p->mu = R(c.mu); p->KFZX = R(c.KFZX);
+  p->la = R(c.la); p->lb = R(c.lb); p->mass = R(c.mass); p->Izz = R(c.Izz); p->inv_mass = R(1) / R(c.mass); p->inv_Izz = R(1) / R(c.Izz); p->mu = R(c.mu); p->KFZX = R(c.KFZX);
   p->FZF0 = R(c.KFZF) * R(c.g); p->FZR0 = R(c.KFZR) * R(c.g);
   p->tireB = R(c.tire[0]) / R(c.mu); p->tireC = R(c.tire[1]); p->tireD = R(c.tire[2]); p->tireE = R(c.tire[3]);
   p->Lwb = R(c.la) + R(c.lb); p->inv_Lwb = R(1) / p->Lwb;

@@ -57,96 +57,124 @@ __global__ void __launch_bounds__(128) begin_kernel(const double* __restrict__ h
   for (int i = threadIdx.x; i < count; i += 128) dev_in[first + i] = host_in[first + i];
 }
 
-// Per-sample accumulators of the rollout (registers).
-template <class R>
+// Per-sample accumulators of the rollout (registers); V carries one or two samples.
+template <class V>
 struct RolloutAcc {
-  R stage = R(0);   // stage + control cost (MPPIUtils.jl:45, vehicledynamics.jl:52)
-  R viol = R(0);    // sum of bound violations (slack applied once at the end)
-  int hits = 0;     // obstacle hits
+  V stage = V(0);   // stage + control cost (MPPIUtils.jl:45, vehicledynamics.jl:52)
+  V viol = V(0);    // sum of bound violations (slack applied once at the end)
+  typename Math<V>::Count hits = Math<V>::count(Math<V>::lt(V(1), V(0)));   // obstacle hits
 };
 
-// The horizon loop for one sample, specialised on the number of circle quads held in
-// registers (NQ >= 0) or reading the circle table (NQ < 0).
-template <class R, class Model, int SRC, int NQ>
-__device__ __forceinline__ void rollout_horizon(const StaticParams<R>& p, const Buffers<R>& buf, Model& veh,
-                                                RolloutAcc<R>& acc, const HotParams<R, Model::NX>* sHot,
-                                                const R* sU, const R* sBlk, int b, int k) {
-  using R2 = typename Vec2<R>::type;
-  using R4 = typename Vec4<R>::type;
+template <class V> struct Ctl { V x, y; };   // the two controls (sr, ax) / their noise
+
+// the same model for another value type
+template <class Model, class V> struct Rebind;
+template <class R, class V> struct Rebind<Kin5<R>, V> { using type = Kin5<V>; };
+template <class R, class V> struct Rebind<Dyn7<R>, V> { using type = Dyn7<V>; };
+
+// The horizon loop for the LANES samples of one thread, specialised on the number of circle
+// quads held in registers (NQ >= 0) or reading the circle table (NQ < 0).
+template <class V, class Model, int SRC, int NQ>
+__device__ __forceinline__ void rollout_horizon(const StaticParams<typename Math<V>::S>& p, const Buffers<typename Math<V>::S>& buf,
+                                                Model& veh, RolloutAcc<V>& acc, const HotParams<typename Math<V>::S, Model::NX>* sHot,
+                                                const typename Math<V>::S* sU, const typename Math<V>::S* sBlk, int b, int k) {
+  using M = Math<V>;
+  using S = typename M::S;
+  using S2 = typename Vec2<S>::type;
+  using S4 = typename Vec4<S>::type;
+  constexpr int LANES = M::LANES;
   const int N = p.N;
-  const HotParams<R, Model::NX> hp = *sHot;   // smem -> registers (unused fields are dead)
+  const HotParams<S, Model::NX> hp = *sHot;   // smem -> registers (unused fields are dead)
   const bool walls = p.n_blocks > 0;
   const size_t estride = size_t(p.K_local);
-  R2* eps = reinterpret_cast<R2*>(buf.eps) + size_t(b) * N * estride + k;
-  const R4* nu_p = reinterpret_cast<const R4*>(sU);
-  R cu0 = R(0), cu1 = R(0);
+  S2* eps = reinterpret_cast<S2*>(buf.eps) + size_t(b) * N * estride + k;
+  const S4* nu_p = reinterpret_cast<const S4*>(sU);
+  auto store_eps = [&](S2* dst, Ctl<V> e) __attribute__((always_inline)) {
+    if (LANES == 1) *dst = S2{M::lane(e.x, 0), M::lane(e.y, 0)};
+    else *reinterpret_cast<S4*>(dst) = S4{M::lane(e.x, 0), M::lane(e.y, 0), M::lane(e.x, 1), M::lane(e.y, 1)};   // two adjacent samples
+  };
+  auto load_eps = [&](const S2* src) __attribute__((always_inline)) {
+    Ctl<V> e;
+    if (LANES == 1) { const S2 t = *src; e.x = V(t.x); e.y = V(t.y); }
+    else { const S4 t = *reinterpret_cast<const S4*>(src); e.x = M::make2(t.x, t.z); e.y = M::make2(t.y, t.w); }
+    return e;
+  };
+  V cu0 = V(0), cu1 = V(0);
   if (SRC == SRC_DWA) {
-    cu0 = R(buf.cand[k]);
-    cu1 = R(buf.cand[estride + k]);
+    cu0 = M::make2(S(buf.cand[k]), S(buf.cand[k + LANES - 1]));
+    cu1 = M::make2(S(buf.cand[estride + k]), S(buf.cand[estride + k + LANES - 1]));
   }
   // one horizon step: PushInBounds, control cost, stage cost, Heun step, tests of x_{j+1}
-  auto advance = [&](R4 nu, R2 e) {
-    R u0, u1;
+  auto advance = [&](S4 nu, Ctl<V> e) __attribute__((always_inline)) {
+    V u0, u1;
     if (SRC == SRC_DWA) {
       u0 = cu0; u1 = cu1;
     } else {
-      u0 = Math<R>::fmin(Math<R>::fmax(nu.x + e.x, hp.CL[0]), hp.CU[0]);   // PushInBounds (:13-20)
-      u1 = Math<R>::fmin(Math<R>::fmax(nu.y + e.y, hp.CL[1]), hp.CU[1]);
-      acc.stage += nu.z * (u0 - nu.x) + nu.w * (u1 - nu.y);                // lambda*U_nom'*inv(Sigma)*(u-U_nom) (:45)
+      u0 = M::fmin(M::fmax(V(nu.x) + e.x, V(hp.CL[0])), V(hp.CU[0]));   // PushInBounds (:13-20)
+      u1 = M::fmin(M::fmax(V(nu.y) + e.y, V(hp.CL[1])), V(hp.CU[1]));
+      acc.stage += M::fma(V(nu.z), u0 - V(nu.x), V(nu.w) * (u1 - V(nu.y)));   // lambda*U_nom'*inv(Sigma)*(u-U_nom) (:45)
     }
     acc.stage += veh.stage_cost(hp, u0, u1);       // VehicleDynamics cost at the pre-step state
     veh.step(hp, u0, u1);                          // Rungekutta2 (:76-90)
-    if (NQ >= 0) acc.hits += circle_hits_regs<R, (NQ > 0 ? NQ : 0)>(hp, veh.s[0], veh.s[1]);   // x_{j+1}: ObstacleEvaluation
-    else acc.hits += circle_hits(p, veh.s[0], veh.s[1]);
-    if (walls) acc.hits += block_hits<R>(hp, hp.blk_all, sBlk, p.n_blocks, veh.s[0], veh.s[1], veh.sn, veh.cs);
-    acc.viol += bound_violation<R, Model::NX>(hp, veh.s);                 // BoundEvaluation
+    if (NQ >= 0) acc.hits += circle_hits_regs<V, (NQ > 0 ? NQ : 0)>(hp, veh.s[0], veh.s[1]);   // x_{j+1}: ObstacleEvaluation
+    else acc.hits += circle_hits<V>(p, veh.s[0], veh.s[1]);
+    if (walls) acc.hits += block_hits<V>(hp, hp.blk_all, sBlk, p.n_blocks, veh.s[0], veh.s[1], veh.sn, veh.cs);
+    acc.viol += bound_violation<V, Model::NX>(hp, veh.s);                 // BoundEvaluation
   };
   if (SRC == SRC_PHILOX) {
-    // one Philox4x32-10 call feeds two horizon steps; eps = chol(Sigma) * z (MPPIUtils.jl:6)
-    // is kept for the update kernel / oracle replay
-    const R L00 = hp.L00, L10 = hp.L10, L11 = hp.L11;
+    // one Philox4x32-10 call per sample feeds two horizon steps; eps = chol(Sigma) * z
+    // (MPPIUtils.jl:6) is kept for the update kernel / oracle replay
+    const S L00 = hp.L00, L10 = hp.L10, L11 = hp.L11;
     const uint32_t gk = uint32_t(p.k_offset + k), iter = *buf.iter;
     // software pipeline: the noise of pair j+2 is generated while pair j integrates, so the
     // integer Philox rounds and the MUFU work of Box-Muller fill the FP32 recurrence's issue gaps
-    auto draw = [&](int j, R2& ea, R2& eb) {
-      const uint4 rnd = philox4x32_10(make_uint4(gk, uint32_t(j >> 1), iter, uint32_t(b)), hp.key);
-      float z0, z1;
-      box_muller(rnd.x, rnd.y, &z0, &z1);
-      ea.x = L00 * R(z0);
-      ea.y = L10 * R(z0) + L11 * R(z1);
-      box_muller(rnd.z, rnd.w, &z0, &z1);
-      eb.x = L00 * R(z0);
-      eb.y = L10 * R(z0) + L11 * R(z1);
+    auto draw = [&](int j, Ctl<V>& ea, Ctl<V>& eb) __attribute__((always_inline)) {
+      float za0[2], za1[2], zb0[2], zb1[2];
+#pragma unroll
+      for (int l = 0; l < LANES; ++l) {
+        const uint4 rnd = philox4x32_10(make_uint4(gk + l, uint32_t(j >> 1), iter, uint32_t(b)), hp.key);
+        box_muller(rnd.x, rnd.y, &za0[l], &za1[l]);
+        box_muller(rnd.z, rnd.w, &zb0[l], &zb1[l]);
+      }
+      const V a0 = M::make2(S(za0[0]), S(za0[LANES - 1])), a1 = M::make2(S(za1[0]), S(za1[LANES - 1]));
+      const V b0 = M::make2(S(zb0[0]), S(zb0[LANES - 1])), b1 = M::make2(S(zb1[0]), S(zb1[LANES - 1]));
+      ea.x = V(L00) * a0; ea.y = M::fma(V(L11), a1, V(L10) * a0);
+      eb.x = V(L00) * b0; eb.y = M::fma(V(L11), b1, V(L10) * b0);
     };
-    R2 na, nb;
+    Ctl<V> na, nb;
     draw(0, na, nb);
     for (int j = 0; j < N; j += 2) {
-      const R2 ea = na, eb = nb;
+      const Ctl<V> ea = na, eb = nb;
       if (j + 2 < N) draw(j + 2, na, nb);
-      *eps = ea;
+      store_eps(eps, ea);
       advance(nu_p[j], ea);
       if (j + 1 < N) {
-        eps[estride] = eb;
+        store_eps(eps + estride, eb);
         advance(nu_p[j + 1], eb);
       }
       eps += 2 * estride;
     }
   } else if (SRC == SRC_SUPPLIED) {
-    R2 e_next = *eps;
+    Ctl<V> e_next = load_eps(eps);
     for (int j = 0; j < N; ++j) {
-      const R2 e = e_next;
+      const Ctl<V> e = e_next;
       eps += estride;
-      if (j + 1 < N) e_next = *eps;   // prefetch next step's noise
+      if (j + 1 < N) e_next = load_eps(eps);   // prefetch next step's noise
       advance(nu_p[j], e);
     }
   } else {
-    for (int j = 0; j < N; ++j) advance(R4{R(0), R(0), R(0), R(0)}, R2{R(0), R(0)});
+    for (int j = 0; j < N; ++j) advance(S4{S(0), S(0), S(0), S(0)}, Ctl<V>{V(0), V(0)});
   }
 }
 
-template <class R, class Model, int SRC>
+// V = float / double: one sample per thread.  V = f32x2: two adjacent samples per thread on the
+// packed FP32 pipe (K_local must be even; chosen by the host for large sample counts).
+template <class V, class Model, int SRC>
 __global__ void __launch_bounds__(ROLLOUT_BS)
-rollout_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) {
+rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, const Buffers<typename Math<V>::S> buf) {
+  using M = Math<V>;
+  using R = typename M::S;
+  constexpr int LANES = M::LANES;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   R* sU = reinterpret_cast<R*>(smem_raw);  // [N][4]: u0, u1, g0, g1
   R* sBlk = sU + 4 * p.N;                  // [n_blocks][8]: wall table
@@ -156,7 +184,7 @@ rollout_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) 
 
   const int b = blockIdx.y;
   const int N = p.N;
-  const int k = blockIdx.x * ROLLOUT_BS + threadIdx.x;
+  const int k = (blockIdx.x * ROLLOUT_BS + threadIdx.x) * LANES;   // first sample of this thread
   trace_begin(buf.dbg, buf.trace, 0);
   if (threadIdx.x == ROLLOUT_BS - 1) sHot.fill(p);
   for (int i = threadIdx.x; i < 8 * p.n_blocks; i += ROLLOUT_BS) sBlk[i] = (&p.blk[0][0])[i];
@@ -173,35 +201,45 @@ rollout_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) 
   }
   __syncthreads();
 
-  R cost = R(0);
-  RolloutAcc<R> acc;
+  unsigned long long key = 0xFFFFFFFFFFFFFFFFull;
+  int n_feas = 0;
   if (active) {
     const double* x0 = buf.x0 + size_t(b) * MPPI_MAX_NX;
+    RolloutAcc<V> acc;
     Model veh;
     veh.init(p, x0);
-    const R gx0 = veh.s[0] - p.goal[0], gy0 = veh.s[1] - p.goal[1];
-    const R d0 = gx0 * gx0 + gy0 * gy0;
+    const V gx0 = veh.s[0] - V(p.goal[0]), gy0 = veh.s[1] - V(p.goal[1]);
+    const V d0 = M::fma(gx0, gx0, gy0 * gy0);
     const int nq = (p.n_circles + 3) >> 2;   // warp-uniform: the whole horizon loop is specialised
-    if (sizeof(R) == 8) rollout_horizon<R, Model, SRC, -1>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
-    else if (nq == 0) rollout_horizon<R, Model, SRC, 0>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
-    else if (nq == 1) rollout_horizon<R, Model, SRC, 1>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
-    else if (nq == 2) rollout_horizon<R, Model, SRC, 2>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
-    else rollout_horizon<R, Model, SRC, -1>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
-    acc.stage += veh.stage_cost(p, R(0), R(0));      // terminal slot: VehicleDynamics(x_N, [0,0]) (:49,:53)
-    const R gx = veh.s[0] - p.goal[0], gy = veh.s[1] - p.goal[1];
-    const R term = Math<R>::div(gx * gx + gy * gy, d0) * p.term_scale;   // (:54)
-    cost = acc.stage + p.slack * acc.viol + p.obs_pen * R(acc.hits) + term;
-    buf.costs[size_t(b) * p.K_local + k] = cost;
-    buf.flags[size_t(b) * p.K_local + k] =
-        uint8_t(((acc.hits == 0 && !(acc.viol > R(0))) ? MPPI_FLAG_FEASIBLE : 0) | (acc.hits ? MPPI_FLAG_COLLIDED : 0) |
-                ((acc.viol > R(0)) ? MPPI_FLAG_OOB : 0));
+    if (sizeof(R) == 8) rollout_horizon<V, Model, SRC, -1>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
+    else if (nq == 0) rollout_horizon<V, Model, SRC, 0>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
+    else if (nq == 1) rollout_horizon<V, Model, SRC, 1>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
+    else if (nq == 2) rollout_horizon<V, Model, SRC, 2>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
+    else rollout_horizon<V, Model, SRC, -1>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
+    acc.stage += veh.stage_cost(p, V(0), V(0));      // terminal slot: VehicleDynamics(x_N, [0,0]) (:49,:53)
+    const V gx = veh.s[0] - V(p.goal[0]), gy = veh.s[1] - V(p.goal[1]);
+    const V term = M::div(M::fma(gx, gx, gy * gy), d0) * V(p.term_scale);   // (:54)
+    const V cost = M::fma(V(p.slack), acc.viol, M::fma(V(p.obs_pen), M::to_real(acc.hits), acc.stage)) + term;
+#pragma unroll
+    for (int l = 0; l < LANES; ++l) {
+      if (k + l < p.K_local) {
+        const R c = M::lane(cost, l), vl = M::lane(acc.viol, l);
+        const int hl = M::lane(acc.hits, l);
+        const bool feas = hl == 0 && !(vl > R(0));
+        buf.costs[size_t(b) * p.K_local + k + l] = c;
+        buf.flags[size_t(b) * p.K_local + k + l] =
+            uint8_t((feas ? MPPI_FLAG_FEASIBLE : 0) | (hl ? MPPI_FLAG_COLLIDED : 0) | ((vl > R(0)) ? MPPI_FLAG_OOB : 0));
+        const unsigned long long kk = make_key(c, (unsigned int)(k + l));
+        key = kk < key ? kk : key;
+        n_feas += feas ? 1 : 0;
+      }
+    }
   }
   // block epilogue: (min cost, first index) and feasible count -> one atomic each
-  unsigned long long key = active ? make_key(cost, (unsigned int)k) : 0xFFFFFFFFFFFFFFFFull;
   key = warp_min_u64(key);
-  const unsigned feas_mask = __ballot_sync(0xffffffffu, active && acc.hits == 0 && !(acc.viol > R(0)));
+  n_feas = warp_sum(n_feas);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  if (lane == 0) { s_key[wid] = key; s_feas[wid] = __popc(feas_mask); }
+  if (lane == 0) { s_key[wid] = key; s_feas[wid] = n_feas; }
   __syncthreads();
   if (threadIdx.x == 0) {
     int f = 0;

@@ -1,6 +1,7 @@
 // mppi_models.cuh — vehicle models, Heun step, obstacle/bound tests, Philox.
 #pragma once
 #include "mppi_device.cuh"
+#include "mppi_pack.cuh"
 
 namespace mppi {
 
@@ -13,45 +14,49 @@ namespace mppi {
 //     corrector is x + dt/2*(k+k)); tan(sa_next) and sincos(psi_next) are
 //     carried to the next step's k1, so each step costs 2 sincos + 1 tan.
 // ---------------------------------------------------------------------------
-template <class R>
+// V is the value type a thread carries: float / double (one sample) or f32x2 (two samples on the
+// packed FP32 pipe, mppi_pack.cuh); parameters are scalars of type Math<V>::S.  Multiply-adds are
+// written as explicit fma so that every instantiation performs the same operation sequence.
+template <class V>
 struct Kin5 {
+  using M = Math<V>;
+  using S = typename M::S;
   static constexpr int NX = 5;
   static constexpr int IPSI = 2;
-  R s[NX];
-  R sn, cs;   // sin/cos of s[IPSI], carried between steps
-  R tn;       // tan(sa) / L, carried between steps
+  V s[NX];
+  V sn, cs;   // sin/cos of s[IPSI], carried between steps
+  V tn;       // tan(sa) / L, carried between steps
 
-  __device__ __forceinline__ void init(const StaticParams<R>& p, const double* x0) {
+  __device__ __forceinline__ void init(const StaticParams<S>& p, const double* x0) {
 #pragma unroll
-    for (int i = 0; i < NX; ++i) s[i] = R(x0[i]);
-    Math<R>::sincos(s[IPSI], &sn, &cs);
-    tn = Math<R>::over(Math<R>::tan(s[4]), p.Lwb, p.inv_Lwb);
+    for (int i = 0; i < NX; ++i) s[i] = V(S(x0[i]));
+    M::sincos(s[IPSI], &sn, &cs);
+    tn = M::over(M::tan(s[4]), p.Lwb, p.inv_Lwb);
   }
   // stage cost of VehicleDynamics at (state, u): SURVEY 8(a) a6 = dynamic cost with v = r = 0
   template <class P>
-  __device__ __forceinline__ R stage_cost(const P& p, R sr, R ax) const {
-    return p.w[2] * (ax * ax) + p.w[3] * (sr * sr) + p.w[4] * (s[4] * s[4]) + p.w[5] * (s[1] * s[1]);
+  __device__ __forceinline__ V stage_cost(const P& p, V sr, V ax) const {
+    return M::fma(V(p.w[5]), s[1] * s[1], M::fma(V(p.w[4]), s[4] * s[4], M::fma(V(p.w[3]), sr * sr, V(p.w[2]) * (ax * ax))));
   }
   template <class P>
-  __device__ __forceinline__ void step(const P& p, R sr, R ax) {
+  __device__ __forceinline__ void step(const P& p, V sr, V ax) {
     // k1 at (s, u)
-    const R k1x = s[3] * cs, k1y = s[3] * sn, k1p = s[3] * tn;   // ux cosψ, ux sinψ, ux/L tan(sa)
+    const V k1x = s[3] * cs, k1y = s[3] * sn, k1p = s[3] * tn;   // ux cosψ, ux sinψ, ux/L tan(sa)
     // predictor x + k1*dt
-    const R psit = s[2] + k1p * p.dt;
-    const R uxt = s[3] + ax * p.dt;
-    const R sat = s[4] + sr * p.dt;
-    R st, ct;
-    Math<R>::sincos(psit, &st, &ct);
-    const R tnt = Math<R>::over(Math<R>::tan(sat), p.Lwb, p.inv_Lwb);
-    const R k2x = uxt * ct, k2y = uxt * st, k2p = uxt * tnt;
+    const V psit = M::fma(k1p, V(p.dt), s[2]);
+    const V uxt = M::fma(ax, V(p.dt), s[3]);
+    const V sat = M::fma(sr, V(p.dt), s[4]);
+    V st, ct;
+    M::sincos(psit, &st, &ct);
+    const V tnt = M::over(M::tan(sat), p.Lwb, p.inv_Lwb);
     // corrector x + dt*(k1+k2)/2
-    s[0] = s[0] + p.half_dt * (k1x + k2x);
-    s[1] = s[1] + p.half_dt * (k1y + k2y);
-    s[2] = s[2] + p.half_dt * (k1p + k2p);
+    s[0] = M::fma(V(p.half_dt), M::fma(uxt, ct, k1x), s[0]);
+    s[1] = M::fma(V(p.half_dt), M::fma(uxt, st, k1y), s[1]);
+    s[2] = M::fma(V(p.half_dt), M::fma(uxt, tnt, k1p), s[2]);
     s[3] = uxt;
     s[4] = sat;
     tn = tnt;
-    Math<R>::sincos(s[2], &sn, &cs);
+    M::sincos(s[2], &sn, &cs);
   }
 };
 
@@ -60,68 +65,70 @@ struct Kin5 {
 // State [x, y, v, r, psi, ux, sa], control [sr, ax];
 // derivative order [dx, dy, dv, dr, dpsi, du, dsa] (:50) == state order.
 // ---------------------------------------------------------------------------
-template <class R>
+template <class V>
 struct Dyn7 {
+  using M = Math<V>;
+  using S = typename M::S;
   static constexpr int NX = 7;
   static constexpr int IPSI = 4;
-  R s[NX];
-  R sn, cs;
+  V s[NX];
+  V sn, cs;
 
-  __device__ __forceinline__ void init(const StaticParams<R>& p, const double* x0) {
+  __device__ __forceinline__ void init(const StaticParams<S>& p, const double* x0) {
 #pragma unroll
-    for (int i = 0; i < NX; ++i) s[i] = R(x0[i]);
-    Math<R>::sincos(s[IPSI], &sn, &cs);
+    for (int i = 0; i < NX; ++i) s[i] = V(S(x0[i]));
+    M::sincos(s[IPSI], &sn, &cs);
   }
   template <class P>
-  __device__ __forceinline__ R stage_cost(const P& p, R sr, R ax) const {  // :52
-    return s[2] * s[2] * p.w[0] + p.w[1] * (s[3] * s[3]) + p.w[2] * (ax * ax) + p.w[3] * (sr * sr) +
-           p.w[4] * (s[6] * s[6]) + p.w[5] * (s[1] * s[1]);
+  __device__ __forceinline__ V stage_cost(const P& p, V sr, V ax) const {  // :52
+    return M::fma(V(p.w[5]), s[1] * s[1], M::fma(V(p.w[4]), s[6] * s[6], M::fma(V(p.w[3]), sr * sr,
+           M::fma(V(p.w[2]), ax * ax, M::fma(V(p.w[1]), s[3] * s[3], V(p.w[0]) * (s[2] * s[2]))))));
   }
   // lateral tyre force (:35-38): mu*FZ*D*sin(C*atan(X - E*(X - atan X))), X = B*alpha
   template <class P>
-  static __device__ __forceinline__ R tyre(const P& p, R FZ, R alpha) {
-    const R X = p.tireB * alpha;
-    const R inner = X - p.tireE * (X - Math<R>::atan(X));
-    return p.mu * FZ * p.tireD * Math<R>::sin(p.tireC * Math<R>::atan(inner));
+  static __device__ __forceinline__ V tyre(const P& p, V FZ, V alpha) {
+    const V X = V(p.tireB) * alpha;
+    const V inner = M::fma(V(-p.tireE), X - M::atan(X), X);
+    return (V(p.mu * p.tireD) * FZ) * M::sin(V(p.tireC) * M::atan(inner));
   }
   // derivatives of (v, r) and the planar velocity at state q with heading sin/cos (sq, cq)
   template <class P>
-  static __device__ __forceinline__ void deriv(const P& p, R v, R r, R ux, R sa, R sq, R cq,
-                                               R ax, R* dx, R* dy, R* dv, R* dr) {
-    const R t = ax - r * v;
-    const R FZF = R(2) * (p.FZF0 - t * p.KFZX);                              // :30
-    const R FZR = R(2) * (p.FZR0 + t * p.KFZX);                              // :31
-    const R den = ux + R(0.01);
-    const R alpha_f = Math<R>::atan_ratio(v + p.la * r, den) - sa;           // :32
-    const R alpha_r = Math<R>::atan_ratio(v - p.lb * r, den);                // :33
-    const R FY1 = tyre(p, FZF, alpha_f);
-    const R FY2 = tyre(p, FZR, alpha_r);
-    const R uxc = ux <= R(0) ? R(0) : ux;                                    // :40-42
-    *dx = uxc * cq - v * sq;                                                 // :43
-    *dy = uxc * sq + v * cq;                                                 // :44
-    *dv = Math<R>::div(FY1 + FY2, p.mass) - r * uxc;                         // :46
-    *dr = Math<R>::div(FY1 * p.la - FY2 * p.lb, p.Izz);                      // :47
+  static __device__ __forceinline__ void deriv(const P& p, V v, V r, V ux, V sa, V sq, V cq,
+                                               V ax, V* dx, V* dy, V* dv, V* dr) {
+    const V t = M::fma(-r, v, ax);                                           // ax - r*v
+    const V FZF = V(S(2)) * M::fma(t, V(-p.KFZX), V(p.FZF0));                // :30
+    const V FZR = V(S(2)) * M::fma(t, V(p.KFZX), V(p.FZR0));                 // :31
+    const V den = ux + V(S(0.01));
+    const V alpha_f = M::atan_ratio(M::fma(V(p.la), r, v), den) - sa;        // :32
+    const V alpha_r = M::atan_ratio(M::fma(V(-p.lb), r, v), den);            // :33
+    const V FY1 = tyre(p, FZF, alpha_f);
+    const V FY2 = tyre(p, FZR, alpha_r);
+    const V uxc = M::fmax(ux, V(S(0)));                                      // :40-42
+    *dx = M::fma(uxc, cq, -(v * sq));                                        // :43
+    *dy = M::fma(uxc, sq, v * cq);                                           // :44
+    *dv = M::fma(-r, uxc, M::over(FY1 + FY2, p.mass, p.inv_mass));           // :46
+    *dr = M::over(M::fma(FY1, V(p.la), -(FY2 * V(p.lb))), p.Izz, p.inv_Izz); // :47
   }
   template <class P>
-  __device__ __forceinline__ void step(const P& p, R sr, R ax) {
-    R k1x, k1y, k1v, k1r;
+  __device__ __forceinline__ void step(const P& p, V sr, V ax) {
+    V k1x, k1y, k1v, k1r;
     deriv(p, s[2], s[3], s[5], s[6], sn, cs, ax, &k1x, &k1y, &k1v, &k1r);
-    const R k1p = s[3];                                                      // dpsi = r (:45)
-    const R vt = s[2] + k1v * p.dt, rt = s[3] + k1r * p.dt;
-    const R psit = s[4] + k1p * p.dt;
-    const R uxt = s[5] + ax * p.dt, sat = s[6] + sr * p.dt;
-    R st, ct;
-    Math<R>::sincos(psit, &st, &ct);
-    R k2x, k2y, k2v, k2r;
+    const V k1p = s[3];                                                      // dpsi = r (:45)
+    const V vt = M::fma(k1v, V(p.dt), s[2]), rt = M::fma(k1r, V(p.dt), s[3]);
+    const V psit = M::fma(k1p, V(p.dt), s[4]);
+    const V uxt = M::fma(ax, V(p.dt), s[5]), sat = M::fma(sr, V(p.dt), s[6]);
+    V st, ct;
+    M::sincos(psit, &st, &ct);
+    V k2x, k2y, k2v, k2r;
     deriv(p, vt, rt, uxt, sat, st, ct, ax, &k2x, &k2y, &k2v, &k2r);
-    s[0] = s[0] + p.half_dt * (k1x + k2x);
-    s[1] = s[1] + p.half_dt * (k1y + k2y);
-    s[2] = s[2] + p.half_dt * (k1v + k2v);
-    s[3] = s[3] + p.half_dt * (k1r + k2r);
-    s[4] = s[4] + p.half_dt * (k1p + rt);
+    s[0] = M::fma(V(p.half_dt), k1x + k2x, s[0]);
+    s[1] = M::fma(V(p.half_dt), k1y + k2y, s[1]);
+    s[2] = M::fma(V(p.half_dt), k1v + k2v, s[2]);
+    s[3] = M::fma(V(p.half_dt), k1r + k2r, s[3]);
+    s[4] = M::fma(V(p.half_dt), k1p + rt, s[4]);
     s[5] = uxt;   // == ux + dt/2*(ax+ax)
     s[6] = sat;
-    Math<R>::sincos(s[4], &sn, &cs);
+    M::sincos(s[4], &sn, &cs);
   }
 };
 
@@ -132,43 +139,51 @@ struct Dyn7 {
 // The circle table is padded on the host to a multiple of 4 with never-hit entries
 // (r^2 = -1), so the common small counts run as fully unrolled groups whose table
 // entries are immediate constant-bank operands (no per-circle load / loop overhead).
-template <class R, int Q>
-__device__ __forceinline__ int circle_hits_quads(const StaticParams<R>& p, R x, R y) {
-  int hits = 0;
+template <class V, int Q>
+__device__ __forceinline__ typename Math<V>::Count circle_hits_quads(const StaticParams<typename Math<V>::S>& p, V x, V y) {
+  using M = Math<V>;
+  typename M::Count hits = M::count(M::lt(V(1), V(0)));   // zero
 #pragma unroll
   for (int o = 0; o < 4 * Q; ++o) {
-    const R dx = x - p.circ[o][0], dy = y - p.circ[o][1];
-    hits += (dx * dx + dy * dy <= p.circ[o][2]) ? 1 : 0;   // sum((s-o).^2) <= r^2
+    const V dx = x - V(p.circ[o][0]), dy = y - V(p.circ[o][1]);
+    hits += M::count(M::le(M::fma(dx, dx, dy * dy), V(p.circ[o][2])));   // sum((s-o).^2) <= r^2
   }
   return hits;
 }
 // the first 4*Q circles of a register-resident table (horizon loop of the rollout kernel)
-template <class R, int Q, class P>
-__device__ __forceinline__ int circle_hits_regs(const P& hp, R px, R py) {
-  int h = 0;
+template <class V, int Q, class P>
+__device__ __forceinline__ typename Math<V>::Count circle_hits_regs(const P& hp, V px, V py) {
+  using M = Math<V>;
+  typename M::Count h = M::count(M::lt(V(1), V(0)));
 #pragma unroll
   for (int o = 0; o < 4 * Q; ++o) {
-    const R dx = px - hp.circ[o][0], dy = py - hp.circ[o][1];
-    h += (dx * dx + dy * dy <= hp.circ[o][2]) ? 1 : 0;
+    const V dx = px - V(hp.circ[o][0]), dy = py - V(hp.circ[o][1]);
+    h += M::count(M::le(M::fma(dx, dx, dy * dy), V(hp.circ[o][2])));
   }
   return h;
 }
 
-template <class R>
-__device__ __forceinline__ int circle_hits(const StaticParams<R>& p, R x, R y) {
+template <class V>
+__device__ __forceinline__ typename Math<V>::Count circle_hits(const StaticParams<typename Math<V>::S>& p, V x, V y) {
+  using M = Math<V>;
   switch ((p.n_circles + 3) >> 2) {   // warp-uniform
-    case 0: return 0;
-    case 1: return circle_hits_quads<R, 1>(p, x, y);
-    case 2: return circle_hits_quads<R, 2>(p, x, y);
+    case 0: return M::count(M::lt(V(1), V(0)));
+    case 1: return circle_hits_quads<V, 1>(p, x, y);
+    case 2: return circle_hits_quads<V, 2>(p, x, y);
     default: break;
   }
-  int hits = 0;
+  typename M::Count hits = M::count(M::lt(V(1), V(0)));
   for (int o = 0; o < p.n_circles; ++o) {
-    const R dx = x - p.circ[o][0], dy = y - p.circ[o][1];
-    hits += (dx * dx + dy * dy <= p.circ[o][2]) ? 1 : 0;
+    const V dx = x - V(p.circ[o][0]), dy = y - V(p.circ[o][1]);
+    hits += M::count(M::le(M::fma(dx, dx, dy * dy), V(p.circ[o][2])));
   }
   return hits;
 }
+
+// hits = tested - free, per lane
+template <class V> __device__ __forceinline__ typename Math<V>::Count hits_from_free(int tested, typename Math<V>::Count fr);
+template <> __device__ __forceinline__ int hits_from_free<float>(int tested, int fr) { return tested - fr; }
+template <> __device__ __forceinline__ int hits_from_free<double>(int tested, int fr) { return tested - fr; }
 
 // Rectangle-vs-rectangle with the reference's ConvexCollision semantics
 // (CollisionDetection/src/utils.jl:37-74): "free" needs a separating axis among
@@ -185,59 +200,67 @@ __device__ __forceinline__ int circle_hits(const StaticParams<R>& p, R x, R y) {
 // the kernel parameter itself, or — in the rollout kernel — a shared-memory copy read as two
 // broadcast 128-bit loads per wall (a parameter table indexed by a loop counter costs an LDC
 // with register index per field).  V carries veh_off / veh_hl / veh_hw (StaticParams or HotParams).
-template <class R, class V>
-__device__ __forceinline__ int block_hits(const V& veh, const R* all4, const R* tbl, int n_blocks, R x, R y, R sn, R cs) {
-  using R4 = typename Vec4<R>::type;
-  int hits = 0;
-  const R vx = Math<R>::fma(veh.veh_off, cs, x), vy = Math<R>::fma(veh.veh_off, sn, y);
+template <class V, class P>
+__device__ __forceinline__ typename Math<V>::Count block_hits(const P& veh, const typename Math<V>::S* all4, const typename Math<V>::S* tbl,
+                                                              int n_blocks, V x, V y, V sn, V cs) {
+  using M = Math<V>;
+  using S = typename M::S;
+  using S4 = typename Vec4<S>::type;
+  typename M::Count hits = M::count(M::lt(V(1), V(0)));
+  const V vx = M::fma(V(veh.veh_off), cs, x), vy = M::fma(V(veh.veh_off), sn, y);
   const unsigned mask = __activemask();
   {
-    const R ax = vx - all4[0], ay = vy - all4[1];
-    if (__ballot_sync(mask, Math<R>::fma(ax, ax, ay * ay) < all4[2]) == 0u) return 0;   // far from every wall
+    const V ax = vx - V(all4[0]), ay = vy - V(all4[1]);
+    if (__ballot_sync(mask, M::any(M::lt(M::fma(ax, ax, ay * ay), V(all4[2])))) == 0u) return hits;   // far from every wall
   }
-  // exact rectangle-rectangle test against wall b
-  auto exact = [&](const R4 w0, const R4 w1, R dx, R dy) {
-    const R C = w0.z, S = w0.w, wl = w1.x, ww = w1.y;
-    const R ac = Math<R>::fabs(Math<R>::fma(cs, C, sn * S));    // |cos(ψ-Ψ)|
-    const R as = Math<R>::fabs(Math<R>::fma(sn, C, -(cs * S))); // |sin(ψ-Ψ)|
-    const bool sepW = (Math<R>::fabs(Math<R>::fma(dx, C, dy * S)) >= Math<R>::fma(veh.veh_hl, ac, Math<R>::fma(veh.veh_hw, as, wl))) ||
-                      (Math<R>::fabs(Math<R>::fma(dy, C, -(dx * S))) >= Math<R>::fma(veh.veh_hl, as, Math<R>::fma(veh.veh_hw, ac, ww)));
-    const bool sepV = (Math<R>::fabs(Math<R>::fma(dx, cs, dy * sn)) >= Math<R>::fma(wl, ac, Math<R>::fma(ww, as, veh.veh_hl))) ||
-                      (Math<R>::fabs(Math<R>::fma(dy, cs, -(dx * sn))) >= Math<R>::fma(wl, as, Math<R>::fma(ww, ac, veh.veh_hw)));
-    return (sepW && sepV) ? 0 : 1;   // !ConvexCollision => hit (hybrid_astar_utils.jl:198)
+  // exact rectangle-rectangle test against one wall
+  auto exact = [&](const S4 w0, const S4 w1, V dx, V dy) __attribute__((always_inline)) {
+    const V C = V(w0.z), Sn = V(w0.w), wl = V(w1.x), ww = V(w1.y), hl = V(veh.veh_hl), hw = V(veh.veh_hw);
+    const V ac = M::fabs(M::fma(cs, C, sn * Sn));     // |cos(ψ-Ψ)|
+    const V as = M::fabs(M::fma(sn, C, -(cs * Sn)));  // |sin(ψ-Ψ)|
+    const auto sepW = m_or(M::ge(M::fabs(M::fma(dx, C, dy * Sn)), M::fma(hl, ac, M::fma(hw, as, wl))),
+                           M::ge(M::fabs(M::fma(dy, C, -(dx * Sn))), M::fma(hl, as, M::fma(hw, ac, ww))));
+    const auto sepV = m_or(M::ge(M::fabs(M::fma(dx, cs, dy * sn)), M::fma(wl, ac, M::fma(ww, as, hl))),
+                           M::ge(M::fabs(M::fma(dy, cs, -(dx * sn))), M::fma(wl, as, M::fma(ww, ac, hw))));
+    return M::count(m_and(sepW, sepV));   // 1 = free; !ConvexCollision => hit (hybrid_astar_utils.jl:198)
   };
-  const R4* t4 = reinterpret_cast<const R4*>(tbl);
+  const S4* t4 = reinterpret_cast<const S4*>(tbl);
+  typename M::Count freec = hits;
+  int tested = 0;
   if (n_blocks <= 4) {   // few walls: straight loop the compiler can unroll and software-pipeline
 #pragma unroll 4
     for (int b = 0; b < n_blocks; ++b) {
-      const R4 w0 = t4[2 * b], w1 = t4[2 * b + 1];
-      hits += exact(w0, w1, vx - w0.x, vy - w0.y);
+      const S4 w0 = t4[2 * b], w1 = t4[2 * b + 1];
+      freec += exact(w0, w1, vx - V(w0.x), vy - V(w0.y));
     }
+    tested = n_blocks;
   } else {               // many walls: per-wall bounding-circle vote first
     for (int b = 0; b < n_blocks; ++b) {
-      const R4 w0 = t4[2 * b], w1 = t4[2 * b + 1];
-      const R dx = vx - w0.x, dy = vy - w0.y;
-      if (__ballot_sync(mask, Math<R>::fma(dx, dx, dy * dy) < w1.z) == 0u) continue;   // provably free for every lane
-      hits += exact(w0, w1, dx, dy);
+      const S4 w0 = t4[2 * b], w1 = t4[2 * b + 1];
+      const V dx = vx - V(w0.x), dy = vy - V(w0.y);
+      if (__ballot_sync(mask, M::any(M::lt(M::fma(dx, dx, dy * dy), V(w1.z)))) == 0u) continue;   // provably free for every lane
+      freec += exact(w0, w1, dx, dy);
+      ++tested;
     }
   }
-  return hits;
+  return hits_from_free<V>(tested, freec);   // hits = walls tested - walls found free
 }
-template <class R>
-__device__ __forceinline__ int block_hits(const StaticParams<R>& p, R x, R y, R sn, R cs) {
-  return block_hits<R>(p, p.blk_all, &p.blk[0][0], p.n_blocks, x, y, sn, cs);
+template <class V>
+__device__ __forceinline__ typename Math<V>::Count block_hits(const StaticParams<typename Math<V>::S>& p, V x, V y, V sn, V cs) {
+  return block_hits<V>(p, p.blk_all, &p.blk[0][0], p.n_blocks, x, y, sn, cs);
 }
 
 // BoundEvaluation (MPPIUtils.jl:135-151): sum of violations |x - XL|, |x - XU|
 // (strict inequalities; the slack factor is applied once at the end).
 // XL <= XU, so at most one side is violated: max(XL - s, s - XU, 0) equals the sum of
 // the two one-sided terms exactly (the other term is +0).
-template <class R, int NX, class P>
-__device__ __forceinline__ R bound_violation(const P& p, const R* s) {
-  R acc = R(0);
+template <class V, int NX, class P>
+__device__ __forceinline__ V bound_violation(const P& p, const V* s) {
+  using M = Math<V>;
+  V acc = V(0);
 #pragma unroll
   for (int i = 0; i < NX; ++i)
-    acc += Math<R>::fmax(Math<R>::fmax(p.XL[i] - s[i], s[i] - p.XU[i]), R(0));
+    acc += M::fmax(M::fmax(V(p.XL[i]) - s[i], s[i] - V(p.XU[i])), V(0));
   return acc;
 }
 

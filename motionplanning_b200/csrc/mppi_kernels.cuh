@@ -13,7 +13,7 @@ enum { SRC_SUPPLIED = 0, SRC_PHILOX = 1, SRC_DWA = 2 };
 constexpr int ROLLOUT_BS = 64;   // 65,536 samples = 1024 CTAs = 6.9 per SM: one balanced wave on 148 SMs
 constexpr int UPDATE_BS = 256;
 constexpr int UPDATE_JG = 4;
-constexpr int FINAL_BS = 256;
+constexpr int FINAL_BS = 1024;  // 32 warps: the partial tree covers 128 columns per pass with 4 per warp
 constexpr int CUTOFF_BS = 1024;
 
 

@@ -116,6 +116,96 @@ __global__ void __launch_bounds__(UPDATE_BS) update_kernel(const __grid_constant
 }
 
 // ---------------------------------------------------------------------------
+// States x_0..x_N of the nominal rollout into shared memory rows [state | sin ψ | cos ψ].
+// Generic form: one thread integrates the Heun recurrence (the only sequential part).
+// Kinematic bicycle: the model is triangular — (sa, ux) are running sums of the controls, ψ a
+// running sum of terms that depend on (sa, ux) only, (x, y) running sums of terms that depend on
+// (ψ, ux) only — so the recurrence splits into three short scans (one fma per step) with the
+// transcendental work done for all steps in parallel in between.  The scans are warp-shuffle prefix
+// sums, so states differ from the sequential form by summation order only (a few ulp).
+// `sT` is scratch [N+1][3].  Must be called by all threads of the block.
+// ---------------------------------------------------------------------------
+template <class Model>
+struct NominalStates {
+  using R = typename Model::S;
+  static constexpr int NX = Model::NX, ROW = Model::NX + 2;
+  static __device__ __forceinline__ void run(const StaticParams<R>& p, const double* x0, const R* sNew, R* sX, R* /*sT*/, int N, int t) {
+    if (t == 0) {
+      Model veh;
+      veh.init(p, x0);
+#pragma unroll
+      for (int i = 0; i < NX; ++i) sX[i] = veh.s[i];
+      sX[NX] = veh.sn; sX[NX + 1] = veh.cs;
+      for (int j = 0; j < N; ++j) {
+        veh.step(p, sNew[2 * j], sNew[2 * j + 1]);
+        R* row = sX + (j + 1) * ROW;
+#pragma unroll
+        for (int i = 0; i < NX; ++i) row[i] = veh.s[i];
+        row[NX] = veh.sn; row[NX + 1] = veh.cs;
+      }
+    }
+    __syncthreads();
+  }
+};
+
+template <class R>
+struct NominalStates<Kin5<R>> {
+  using M = Math<R>;
+  static constexpr int NX = 5, ROW = 7;   // x, y, psi, ux, sa, sin psi, cos psi
+  // out[(j+1) * ROW] = init + sum_{i<=j} coef * in[i * stride]: one warp, 32 steps per pass as a
+  // shuffle prefix sum (5 shuffle+add levels instead of 32 dependent shared-memory round trips)
+  static __device__ __forceinline__ void warp_scan(const R* in, int stride, R coef, R init, R* out, int N, int lane) {
+    R carry = init;
+    for (int j0 = 0; j0 < N; j0 += 32) {
+      const int j = j0 + lane;
+      R v = (j < N) ? coef * in[j * stride] : R(0);
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const R n = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += n;
+      }
+      v += carry;
+      if (j < N) out[(j + 1) * ROW] = v;
+      carry = __shfl_sync(0xffffffffu, v, 31);
+    }
+  }
+  static __device__ __forceinline__ void run(const StaticParams<R>& p, const double* x0, const R* sNew, R* sX, R* sT, int N, int t) {
+    const int nt = blockDim.x;
+    // scan 1: sa (warp 0) and ux (warp 1) are running sums of the controls: s + u*dt
+    const int lane = t & 31;
+    if (t < NX) sX[t] = R(x0[t]);
+    if (t < 32) warp_scan(sNew, 2, p.dt, R(x0[4]), sX + 4, N, lane);
+    else if (t < 64) warp_scan(sNew + 1, 2, p.dt, R(x0[3]), sX + 3, N, lane);
+    __syncthreads();
+    for (int j = t; j <= N; j += nt) sT[3 * j] = M::over(M::tan(sX[j * ROW + 4]), p.Lwb, p.inv_Lwb);   // tan(sa_j)/L
+    __syncthreads();
+    for (int j = t; j < N; j += nt)   // k1p + k2p of step j
+      sT[3 * j + 1] = M::fma(sX[(j + 1) * ROW + 3], sT[3 * (j + 1)], sX[j * ROW + 3] * sT[3 * j]);
+    __syncthreads();
+    // scan 2: psi_{j+1} = psi_j + dt/2 (k1p + k2p)
+    if (t < 32) warp_scan(sT + 1, 3, p.half_dt, sX[2], sX + 2, N, lane);
+    __syncthreads();
+    for (int j = t; j <= N; j += nt) {
+      R* row = sX + j * ROW;
+      M::sincos(row[2], &row[5], &row[6]);                         // carried sin/cos of psi_j
+      if (j < N) {
+        const R psit = M::fma(row[3] * sT[3 * j], p.dt, row[2]);   // predictor heading
+        R st, ct;
+        M::sincos(psit, &st, &ct);
+        const R uxt = sX[(j + 1) * ROW + 3];
+        sT[3 * j + 1] = M::fma(uxt, ct, row[3] * row[6]);          // k1x + k2x
+        sT[3 * j + 2] = M::fma(uxt, st, row[3] * row[5]);          // k1y + k2y
+      }
+    }
+    __syncthreads();
+    // scan 3: x (warp 0) and y (warp 1)
+    if (t < 32) warp_scan(sT + 1, 3, p.half_dt, sX[0], sX + 0, N, lane);
+    else if (t < 64) warp_scan(sT + 2, 3, p.half_dt, sX[1], sX + 1, N, lane);
+    __syncthreads();
+  }
+};
+
+// ---------------------------------------------------------------------------
 // finalize_kernel.  One block per instance.
 //   PH_PARTIAL: sum the update partials in fixed order -> this rank's
 //               (rho, eta, argmin, counts, S) against its LOCAL rho.
@@ -169,7 +259,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
         const int lane = t & 31, wid = t >> 5, ks_n = buf.ksplit;
         const R* Sp = buf.Spart + size_t(b) * ks_n * N * 2;
         const R* Ep = buf.eta_part + size_t(b) * ks_n;
-        constexpr int NW = FINAL_BS / 32, CB = 16;   // CB columns per warp in flight (independent loads + trees)
+        constexpr int NW = FINAL_BS / 32, CB = 4;    // CB columns per warp in flight (independent loads + trees)
         for (int col0 = wid; col0 <= 2 * N; col0 += NW * CB) {   // col = c*N + j; col == 2N: eta
           double s[CB];
 #pragma unroll
@@ -313,21 +403,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
   constexpr int NX = Model::NX, ROW = Model::NX + 2;   // state, sin(heading), cos(heading)
   R* sX = sNew + 2 * N;                 // [N+1][ROW]
   R* sC = sX + (N + 1) * ROW;           // [N+1][3]: stage+control cost, bound violation, hits
-  if (t == 0) {
-    Model veh;
-    veh.init(p, buf.x0 + size_t(b) * MPPI_MAX_NX);
-#pragma unroll
-    for (int i = 0; i < NX; ++i) sX[i] = veh.s[i];
-    sX[NX] = veh.sn; sX[NX + 1] = veh.cs;
-    for (int j = 0; j < N; ++j) {
-      veh.step(p, sNew[2 * j], sNew[2 * j + 1]);
-      R* row = sX + (j + 1) * ROW;
-#pragma unroll
-      for (int i = 0; i < NX; ++i) row[i] = veh.s[i];
-      row[NX] = veh.sn; row[NX + 1] = veh.cs;
-    }
-  }
-  __syncthreads();
+  NominalStates<Model>::run(p, buf.x0 + size_t(b) * MPPI_MAX_NX, sNew, sX, sC, N, t);
   MPPI_STAMP(4);
   double* tr = buf.res_traj + size_t(b) * (N + 1) * NX;   // col-major (N+1) x n_x
   for (int j = t; j <= N; j += FINAL_BS) {
@@ -352,11 +428,14 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
   }
   __syncthreads();
   MPPI_STAMP(5);
+  R stage = R(0), viol = R(0), fh = R(0);
+  if (t < 32) {   // fixed-shape tree over the horizon: lanes stride over j, then a shuffle tree
+    for (int j = t; j <= N; j += 32) { stage += sC[3 * j]; viol += sC[3 * j + 1]; fh += sC[3 * j + 2]; }
+    stage = warp_sum(stage); viol = warp_sum(viol); fh = warp_sum(fh);
+  }
   if (t == 0) {
     const R gx0 = sX[0] - p.goal[0], gy0 = sX[1] - p.goal[1];
     const R d0 = gx0 * gx0 + gy0 * gy0;
-    R stage = R(0), viol = R(0), fh = R(0);
-    for (int j = 0; j <= N; ++j) { stage += sC[3 * j]; viol += sC[3 * j + 1]; fh += sC[3 * j + 2]; }
     const int hits = int(fh);
     const R gx = sX[N * ROW] - p.goal[0], gy = sX[N * ROW + 1] - p.goal[1];
     const R term = Math<R>::div(gx * gx + gy * gy, d0) * p.term_scale;

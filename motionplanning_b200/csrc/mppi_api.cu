@@ -101,7 +101,7 @@ int32_t mppi_destroy(mppi_handle_t* h) {
   void* dev[] = {h->d_in, h->d_eps, h->d_costs, h->d_flags, h->d_scratch, h->d_scratch_tmpl, h->d_iter, h->d_Spart,
                  h->d_eta_part, h->d_partial, h->d_gathered, h->d_res, h->d_cand, h->d_dbg, h->d_seq};
   for (void* p : dev) if (p) cudaFree(p);
-  void* host[] = {h->h_in, h->h_res, h->h_partial, h->h_gathered, h->h_seq};
+  void* host[] = {h->h_in, h->h_res, h->h_partial, h->h_gathered, h->h_seq, h->h_ll};
   for (void* p : host) if (p) cudaFreeHost(p);
   for (auto& e : h->ev) if (e) cudaEventDestroy(e);
   if (h->stream) cudaStreamDestroy(h->stream);
@@ -148,7 +148,8 @@ static int create_impl(mppi_handle* h) {
   MPPI_CUDA(h, cudaMalloc(&h->d_dbg, 16 * sizeof(unsigned long long)));
   MPPI_CUDA(h, cudaMemset(h->d_dbg, 0, 16 * sizeof(unsigned long long)));
   // inputs and results are MAPPED pinned memory: for B == 1 the step's kernels read / write them
-  // directly over PCIe (no memcpy nodes in the step graph) and the host spins on h_seq
+  // directly over PCIe (no memcpy nodes in the step graph); every 16-byte result line carries the
+  // step's sequence number, so the host needs no separate completion flag (and the GPU no system fence)
   MPPI_CUDA(h, cudaHostAlloc(&h->h_in, B * (MPPI_MAX_NX + 2 * N) * sizeof(double), cudaHostAllocMapped));
   MPPI_CUDA(h, cudaHostAlloc(&h->h_seq, sizeof(unsigned long long), cudaHostAllocMapped));
   *h->h_seq = 0;
@@ -156,6 +157,9 @@ static int create_impl(mppi_handle* h) {
   MPPI_CUDA(h, cudaMemset(h->d_seq, 0, sizeof(unsigned long long)));
   MPPI_CUDA(h, cudaHostAlloc(&h->h_res, (B * (RES_SCALARS + 2 * N) + (N + 1) * c.n_x) * sizeof(double), cudaHostAllocMapped));
   h->h_traj = h->h_res + B * (RES_SCALARS + 2 * N);
+  h->n_ll = RES_SCALARS + 2 * N + (N + 1) * c.n_x;
+  MPPI_CUDA(h, cudaHostAlloc(&h->h_ll, size_t(h->n_ll) * 16, cudaHostAllocMapped));
+  memset(h->h_ll, 0, size_t(h->n_ll) * 16);
   MPPI_CUDA(h, cudaMallocHost(&h->h_partial, B * h->plen * sizeof(double)));
   MPPI_CUDA(h, cudaMallocHost(&h->h_gathered, 8 * B * h->plen * sizeof(double)));
   // inputs: X0 from the config for every instance, zero nominal (setup.jl:55)

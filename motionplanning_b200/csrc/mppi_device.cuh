@@ -112,7 +112,7 @@ struct Buffers {
   double* res_control;  // [B][2*N]  col-major N x m
   double* res_traj;     // [B][(N+1)*n_x] col-major (N+1) x n_x
   const double* cand;   // DWA: [K][2] col-major K x m candidates
-  double* host_res;         // mapped pinned host mirror of the result block (B == 1), or nullptr
+  uint4* host_res;          // mapped pinned host mirror of the result block (B == 1) as LL lines {lo, flag, hi, flag}, or nullptr
   unsigned long long* seq;  // device count of completed steps
   volatile unsigned long long* host_seq;  // mapped pinned host copy of *seq: the completion flag the host spins on
   unsigned long long* dbg;  // [16] SM-clock stamps at the phase boundaries of finalize (instance 0)

@@ -76,6 +76,8 @@ struct mppi_handle {
   // pinned host mirrors
   double* h_in = nullptr;
   double* h_res = nullptr;
+  unsigned long long* h_ll = nullptr;    // mapped pinned: the B == 1 result block as LL lines, two 8-byte words {value lo32 | flag, value hi32 | flag} per double
+  int n_ll = 0;
   double* h_traj = nullptr;      // inside the h_res allocation
   double* h_partial = nullptr;
   double* h_gathered = nullptr;

@@ -30,6 +30,19 @@ template <class R> const StaticParams<R>& params_of(const mppi_handle* h);
 template <> inline const StaticParams<float>& params_of<float>(const mppi_handle* h) { return h->pf; }
 template <> inline const StaticParams<double>& params_of<double>(const mppi_handle* h) { return h->pd; }
 
+// long horizons need more than the default 48 KB of dynamic shared memory: opt in once per instantiation
+template <class R, class Model, int SRC, int PHASES>
+cudaError_t launch_finalize(int B, size_t smem, cudaStream_t s, const StaticParams<R>& p, const Buffers<R>& buf) {
+  static size_t allowed = 48 * 1024;
+  if (smem > allowed) {
+    cudaError_t e = cudaFuncSetAttribute(finalize_kernel<R, Model, SRC, PHASES>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    if (e != cudaSuccess) return e;
+    allowed = smem;
+  }
+  finalize_kernel<R, Model, SRC, PHASES><<<B, FINAL_BS, smem, s>>>(p, buf);
+  return cudaSuccess;
+}
+
 template <class R, class Model, int SRC>
 int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all events, 2 = inner boundaries only (graph nodes)
   const StaticParams<R>& p = params_of<R>(h);
@@ -37,7 +50,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   if (v & V_FUSED_FINAL) { buf.gathered = buf.partial; buf.n_ranks = 1; }   // single rank: combine reads its own partial
   const int B = h->cfg.B, N = h->cfg.N, K = h->K_local, nx = h->cfg.n_x;
   cudaStream_t s = h->stream;
-  if ((v & V_HOST_RES) && B == 1) buf.host_res = h->h_res;
+  if ((v & V_HOST_RES) && B == 1) buf.host_res = reinterpret_cast<uint4*>(h->h_ll);
   const size_t in_bytes = size_t(B) * (MPPI_MAX_NX + 2 * N) * sizeof(double);
   const size_t res_bytes = size_t(B) * (RES_SCALARS + 2 * N) * sizeof(double);
   const size_t smemU = (size_t(N) * 4 + size_t(8) * p.n_blocks) * sizeof(R);   // nominal + wall table
@@ -83,17 +96,22 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
     }
     if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[2], s));
   }
-  const size_t smemF = (size_t(N) * 6 + size_t(N + 1) * (Model::NX + 2 + 3)) * sizeof(R);
+  // finalize's shared memory: result block + own partial (+ G gathered partials for the in-kernel
+  // exchange) in double, then nominal controls, states and per-step costs in R
+  const size_t plen = PART_HDR + 2 * size_t(N);
+  const size_t smemF = (RES_SCALARS + 2 * size_t(N) + size_t(N + 1) * Model::NX + plen) * sizeof(double) +
+                       (size_t(N) * 6 + size_t(N + 1) * (Model::NX + 2 + 3)) * sizeof(R);
+  const size_t smemX = smemF + size_t(h->n_ranks) * plen * sizeof(double);
   if (v & V_FUSED_FINAL) {
-    finalize_kernel<R, Model, SRC, PH_PARTIAL | PH_COMBINE><<<B, FINAL_BS, smemF, s>>>(p, buf);
+    MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_PARTIAL | PH_COMBINE>(B, smemF, s, p, buf)));
     h->launches++;
   }
   if (v & V_XFINAL) {
-    finalize_kernel<R, Model, SRC, PH_PARTIAL | PH_XCHG | PH_COMBINE><<<B, FINAL_BS, smemF, s>>>(p, buf);
+    MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_PARTIAL | PH_XCHG | PH_COMBINE>(B, smemX, s, p, buf)));
     h->launches++;
   }
   if (v & V_PARTIAL) {
-    finalize_kernel<R, Model, SRC, PH_PARTIAL><<<B, FINAL_BS, smemF, s>>>(p, buf);
+    MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_PARTIAL>(B, smemF, s, p, buf)));
     h->launches++;
   }
   if (v & V_D2H_PARTIAL)
@@ -107,7 +125,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
     if (r != ncclSuccess) { h->err = std::string("ncclAllGather: ") + api.GetErrorString(r); return MPPI_ENCCL; }
   }
   if (v & V_COMBINE) {
-    finalize_kernel<R, Model, SRC, PH_COMBINE><<<B, FINAL_BS, smemF, s>>>(p, buf);
+    MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_COMBINE>(B, smemF, s, p, buf)));
     h->launches++;
   }
   if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[3], s));
@@ -163,23 +181,40 @@ inline int take_dirty(mppi_handle* h) {
   return v;
 }
 
-// Wait for the step whose finalize carries sequence number seq_launched.  B == 1: spin on the
-// mapped completion flag (the result block is already in host memory when it flips), checking
-// the stream now and then so that a faulted launch cannot hang the caller.  Otherwise: stream sync.
+// Wait for the step whose finalize carries sequence number seq_launched.  B == 1: the result block
+// arrives in mapped host memory as LL lines, each 8-byte half {value bits | flag} written atomically
+// with flag = the step's sequence number, so "every line carries this step's flag" IS completion:
+// one PCIe one-way trip after the last store, no fence and no second flag write on the GPU.  The
+// stream is checked now and then so that a faulted launch cannot hang the caller.  Otherwise: stream sync.
 inline int wait_step(mppi_handle* h, bool flag_ok) {
   if (flag_ok && h->cfg.B == 1) {
-    volatile unsigned long long* f = h->h_seq;
-    for (unsigned spins = 1;; ++spins) {
-      if (*f >= h->seq_launched) { h->timings_pending = true; h->inputs_busy = false; return MPPI_OK; }
-      if ((spins & 0x3FFF) == 0) {
-        const cudaError_t e = cudaStreamQuery(h->stream);
-        if (e == cudaSuccess) break;          // everything retired: fall through to the sync below
-        if (e != cudaErrorNotReady) { h->err = std::string("step failed: ") + cudaGetErrorString(e); return MPPI_ECUDA; }
-      }
+    const unsigned long long f = (unsigned long long)(uint32_t(h->seq_launched)) << 32;
+    const volatile unsigned long long* L = h->h_ll;
+    const int n = h->n_ll;
+    unsigned spins = 0;
+    bool faulted = false;
+    for (int i = n - 1, done = 0; done < n;) {   // last line first (it is stored last), then the rest in order
+      unsigned long long w0, w1;
+      for (;;) {
+        w0 = L[2 * i]; w1 = L[2 * i + 1];
+        if ((w0 & 0xFFFFFFFF00000000ull) == f && (w1 & 0xFFFFFFFF00000000ull) == f) break;
+        if ((++spins & 0x3FFF) == 0) {
+          const cudaError_t e = cudaStreamQuery(h->stream);
+          if (e != cudaErrorNotReady && e != cudaSuccess) { h->err = std::string("step failed: ") + cudaGetErrorString(e); return MPPI_ECUDA; }
+          if (e == cudaSuccess && (spins & 0x3FFFF) == 0) { faulted = true; break; }   // retired long ago, line never came
+        }
 #if defined(__x86_64__)
-      __builtin_ia32_pause();
+        __builtin_ia32_pause();
 #endif
+      }
+      if (faulted) break;
+      const unsigned long long bits = (w0 & 0xFFFFFFFFull) | (w1 << 32);
+      memcpy(&h->h_res[i], &bits, sizeof bits);
+      ++done;
+      i = (done == 1) ? 0 : i + 1;
     }
+    if (!faulted) { h->timings_pending = true; h->inputs_busy = false; return MPPI_OK; }
+    h->err = "step retired without delivering its result block"; return MPPI_ECUDA;
   }
   MPPI_CUDA(h, cudaStreamSynchronize(h->stream));
   h->in_flight = h->inputs_busy = false;

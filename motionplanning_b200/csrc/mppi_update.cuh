@@ -173,9 +173,12 @@ struct NominalStates<Kin5<R>> {
     const int nt = blockDim.x;
     // scan 1: sa (warp 0) and ux (warp 1) are running sums of the controls: s + u*dt
     const int lane = t & 31;
-    if (t < NX) sX[t] = R(x0[t]);
+    // (row 0 is written by a third warp: nvcc threads a lane-dependent `if` ahead of a scan into the
+    // scan's own warp test, the scanning warp then runs split in two, and a split warp takes the
+    // slow divergent form of every shuffle: ~3,000 cycles per scan instead of ~700)
     if (t < 32) warp_scan(sNew, 2, p.dt, R(x0[4]), sX + 4, N, lane);
     else if (t < 64) warp_scan(sNew + 1, 2, p.dt, R(x0[3]), sX + 3, N, lane);
+    else if (t < 64 + NX) sX[t - 64] = R(x0[t - 64]);
     __syncthreads();
     for (int j = t; j <= N; j += nt) sT[3 * j] = M::over(M::tan(sX[j * ROW + 4]), p.Lwb, p.inv_Lwb);   // tan(sa_j)/L
     __syncthreads();
@@ -215,21 +218,58 @@ struct NominalStates<Kin5<R>> {
 // DWA (DWAUtils.jl:152-158): U_new = the arg-min candidate, replicated over the horizon.
 // ---------------------------------------------------------------------------
 enum { PH_PARTIAL = 1, PH_COMBINE = 2, PH_XCHG = 4 };
-#define MPPI_STAMP(i) do { if (t == 0 && b == 0) buf.dbg[i] = clock64(); } while (0)
-
+// phase clocks, written out with the results; stamped by a lane of the LAST warp: an `if (t == 0)` ahead
+// of a warp-collective section gets threaded into that section's warp test and splits warp 0 (see NominalStates)
+#define MPPI_STAMP(i) do { if (t == FINAL_BS - 32) s_clk[i] = clock64(); } while (0)
+__device__ __forceinline__ Scratch fresh_scratch(int K_local) {
+  Scratch fresh;
+  fresh.rho_key = ~0ull; fresh.argmin = ~0u; fresh.feasible_count = 0; fresh.k_eff = K_local; fresh.pad = 0;
+  return fresh;
+}
 template <class R, class Model, int SRC, int PHASES>
 __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) {
+  // Everything this block produces is staged in shared memory and leaves in one burst at the end:
+  // a global store followed by a barrier, or a read-back of a value the block just stored, costs
+  // an L2 round trip (~1,000 cycles, more across the die boundary), and the old form chained six.
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  R* sU = reinterpret_cast<R*>(smem_raw);        // [N][4]: U_nom0, U_nom1, g0, g1
-  R* sNew = sU + 4 * p.N;                        // [N][2]: U_new
+  const int b = blockIdx.x, N = p.N, t = threadIdx.x;
+  constexpr int NX = Model::NX, ROW = Model::NX + 2;   // state, sin(heading), cos(heading)
+  const int plen = PART_HDR + 2 * N;
+  const int n_res = RES_SCALARS + 2 * N + (N + 1) * NX;
+  double* sRS = reinterpret_cast<double*>(smem_raw);   // result block, laid out like the host block:
+  double* sRC = sRS + RES_SCALARS;                     //   scalars | U_new [2][N] | trajectory (N+1) x n_x col-major
+  double* sTR = sRC + 2 * N;
+  double* sOwn = sRS + n_res;                          // [plen] this rank's partial
+  double* sGat = sOwn + plen;                          // [G][plen] all ranks' partials (PH_XCHG only)
+  R* sU = reinterpret_cast<R*>(sGat + ((PHASES & PH_XCHG) ? buf.n_ranks * plen : 0));   // [N][4]: U_nom0, U_nom1, g0, g1
+  R* sNew = sU + 4 * N;                                // [N][2]: U_new
   __shared__ double s_scale[8];
   __shared__ double s_hdr[4];
-  const int b = blockIdx.x, N = p.N, t = threadIdx.x;
-  const int plen = PART_HDR + 2 * N;
+  __shared__ double s_x0[MPPI_MAX_NX];
+  __shared__ unsigned long long s_clk[8];
   double* part = buf.partial + size_t(b) * plen;
   MPPI_STAMP(0);
   trace_begin(buf.dbg, buf.trace, 2);
+  // loads that do not depend on this step's kernels go first, so their latency hides behind the partial tree
   const Scratch sc = buf.scratch[b];
+  unsigned long long seq0 = 0;
+  unsigned int iter0 = 0;
+  if (t == 0) { seq0 = *buf.seq; iter0 = *buf.iter; }
+  const unsigned long long seq_all = *buf.seq;   // every thread stamps its result lines with the step number
+  if (PHASES & PH_COMBINE) {
+    if (t < MPPI_MAX_NX) s_x0[t] = buf.x0[size_t(b) * MPPI_MAX_NX + t];
+    // old nominal + g for the nominal rollout's control-cost term (evaluated against the OLD
+    // U_nom: MPPIUtils.jl:192 runs before main.jl:62 replaces it)
+    const double* Ub = buf.U + size_t(b) * 2 * N;
+    for (int j = t; j < N; j += FINAL_BS) {
+      const R u0 = (SRC == SRC_DWA) ? R(0) : R(Ub[j]), u1 = (SRC == SRC_DWA) ? R(0) : R(Ub[N + j]);
+      sU[4 * j + 0] = u0; sU[4 * j + 1] = u1;
+      sU[4 * j + 2] = p.G00 * u0 + p.G01 * u1;
+      sU[4 * j + 3] = p.G10 * u0 + p.G11 * u1;
+    }
+  }
+  constexpr bool PART_TO_GLOBAL = !(PHASES & PH_COMBINE);   // only a partial-only launch has a consumer outside this block
+  double* pdst = PART_TO_GLOBAL ? part : sOwn;
 
   if (PHASES & PH_PARTIAL) {
     if (SRC == SRC_DWA) {
@@ -246,11 +286,11 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
         __syncthreads();
       }
       if (t == 0) {
-        part[PART_RHO] = double(rho);
-        part[PART_ETA] = 1.0;
-        part[PART_ARGMIN] = double(s_arg) + double(p.k_offset);
-        part[PART_ROLLOUTS] = double(sc.k_eff);
-        part[PART_FEASIBLE] = double(sc.feasible_count);
+        pdst[PART_RHO] = double(rho);
+        pdst[PART_ETA] = 1.0;
+        pdst[PART_ARGMIN] = double(s_arg) + double(p.k_offset);
+        pdst[PART_ROLLOUTS] = double(sc.k_eff);
+        pdst[PART_FEASIBLE] = double(sc.feasible_count);
       }
     } else {
       // Fixed-order tree over the ksplit partials: one warp per output column (2N control
@@ -281,49 +321,47 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
 #pragma unroll
             for (int u = 0; u < CB; ++u) {
               const int col = col0 + u * NW;
-              if (col < 2 * N) part[PART_HDR + col] = s[u];
-              else if (col == 2 * N) part[PART_ETA] = s[u];
+              if (col < 2 * N) pdst[PART_HDR + col] = s[u];
+              else if (col == 2 * N) pdst[PART_ETA] = s[u];
             }
           }
         }
       }
       if (t == 0) {
-        part[PART_RHO] = double(key_cost(sc.rho_key, R(0)));
+        pdst[PART_RHO] = double(key_cost(sc.rho_key, R(0)));
         // FP32 key carries the index unless the cut-off kernel wrote argmin explicitly
         const unsigned int arg = (sizeof(R) == 4 && sc.argmin == 0xFFFFFFFFu) ? (unsigned int)(sc.rho_key & 0xFFFFFFFFull) : sc.argmin;
-        part[PART_ARGMIN] = double(arg) + double(p.k_offset);
-        part[PART_ROLLOUTS] = double(sc.k_eff);
-        part[PART_FEASIBLE] = double(sc.feasible_count);
+        pdst[PART_ARGMIN] = double(arg) + double(p.k_offset);
+        pdst[PART_ROLLOUTS] = double(sc.k_eff);
+        pdst[PART_FEASIBLE] = double(sc.feasible_count);
       }
     }
-    __syncthreads();   // block-scope visibility of `part` for the combine phase (G == 1)
-    if (t == 0) {      // this phase is the last consumer of the scratch: re-arm it for the next step
-      Scratch fresh;
-      fresh.rho_key = ~0ull; fresh.argmin = ~0u; fresh.feasible_count = 0; fresh.k_eff = p.K_local; fresh.pad = 0;
-      buf.scratch[b] = fresh;
-    }
+    __syncthreads();   // block-scope visibility of the partial for the combine phase
   }
   MPPI_STAMP(1);
-  if (!(PHASES & PH_COMBINE)) return;
+  if (!(PHASES & PH_COMBINE)) {
+    if (t == 0) buf.scratch[b] = fresh_scratch(p.K_local);   // last consumer of the scratch: re-arm it for the next step
+    return;
+  }
 
   const int G = buf.n_ranks;
-  const double* gat = buf.gathered;   // [G][B][plen]
+  // gathered partials [G][B][plen]: an earlier kernel's output (COMBINE-only launch), or shared memory
+  const double* gat = (PHASES & PH_PARTIAL) ? sOwn - size_t(b) * plen : buf.gathered;
   size_t gstride = size_t(p.B) * plen;
   bool xchg_timeout = false;
   if (PHASES & PH_XCHG) {
     // In-kernel all-gather over NVLink peer memory (B == 1), LL protocol (see PeerWindow).
     const int me = buf.rank;
-    const unsigned long long step = *buf.seq + 1ull;   // ranks step in lockstep, so this agrees everywhere
+    const unsigned long long step = seq_all + 1ull;   // ranks step in lockstep, so this agrees everywhere
     const int par = int(step & 1ull);
     const uint32_t flag = uint32_t(step);
     for (int i = t; i < plen; i += FINAL_BS) {
-      const double v = part[i];
+      const double v = sOwn[i];
       for (int g = 0; g < G; ++g) ll_store(&buf.peers[g]->line[par][me][i], v, flag);
     }
     __shared__ int s_timeout;
     if (t == 0) s_timeout = 0;
     __syncthreads();
-    double* mine = buf.partial + size_t(plen);   // scratch behind this rank's partial: [G][plen] received copies
     const unsigned long long t0 = globaltimer_ns();
     for (int i = t; i < G * plen; i += FINAL_BS) {
       const int g = i / plen, e = i - g * plen;
@@ -332,56 +370,45 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
       while (!ll_try_load(src, flag, &v)) {
         if (globaltimer_ns() - t0 > 2000000000ull) { s_timeout = 1; buf.peers[me]->timeout = step; break; }
       }
-      mine[i] = v;
+      sGat[i] = v;
     }
     __syncthreads();
     xchg_timeout = s_timeout != 0;
-    gat = mine;
+    gat = sGat;
     gstride = plen;
   }
   if (t == 0) {
     // global rho = isless-min over ranks (NaN last); ties -> lowest rank == lowest global index
     int best = 0;
-    double rho = __ldcg(gat + b * plen + PART_RHO);
+    double rho = gat[b * plen + PART_RHO];
     for (int g = 1; g < G; ++g) {
-      const double r = __ldcg(gat + g * gstride + b * plen + PART_RHO);
+      const double r = gat[g * gstride + b * plen + PART_RHO];
       if (r < rho || (r == r && rho != rho)) { rho = r; best = g; }
     }
     double eta = 0.0, rollouts = 0.0, feas = 0.0;
     for (int g = 0; g < G; ++g) {
       const double* pg = gat + g * gstride + b * plen;
-      const double sc_g = (G == 1) ? 1.0 : exp(-(__ldcg(pg + PART_RHO) - rho) / double(p.lambda));
+      const double sc_g = (G == 1) ? 1.0 : exp(-(pg[PART_RHO] - rho) / double(p.lambda));
       s_scale[g] = sc_g;
-      eta += __ldcg(pg + PART_ETA) * sc_g;
-      rollouts += __ldcg(pg + PART_ROLLOUTS);
-      feas += __ldcg(pg + PART_FEASIBLE);
+      eta += pg[PART_ETA] * sc_g;
+      rollouts += pg[PART_ROLLOUTS];
+      feas += pg[PART_FEASIBLE];
     }
     s_hdr[0] = eta;
-    double* rs = buf.res_scalars + size_t(b) * RES_SCALARS;
-    rs[RES_ROLLOUTS] = xchg_timeout ? -1.0 : rollouts + 1.0;   // RolloutCount starts at 1 (MPPIUtils.jl:171,197); -1: exchange timed out
-    rs[RES_FEASCOUNT] = feas;
-    rs[RES_ARGMIN] = __ldcg(gat + best * gstride + b * plen + PART_ARGMIN) + 1.0;   // 1-based like Julia
-    rs[RES_RHO] = rho;
-    rs[RES_ETA] = eta;
-  }
-  MPPI_STAMP(2);
-  // stage old nominal + g for the nominal rollout's control-cost term (evaluated
-  // against the OLD U_nom: MPPIUtils.jl:192 runs before main.jl:62 replaces it)
-  const double* Ub = buf.U + size_t(b) * 2 * N;
-  for (int j = t; j < N; j += FINAL_BS) {
-    const R u0 = (SRC == SRC_DWA) ? R(0) : R(Ub[j]), u1 = (SRC == SRC_DWA) ? R(0) : R(Ub[N + j]);
-    sU[4 * j + 0] = u0; sU[4 * j + 1] = u1;
-    sU[4 * j + 2] = p.G00 * u0 + p.G01 * u1;
-    sU[4 * j + 3] = p.G10 * u0 + p.G11 * u1;
+    sRS[RES_ROLLOUTS] = xchg_timeout ? -1.0 : rollouts + 1.0;   // RolloutCount starts at 1 (MPPIUtils.jl:171,197); -1: exchange timed out
+    sRS[RES_FEASCOUNT] = feas;
+    sRS[RES_ARGMIN] = gat[best * gstride + b * plen + PART_ARGMIN] + 1.0;   // 1-based like Julia
+    sRS[RES_RHO] = rho;
+    sRS[RES_ETA] = eta;
   }
   __syncthreads();
-  double* rc = buf.res_control + size_t(b) * 2 * N;
+  MPPI_STAMP(2);
   if (SRC == SRC_DWA) {
-    const size_t arg = size_t(buf.res_scalars[size_t(b) * RES_SCALARS + RES_ARGMIN] - 1.0) - p.k_offset;
+    const size_t arg = size_t(sRS[RES_ARGMIN] - 1.0) - p.k_offset;
     for (int i = t; i < 2 * N; i += FINAL_BS) {
       const int c = i / N, j = i - c * N;
       const double u = buf.cand[size_t(c) * p.K_local + arg];
-      rc[i] = u;
+      sRC[i] = u;
       sNew[2 * j + c] = R(u);
     }
   } else {
@@ -389,28 +416,26 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
     for (int i = t; i < 2 * N; i += FINAL_BS) {
       const int c = i / N, j = i - c * N;
       double s = 0.0;
-      for (int g = 0; g < G; ++g) s += __ldcg(gat + g * gstride + b * plen + PART_HDR + i) * s_scale[g];
+      for (int g = 0; g < G; ++g) s += gat[g * gstride + b * plen + PART_HDR + i] * s_scale[g];
       const double u = s / eta;
-      rc[i] = u;
+      sRC[i] = u;
       sNew[2 * j + c] = R(u);
     }
   }
   __syncthreads();
   MPPI_STAMP(3);
   // Final nominal rollout, TrajectoryRollout(MPPI, MPPICtrl) (MPPIUtils.jl:192).  Only the
-  // state recurrence is sequential: thread 0 integrates x_0..x_N into shared memory, then the
-  // N+1 states are costed / tested / exported in parallel and summed in horizon order.
-  constexpr int NX = Model::NX, ROW = Model::NX + 2;   // state, sin(heading), cos(heading)
+  // state recurrence is sequential (NominalStates); then the N+1 states are costed / tested /
+  // exported in parallel and summed in horizon order.
   R* sX = sNew + 2 * N;                 // [N+1][ROW]
   R* sC = sX + (N + 1) * ROW;           // [N+1][3]: stage+control cost, bound violation, hits
-  NominalStates<Model>::run(p, buf.x0 + size_t(b) * MPPI_MAX_NX, sNew, sX, sC, N, t);
+  NominalStates<Model>::run(p, s_x0, sNew, sX, sC, N, t);
   MPPI_STAMP(4);
-  double* tr = buf.res_traj + size_t(b) * (N + 1) * NX;   // col-major (N+1) x n_x
   for (int j = t; j <= N; j += FINAL_BS) {
     const R* row = sX + j * ROW;
     Model veh;
 #pragma unroll
-    for (int i = 0; i < NX; ++i) { veh.s[i] = row[i]; tr[size_t(i) * (N + 1) + j] = double(row[i]); }
+    for (int i = 0; i < NX; ++i) { veh.s[i] = row[i]; sTR[size_t(i) * (N + 1) + j] = double(row[i]); }
     R c = R(0), v = R(0);
     int hits = 0;
     if (j < N) {
@@ -428,41 +453,50 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
   }
   __syncthreads();
   MPPI_STAMP(5);
-  R stage = R(0), viol = R(0), fh = R(0);
   if (t < 32) {   // fixed-shape tree over the horizon: lanes stride over j, then a shuffle tree
+    R stage = R(0), viol = R(0), fh = R(0);
     for (int j = t; j <= N; j += 32) { stage += sC[3 * j]; viol += sC[3 * j + 1]; fh += sC[3 * j + 2]; }
     stage = warp_sum(stage); viol = warp_sum(viol); fh = warp_sum(fh);
+    if (t == 0) {
+      const R gx0 = sX[0] - p.goal[0], gy0 = sX[1] - p.goal[1];
+      const R d0 = gx0 * gx0 + gy0 * gy0;
+      const int hits = int(fh);
+      const R gx = sX[N * ROW] - p.goal[0], gy = sX[N * ROW + 1] - p.goal[1];
+      const R term = Math<R>::div(gx * gx + gy * gy, d0) * p.term_scale;
+      const R cost = stage + p.slack * viol + p.obs_pen * R(hits) + term;
+      const bool feas = (hits == 0 && !(viol > R(0)));
+      sRS[RES_COST] = double(cost);
+      sRS[RES_FEASIBLE] = feas ? 1.0 : 0.0;
+      sRS[RES_FLAGS] = double((feas ? MPPI_FLAG_FEASIBLE : 0) | (hits ? MPPI_FLAG_COLLIDED : 0) | ((viol > R(0)) ? MPPI_FLAG_OOB : 0));
+    }
+  }
+  __syncthreads();
+  MPPI_STAMP(6);
+  // one burst out: device result arrays, and for B == 1 the caller-visible mapped host block
+  // (posted PCIe writes, no D2H memcpy node; the host spins on host_seq instead of a stream synchronise)
+  double* rs = buf.res_scalars + size_t(b) * RES_SCALARS;
+  double* rc = buf.res_control + size_t(b) * 2 * N;
+  double* tr = buf.res_traj + size_t(b) * (N + 1) * NX;   // col-major (N+1) x n_x
+  const bool to_host = p.B == 1 && buf.host_res != nullptr;
+  const uint32_t flag = uint32_t(seq_all + 1ull);   // host side: wait_step (mppi_pipeline.cuh)
+  for (int i = t; i < n_res; i += FINAL_BS) {
+    const double v = sRS[i];
+    if (to_host) ll_store(buf.host_res + i, v, flag);
+    if (i < RES_SCALARS) rs[i] = v;
+    else if (i < RES_SCALARS + 2 * N) rc[i - RES_SCALARS] = v;
+    else tr[i - RES_SCALARS - 2 * N] = v;
   }
   if (t == 0) {
-    const R gx0 = sX[0] - p.goal[0], gy0 = sX[1] - p.goal[1];
-    const R d0 = gx0 * gx0 + gy0 * gy0;
-    const int hits = int(fh);
-    const R gx = sX[N * ROW] - p.goal[0], gy = sX[N * ROW + 1] - p.goal[1];
-    const R term = Math<R>::div(gx * gx + gy * gy, d0) * p.term_scale;
-    const R cost = stage + p.slack * viol + p.obs_pen * R(hits) + term;
-    double* rs = buf.res_scalars + size_t(b) * RES_SCALARS;
-    const bool feas = (hits == 0 && !(viol > R(0)));
-    rs[RES_COST] = double(cost);
-    rs[RES_FEASIBLE] = feas ? 1.0 : 0.0;
-    rs[RES_FLAGS] = double((feas ? MPPI_FLAG_FEASIBLE : 0) | (hits ? MPPI_FLAG_COLLIDED : 0) | ((viol > R(0)) ? MPPI_FLAG_OOB : 0));
-    MPPI_STAMP(6);
-    if (b == 0) *buf.iter += 1;   // next step draws fresh Philox noise
+    if (PHASES & PH_PARTIAL) buf.scratch[b] = fresh_scratch(p.K_local);   // last consumer of the scratch: re-arm it for the next step
+    if (b == 0) {
+      *buf.iter = iter0 + 1u;   // next step draws fresh Philox noise
+      *buf.seq = seq0 + 1ull;
+      *buf.host_seq = seq0 + 1ull;
+    }
   }
-  if (p.B == 1) {
-    // Results go straight to the caller-visible mapped host block (posted PCIe writes, no D2H
-    // memcpy node); the host spins on host_seq instead of a stream synchronise.
-    __syncthreads();
-    if (buf.host_res) {
-      const int n_res = RES_SCALARS + 2 * N + (N + 1) * NX;   // scalars | U_new | nominal trajectory, contiguous
-      for (int i = t; i < n_res; i += FINAL_BS) buf.host_res[i] = buf.res_scalars[i];
-    }
-    __threadfence_system();
-    __syncthreads();
-    if (t == 0) {
-      const unsigned long long done = *buf.seq + 1ull;
-      *buf.seq = done;
-      *buf.host_seq = done;
-    }
+  if (t == FINAL_BS - 32 && b == 0) {
+#pragma unroll
+    for (int i = 0; i < 7; ++i) buf.dbg[i] = s_clk[i];
   }
   trace_end(buf.dbg, buf.trace, 2);
 }

@@ -22,7 +22,7 @@ for _ in range(20):
     t0=c[8]; spans.append([(c[8+2*i]-t0, c[9+2*i]-t0) for i in range(3)])
 print('in-graph spans ns (start,end) rollout/update/finalize, median:', np.median(np.array(spans),axis=0).tolist())
 mp.set_profiling(0)
-ck=mp.phase_clocks(); pass
+ck=mp.phase_clocks()
 print('finalize phase cycles', [ck[i+1]-ck[i] for i in range(6)], 'total', ck[6]-ck[0])
 
 # ---- host-side cost of the three reference-facing calls (main.jl:59-61) ----

@@ -55,7 +55,7 @@ class Result(C.Structure):
     """mppi_result_t"""
 
     _fields_ = [
-        ("Control", C.POINTER(_d)), ("Traj", C.POINTER(_d)),
+        ("Control", C.c_void_p), ("Traj", C.c_void_p),   # double*: plain addresses, so the per-step path assigns ints
         ("cost", _d),
         ("feasible", _i), ("rollout_count", _i), ("feasible_count", _i), ("argmin_index", _i),
         ("rho", _d), ("eta", _d), ("time_s", _d),

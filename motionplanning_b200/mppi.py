@@ -99,6 +99,19 @@ class MPPISearcher:  # types.jl:46-50
         self.s = MPPISetting()
         self.p = MPPIPlanner(self)
         self.r = MPPIResult()
+        # Per-step fast path (main.jl:59-61 runs these three calls every 20 ms): staging buffers whose
+        # addresses are taken once, prototypes that take plain addresses, one reusable result struct.
+        # Building a ctypes pointer object per call costs more than the copy it describes.
+        lib, vp = self._lib, C.c_void_p
+        self._hv = self._h.value
+        self._x0_buf = np.zeros(cfg.n_x, dtype=np.float64)
+        self._u_buf = np.zeros((cfg.N, 2), dtype=np.float64, order="F")
+        self._x0_ptr, self._u_ptr = self._x0_buf.ctypes.data, self._u_buf.ctypes.data
+        self._f_set_x0 = C.CFUNCTYPE(C.c_int32, vp, vp, C.c_int32)(("mppi_set_x0", lib))
+        self._f_set_nominal = C.CFUNCTYPE(C.c_int32, vp, vp, C.c_int32, C.c_int32)(("mppi_set_nominal", lib))
+        self._f_step = C.CFUNCTYPE(C.c_int32, vp, vp, vp)(("mppi_step", lib))
+        self._res = capi.Result()
+        self._res_ptr = C.addressof(self._res)
 
     # -- plumbing ---------------------------------------------------------
     def _check(self, rc):
@@ -109,6 +122,7 @@ class MPPISearcher:  # types.jl:46-50
         if getattr(self, "_h", None) and self._h.value:
             self._lib.mppi_destroy(self._h)
             self._h = capi._H()
+            self._hv = None
 
     def __del__(self):
         try:
@@ -179,7 +193,7 @@ class MPPISearcher:  # types.jl:46-50
         ctrl = np.empty((N, 2), dtype=np.float64, order="F")
         traj = np.empty((N + 1, nx), dtype=np.float64, order="F")
         res = capi.Result()
-        res.Control, res.Traj = _dptr(ctrl), _dptr(traj)
+        res.Control, res.Traj = ctrl.ctypes.data, traj.ctypes.data
         self._check(self._lib.mppi_fetch_result(self._h, C.byref(res)))
         _store(self, res, ctrl, traj)
 
@@ -218,7 +232,7 @@ class MPPISearcher:  # types.jl:46-50
         ctrl = np.empty((N, 2), dtype=np.float64, order="F")
         traj = np.empty((N + 1, nx), dtype=np.float64, order="F")
         res = capi.Result()
-        res.Control, res.Traj = _dptr(ctrl), _dptr(traj)
+        res.Control, res.Traj = ctrl.ctypes.data, traj.ctypes.data
         self._check(self._lib.mppi_step_combine(self._h, arr, len(partials), C.byref(res)))
         _store(self, res, ctrl, traj)
 
@@ -370,6 +384,11 @@ def defineMPPINominalControl(mppi, *args):
     """defineMPPINominalControl! (setup.jl:70-80): (U) or (U, Sigma)."""
     U = np.asarray(args[0], dtype=np.float64)
     mppi.s.NominalControl = U
+    if len(args) == 1 and U.shape == mppi._u_buf.shape:  # the per-step call (main.jl:60)
+        mppi._u_buf[...] = U
+        if mppi._f_set_nominal(mppi._hv, mppi._u_ptr, U.shape[0], 2):
+            mppi._check(1)
+        return
     Uf = np.asfortranarray(U)
     if U.ndim == 3:  # (N, m, B): instance-major blocks of col-major N x m
         Uf = np.ascontiguousarray(np.transpose(U, (2, 1, 0)))
@@ -385,6 +404,11 @@ def ShiftInitialCondition(mppi, X0):
     """ShiftInitialCondition (MPPIUtils.jl:24-27)."""
     X0 = np.asarray(X0, dtype=np.float64)
     mppi.s.X0 = X0
+    if X0.shape == mppi._x0_buf.shape:  # the per-step call (main.jl:59)
+        mppi._x0_buf[...] = X0
+        if mppi._f_set_x0(mppi._hv, mppi._x0_ptr, X0.shape[0]):
+            mppi._check(1)
+        return
     a = np.ascontiguousarray(X0 if X0.ndim == 1 else X0.T)  # (B, n_x) rows == n_x x B col-major
     mppi._check(mppi._lib.mppi_set_x0(mppi._h, _dptr(a), X0.shape[0]))
 
@@ -395,8 +419,13 @@ def MPPIPlan(mppi, noise=None):
     N, nx = cfg.N, cfg.n_x
     ctrl = np.empty((N, 2), dtype=np.float64, order="F")
     traj = np.empty((N + 1, nx), dtype=np.float64, order="F")
-    res = capi.Result()
-    res.Control, res.Traj = _dptr(ctrl), _dptr(traj)
+    res = mppi._res
+    res.Control, res.Traj = ctrl.ctypes.data, traj.ctypes.data
+    if noise is None:
+        if mppi._f_step(mppi._hv, None, mppi._res_ptr):
+            mppi._check(1)
+        _store(mppi, res, ctrl, traj)
+        return None
     nptr = None
     if noise is not None:
         want = np.float64 if cfg.precision == capi.FP64 else np.float32

@@ -121,6 +121,13 @@ static int create_impl(mppi_handle* h) {
   h->plen = PART_HDR + 2 * c.N;
   int ks = (h->K_local + 2047) / 2048;
   h->ksplit = ks < 1 ? 1 : (ks > 64 ? 64 : ks);
+  {   // enough update blocks for ~2 waves of 4 per SM, and no more: extra blocks only repeat the prologue
+    const int ngroups = (c.N + UPDATE_JG - 1) / UPDATE_JG;
+    const long long per_j = (long long)c.B * h->ksplit;
+    long long js = (1184 + per_j - 1) / per_j;
+    h->jsplit = int(js < 1 ? 1 : (js > ngroups ? ngroups : js));
+    if (const char* e = getenv("MPPI_UPDATE_JSPLIT")) { const int v = atoi(e); if (v >= 1 && v <= ngroups) h->jsplit = v; }
+  }
   h->cutoff = c.feasibility_count < c.K;
   {
     int variant = c.rollout_variant;

@@ -50,7 +50,7 @@ struct mppi_handle {
   mppi_config_t cfg;
   std::string err;
   cudaStream_t stream = nullptr;
-  int K_local = 0, ksplit = 1, plen = 0;
+  int K_local = 0, ksplit = 1, jsplit = 1, plen = 0;   // update_kernel grid = (ksplit, jsplit, B)
   bool cutoff = false;
   bool packed = false;   // rollout carries two samples per thread as f32x2 (FP32, even K_local)
   std::vector<double> circles, blocks;   // host copies (3 x Mc, 5 x Mp col-major)

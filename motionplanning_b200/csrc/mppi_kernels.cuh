@@ -14,6 +14,8 @@ constexpr int ROLLOUT_BS = 64;   // 65,536 samples = 1024 CTAs = 6.9 per SM: one
 constexpr int UPDATE_BS = 256;
 constexpr int UPDATE_JG = 4;
 constexpr int FINAL_BS = 1024;  // 32 warps: the partial tree covers 128 columns per pass with 4 per warp
+constexpr int FINAL_BS_BATCH = 128;   // batched instances (B >= FINAL_BATCH_MIN_B): occupancy over latency
+constexpr int FINAL_BATCH_MIN_B = 64;
 constexpr int CUTOFF_BS = 1024;
 
 

@@ -31,16 +31,21 @@ template <> inline const StaticParams<float>& params_of<float>(const mppi_handle
 template <> inline const StaticParams<double>& params_of<double>(const mppi_handle* h) { return h->pd; }
 
 // long horizons need more than the default 48 KB of dynamic shared memory: opt in once per instantiation
-template <class R, class Model, int SRC, int PHASES>
-cudaError_t launch_finalize(int B, size_t smem, cudaStream_t s, const StaticParams<R>& p, const Buffers<R>& buf) {
+template <class R, class Model, int SRC, int PHASES, int BS>
+cudaError_t launch_finalize_bs(int B, size_t smem, cudaStream_t s, const StaticParams<R>& p, const Buffers<R>& buf) {
   static size_t allowed = 48 * 1024;
   if (smem > allowed) {
-    cudaError_t e = cudaFuncSetAttribute(finalize_kernel<R, Model, SRC, PHASES>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    cudaError_t e = cudaFuncSetAttribute(finalize_kernel<R, Model, SRC, PHASES, BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     if (e != cudaSuccess) return e;
     allowed = smem;
   }
-  finalize_kernel<R, Model, SRC, PHASES><<<B, FINAL_BS, smem, s>>>(p, buf);
+  finalize_kernel<R, Model, SRC, PHASES, BS><<<B, BS, smem, s>>>(p, buf);
   return cudaSuccess;
+}
+template <class R, class Model, int SRC, int PHASES>
+cudaError_t launch_finalize(int B, size_t smem, cudaStream_t s, const StaticParams<R>& p, const Buffers<R>& buf) {
+  if ((PHASES & PH_XCHG) == 0 && B >= FINAL_BATCH_MIN_B) return launch_finalize_bs<R, Model, SRC, PHASES, FINAL_BS_BATCH>(B, smem, s, p, buf);
+  return launch_finalize_bs<R, Model, SRC, PHASES, FINAL_BS>(B, smem, s, p, buf);
 }
 
 template <class R, class Model, int SRC>
@@ -90,8 +95,10 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
     }
     if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[1], s));
     if (SRC != SRC_DWA) {
-      dim3 ug(h->ksplit, (N + UPDATE_JG - 1) / UPDATE_JG, B);
-      update_kernel<R><<<ug, UPDATE_BS, 0, s>>>(p, buf);
+      const int ngroups = (N + UPDATE_JG - 1) / UPDATE_JG;
+      dim3 ug(h->ksplit, h->jsplit, B);
+      const size_t smemR = size_t((ngroups + h->jsplit - 1) / h->jsplit) * (UPDATE_BS / 32) * 2 * UPDATE_JG * sizeof(R);
+      update_kernel<R><<<ug, UPDATE_BS, smemR, s>>>(p, buf);
       h->launches++;
     }
     if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[2], s));

@@ -27,90 +27,109 @@ template <> struct Pair<double> {
 // the 1/eta normalisation is applied once in finalize).  A K x (N*m) streaming
 // reduction: each eps element is read exactly once, 16 B per lane per load,
 // UPDATE_JG independent loads in flight per lane; weights are recomputed from
-// the (L2-resident) costs, never materialised.  HBM/L2-bound; no tensor cores —
+// the (L1/L2-resident) costs, never materialised.  HBM/L2-bound; no tensor cores —
 // this is a GEMV-shaped contraction with arithmetic intensity ~0.5 flop/B.
-// grid = (ksplit, ceil(N/UPDATE_JG), B); deterministic: fixed partition, fixed
+// grid = (ksplit, jsplit, B): a block owns one sample chunk and walks the groups of UPDATE_JG
+// horizon rows jg = blockIdx.y, blockIdx.y + jsplit, ...; per group each warp leaves its tree sum
+// in shared memory and streams on (no barrier), one barrier and one fold at the end.  With one
+// instance jsplit = the number of groups (one group per block, most blocks in flight); with
+// thousands of small instances jsplit = 1, so a block streams its instance's whole eps slab instead
+// of paying launch + prologue + reduction per 32 KB.  Deterministic: fixed partition, fixed
 // tree, partials summed in fixed order by finalize (no float atomics).
 // ---------------------------------------------------------------------------
 template <class R>
 __global__ void __launch_bounds__(UPDATE_BS) update_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) {
-  __shared__ R s_red[UPDATE_BS / 32][2 * UPDATE_JG + 1];
+  extern __shared__ __align__(16) unsigned char upd_smem[];
+  constexpr int NW = UPDATE_BS / 32, COLS = 2 * UPDATE_JG;
+  R* s_red = reinterpret_cast<R*>(upd_smem);   // [local groups][NW][COLS]
+  __shared__ R s_eta[NW];
   const int b = blockIdx.z, N = p.N, K = p.K_local;
   trace_begin(buf.dbg, buf.trace, 1);
-  const int j0 = blockIdx.y * UPDATE_JG;
   const Scratch sc = buf.scratch[b];
   const int keff = sc.k_eff;
   const R rho = key_cost(sc.rho_key, R(0));
   int chunk = (K + gridDim.x - 1) / gridDim.x;
   chunk = (chunk + 1) & ~1;
   const int k0 = blockIdx.x * chunk, k1 = min(k0 + chunk, keff);
-  const bool lead = (blockIdx.y == 0);
   const bool vec_ok = (K & 1) == 0;
-
-  R n0[UPDATE_JG], n1[UPDATE_JG], acc0[UPDATE_JG], acc1[UPDATE_JG];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int ngroups = (N + UPDATE_JG - 1) / UPDATE_JG;
   const double* Ub = buf.U + size_t(b) * 2 * N;
-#pragma unroll
-  for (int jj = 0; jj < UPDATE_JG; ++jj) {
-    const int j = min(j0 + jj, N - 1);
-    n0[jj] = R(Ub[j]); n1[jj] = R(Ub[N + j]);
-    acc0[jj] = R(0); acc1[jj] = R(0);
-  }
-  R eta = R(0);
   const R* cs = buf.costs + size_t(b) * K;
   const R* eb = buf.eps + size_t(b) * N * K * 2;
-  for (int k = k0 + 2 * threadIdx.x; k < k1; k += 2 * UPDATE_BS) {
-    const bool two = (k + 1 < k1);
-    const R c0 = cs[k], c1 = two ? cs[k + 1] : R(0);
-    const R w0 = Math<R>::exp((rho - c0) * p.inv_lambda);
-    const R w1 = two ? Math<R>::exp((rho - c1) * p.inv_lambda) : R(0);
-    if (lead) {
-      eta += w0 + w1;
-      if (sizeof(R) == 8) {   // FP64 key carries no index: first index with cost == rho
-        if (c0 == rho) atomicMin(&buf.scratch[b].argmin, (unsigned int)k);
-        if (two && c1 == rho) atomicMin(&buf.scratch[b].argmin, (unsigned int)(k + 1));
-      }
-    }
-    Pair<R> e[UPDATE_JG];
+  R eta = R(0);
+
+  int gl = 0;
+  for (int jg = blockIdx.y; jg < ngroups; jg += gridDim.y, ++gl) {
+    const int j0 = jg * UPDATE_JG;
+    const bool lead = (jg == 0);   // the block that owns group 0 also sums the weights
+    R n0[UPDATE_JG], n1[UPDATE_JG], acc0[UPDATE_JG], acc1[UPDATE_JG];
 #pragma unroll
     for (int jj = 0; jj < UPDATE_JG; ++jj) {
       const int j = min(j0 + jj, N - 1);
-      const R* src = eb + (size_t(j) * K + k) * 2;
-      if (two && vec_ok) e[jj].load(src);
-      else { e[jj].load1(src); if (two) { Pair<R> t; t.load1(src + 2); e[jj].v.z = t.v.x; e[jj].v.w = t.v.y; } }
+      n0[jj] = R(Ub[j]); n1[jj] = R(Ub[N + j]);
+      acc0[jj] = R(0); acc1[jj] = R(0);
+    }
+    for (int k = k0 + 2 * threadIdx.x; k < k1; k += 2 * UPDATE_BS) {
+      const bool two = (k + 1 < k1);
+      const R c0 = cs[k], c1 = two ? cs[k + 1] : R(0);
+      const R w0 = Math<R>::exp((rho - c0) * p.inv_lambda);
+      const R w1 = two ? Math<R>::exp((rho - c1) * p.inv_lambda) : R(0);
+      if (lead) {
+        eta += w0 + w1;
+        if (sizeof(R) == 8) {   // FP64 key carries no index: first index with cost == rho
+          if (c0 == rho) atomicMin(&buf.scratch[b].argmin, (unsigned int)k);
+          if (two && c1 == rho) atomicMin(&buf.scratch[b].argmin, (unsigned int)(k + 1));
+        }
+      }
+      Pair<R> e[UPDATE_JG];
+#pragma unroll
+      for (int jj = 0; jj < UPDATE_JG; ++jj) {
+        const int j = min(j0 + jj, N - 1);
+        const R* src = eb + (size_t(j) * K + k) * 2;
+        if (two && vec_ok) e[jj].load(src);
+        else { e[jj].load1(src); if (two) { Pair<R> t; t.load1(src + 2); e[jj].v.z = t.v.x; e[jj].v.w = t.v.y; } }
+      }
+#pragma unroll
+      for (int jj = 0; jj < UPDATE_JG; ++jj) {
+        const R ua0 = Math<R>::fmin(Math<R>::fmax(n0[jj] + e[jj].v.x, p.CL[0]), p.CU[0]);
+        const R ua1 = Math<R>::fmin(Math<R>::fmax(n1[jj] + e[jj].v.y, p.CL[1]), p.CU[1]);
+        const R ub0 = Math<R>::fmin(Math<R>::fmax(n0[jj] + e[jj].v.z, p.CL[0]), p.CU[0]);
+        const R ub1 = Math<R>::fmin(Math<R>::fmax(n1[jj] + e[jj].v.w, p.CL[1]), p.CU[1]);
+        acc0[jj] += w0 * ua0 + w1 * ub0;
+        acc1[jj] += w0 * ua1 + w1 * ub1;
+      }
     }
 #pragma unroll
     for (int jj = 0; jj < UPDATE_JG; ++jj) {
-      const R ua0 = Math<R>::fmin(Math<R>::fmax(n0[jj] + e[jj].v.x, p.CL[0]), p.CU[0]);
-      const R ua1 = Math<R>::fmin(Math<R>::fmax(n1[jj] + e[jj].v.y, p.CL[1]), p.CU[1]);
-      const R ub0 = Math<R>::fmin(Math<R>::fmax(n0[jj] + e[jj].v.z, p.CL[0]), p.CU[0]);
-      const R ub1 = Math<R>::fmin(Math<R>::fmax(n1[jj] + e[jj].v.w, p.CL[1]), p.CU[1]);
-      acc0[jj] += w0 * ua0 + w1 * ub0;
-      acc1[jj] += w0 * ua1 + w1 * ub1;
+      acc0[jj] = warp_sum(acc0[jj]);
+      acc1[jj] = warp_sum(acc1[jj]);
+    }
+    if (lane == 0) {
+      R* dst = s_red + (size_t(gl) * NW + wid) * COLS;
+#pragma unroll
+      for (int jj = 0; jj < UPDATE_JG; ++jj) { dst[2 * jj] = acc0[jj]; dst[2 * jj + 1] = acc1[jj]; }
     }
   }
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-#pragma unroll
-  for (int jj = 0; jj < UPDATE_JG; ++jj) {
-    acc0[jj] = warp_sum(acc0[jj]);
-    acc1[jj] = warp_sum(acc1[jj]);
-  }
-  eta = warp_sum(eta);
-  if (lane == 0) {
-#pragma unroll
-    for (int jj = 0; jj < UPDATE_JG; ++jj) { s_red[wid][2 * jj] = acc0[jj]; s_red[wid][2 * jj + 1] = acc1[jj]; }
-    s_red[wid][2 * UPDATE_JG] = eta;
+  const bool has_lead = (blockIdx.y == 0);
+  if (has_lead) {
+    eta = warp_sum(eta);
+    if (lane == 0) s_eta[wid] = eta;
   }
   __syncthreads();
-  if (threadIdx.x < 2 * UPDATE_JG + 1) {
+  for (int i = threadIdx.x; i < gl * COLS; i += UPDATE_BS) {   // fold the warps' sums, one output per thread
+    const int g = i / COLS, col = i - g * COLS;
     R s = R(0);
 #pragma unroll
-    for (int w = 0; w < UPDATE_BS / 32; ++w) s += s_red[w][threadIdx.x];
-    if (threadIdx.x == 2 * UPDATE_JG) {
-      if (lead) buf.eta_part[size_t(b) * gridDim.x + blockIdx.x] = s;
-    } else {
-      const int j = j0 + (threadIdx.x >> 1);
-      if (j < N) buf.Spart[((size_t(b) * gridDim.x + blockIdx.x) * N + j) * 2 + (threadIdx.x & 1)] = s;
-    }
+    for (int w = 0; w < NW; ++w) s += s_red[(size_t(g) * NW + w) * COLS + col];
+    const int j = (blockIdx.y + g * gridDim.y) * UPDATE_JG + (col >> 1);
+    if (j < N) buf.Spart[((size_t(b) * gridDim.x + blockIdx.x) * N + j) * 2 + (col & 1)] = s;
+  }
+  if (has_lead && threadIdx.x == 0) {
+    R s = R(0);
+#pragma unroll
+    for (int w = 0; w < NW; ++w) s += s_eta[w];
+    buf.eta_part[size_t(b) * gridDim.x + blockIdx.x] = s;
   }
   trace_end(buf.dbg, buf.trace, 1);
 }
@@ -209,7 +228,9 @@ struct NominalStates<Kin5<R>> {
 };
 
 // ---------------------------------------------------------------------------
-// finalize_kernel.  One block per instance.
+// finalize_kernel.  One block per instance: BS = FINAL_BS threads for a single instance (latency:
+// 32 warps cover the partial tree in one pass), FINAL_BS_BATCH when there are more instances than
+// SMs (throughput: many small blocks per SM instead of one 1024-thread block at a time).
 //   PH_PARTIAL: sum the update partials in fixed order -> this rank's
 //               (rho, eta, argmin, counts, S) against its LOCAL rho.
 //   PH_COMBINE: fold all ranks' partials in rank order with the rescale
@@ -220,14 +241,14 @@ struct NominalStates<Kin5<R>> {
 enum { PH_PARTIAL = 1, PH_COMBINE = 2, PH_XCHG = 4 };
 // phase clocks, written out with the results; stamped by a lane of the LAST warp: an `if (t == 0)` ahead
 // of a warp-collective section gets threaded into that section's warp test and splits warp 0 (see NominalStates)
-#define MPPI_STAMP(i) do { if (t == FINAL_BS - 32) s_clk[i] = clock64(); } while (0)
+#define MPPI_STAMP(i) do { if (t == BS - 32) s_clk[i] = clock64(); } while (0)
 __device__ __forceinline__ Scratch fresh_scratch(int K_local) {
   Scratch fresh;
   fresh.rho_key = ~0ull; fresh.argmin = ~0u; fresh.feasible_count = 0; fresh.k_eff = K_local; fresh.pad = 0;
   return fresh;
 }
-template <class R, class Model, int SRC, int PHASES>
-__global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) {
+template <class R, class Model, int SRC, int PHASES, int BS>
+__global__ void __launch_bounds__(BS) finalize_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) {
   // Everything this block produces is staged in shared memory and leaves in one burst at the end:
   // a global store followed by a barrier, or a read-back of a value the block just stored, costs
   // an L2 round trip (~1,000 cycles, more across the die boundary), and the old form chained six.
@@ -261,7 +282,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
     // old nominal + g for the nominal rollout's control-cost term (evaluated against the OLD
     // U_nom: MPPIUtils.jl:192 runs before main.jl:62 replaces it)
     const double* Ub = buf.U + size_t(b) * 2 * N;
-    for (int j = t; j < N; j += FINAL_BS) {
+    for (int j = t; j < N; j += BS) {
       const R u0 = (SRC == SRC_DWA) ? R(0) : R(Ub[j]), u1 = (SRC == SRC_DWA) ? R(0) : R(Ub[N + j]);
       sU[4 * j + 0] = u0; sU[4 * j + 1] = u1;
       sU[4 * j + 2] = p.G00 * u0 + p.G01 * u1;
@@ -281,7 +302,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
       __syncthreads();
       if (sizeof(R) == 8) {
         const R* cs = buf.costs + size_t(b) * p.K_local;
-        for (int k = t; k < p.K_local; k += FINAL_BS)
+        for (int k = t; k < p.K_local; k += BS)
           if (cs[k] == rho) atomicMin(&s_arg, (unsigned int)k);
         __syncthreads();
       }
@@ -299,7 +320,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
         const int lane = t & 31, wid = t >> 5, ks_n = buf.ksplit;
         const R* Sp = buf.Spart + size_t(b) * ks_n * N * 2;
         const R* Ep = buf.eta_part + size_t(b) * ks_n;
-        constexpr int NW = FINAL_BS / 32, CB = 4;    // CB columns per warp in flight (independent loads + trees)
+        constexpr int NW = BS / 32, CB = 4;    // CB columns per warp in flight (independent loads + trees)
         for (int col0 = wid; col0 <= 2 * N; col0 += NW * CB) {   // col = c*N + j; col == 2N: eta
           double s[CB];
 #pragma unroll
@@ -355,7 +376,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
     const unsigned long long step = seq_all + 1ull;   // ranks step in lockstep, so this agrees everywhere
     const int par = int(step & 1ull);
     const uint32_t flag = uint32_t(step);
-    for (int i = t; i < plen; i += FINAL_BS) {
+    for (int i = t; i < plen; i += BS) {
       const double v = sOwn[i];
       for (int g = 0; g < G; ++g) ll_store(&buf.peers[g]->line[par][me][i], v, flag);
     }
@@ -363,7 +384,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
     if (t == 0) s_timeout = 0;
     __syncthreads();
     const unsigned long long t0 = globaltimer_ns();
-    for (int i = t; i < G * plen; i += FINAL_BS) {
+    for (int i = t; i < G * plen; i += BS) {
       const int g = i / plen, e = i - g * plen;
       const uint4* src = &buf.peers[me]->line[par][g][e];
       double v = 0.0;
@@ -405,7 +426,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
   MPPI_STAMP(2);
   if (SRC == SRC_DWA) {
     const size_t arg = size_t(sRS[RES_ARGMIN] - 1.0) - p.k_offset;
-    for (int i = t; i < 2 * N; i += FINAL_BS) {
+    for (int i = t; i < 2 * N; i += BS) {
       const int c = i / N, j = i - c * N;
       const double u = buf.cand[size_t(c) * p.K_local + arg];
       sRC[i] = u;
@@ -413,7 +434,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
     }
   } else {
     const double eta = s_hdr[0];
-    for (int i = t; i < 2 * N; i += FINAL_BS) {
+    for (int i = t; i < 2 * N; i += BS) {
       const int c = i / N, j = i - c * N;
       double s = 0.0;
       for (int g = 0; g < G; ++g) s += gat[g * gstride + b * plen + PART_HDR + i] * s_scale[g];
@@ -431,7 +452,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
   R* sC = sX + (N + 1) * ROW;           // [N+1][3]: stage+control cost, bound violation, hits
   NominalStates<Model>::run(p, s_x0, sNew, sX, sC, N, t);
   MPPI_STAMP(4);
-  for (int j = t; j <= N; j += FINAL_BS) {
+  for (int j = t; j <= N; j += BS) {
     const R* row = sX + j * ROW;
     Model veh;
 #pragma unroll
@@ -479,7 +500,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
   double* tr = buf.res_traj + size_t(b) * (N + 1) * NX;   // col-major (N+1) x n_x
   const bool to_host = p.B == 1 && buf.host_res != nullptr;
   const uint32_t flag = uint32_t(seq_all + 1ull);   // host side: wait_step (mppi_pipeline.cuh)
-  for (int i = t; i < n_res; i += FINAL_BS) {
+  for (int i = t; i < n_res; i += BS) {
     const double v = sRS[i];
     if (to_host) ll_store(buf.host_res + i, v, flag);
     if (i < RES_SCALARS) rs[i] = v;
@@ -494,7 +515,7 @@ __global__ void __launch_bounds__(FINAL_BS) finalize_kernel(const __grid_constan
       *buf.host_seq = seq0 + 1ull;
     }
   }
-  if (t == FINAL_BS - 32 && b == 0) {
+  if (t == BS - 32 && b == 0) {
 #pragma unroll
     for (int i = 0; i < 7; ++i) buf.dbg[i] = s_clk[i];
   }

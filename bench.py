@@ -342,6 +342,21 @@ def run_ours(a, rank, world, local_rank):
         k_us.append(mppi.timings_us())
     mppi.set_profiling(False)
     k_us = np.median(np.array(k_us[2:]), axis=0)
+    # ---- the same kernels inside the replayed graph: %globaltimer first-block-in / last-block-out spans
+    #      (mppi_set_profiling(2)); free of the launch and event gaps an eager bracket includes ----
+    g_us = None
+    if not batched:
+        spans = []
+        for i in range(14):
+            l2_flush()
+            mppi.set_profiling(2)
+            mppi.step_async(adopt=False)
+            mppi.sync()
+            c = mppi.phase_clocks()
+            if i >= 2:
+                spans.append([(c[9 + 2 * j] - c[8 + 2 * j]) * 1e-3 for j in range(3)] + [(c[13] - c[8]) * 1e-3])
+        mppi.set_profiling(0)
+        g_us = np.median(np.array(spans), axis=0)
     fp32_peak = mppi.measure_fp32_peak()
     peaks, peak_src = measured_peaks()
     F = sc.flop_per_sample_step(kw["model"], len(circles), len(blocks))
@@ -370,12 +385,18 @@ def run_ours(a, rank, world, local_rank):
                             "ShiftInitialCondition + defineMPPINominalControl + MPPIPlan (host buffers, synchronous)")},
             "gpu_launches": int(launches),
             "kernels_us": {"rollout_cost": float(k_us[0]), "softmin_update": float(k_us[1]), "finalize_nominal": float(k_us[2]),
-                           "step_eager": float(k_us[3])},
+                           "step_eager": float(k_us[3]),
+                           "source": "CUDA events around eager launches on the library stream, L2 flushed, median of 10"},
+            "kernels_us_in_graph": None if g_us is None else {
+                "rollout_cost": float(g_us[0]), "softmin_update": float(g_us[1]), "finalize_nominal": float(g_us[2]),
+                "rollout_start_to_finalize_end": float(g_us[3]),
+                "source": "%globaltimer spans written by the kernels themselves inside the replayed graph (mppi_set_profiling(2))"},
             "roofline": {"kernel": "rollout_kernel", "bound": "fp32", "achieved": roll_tflops, "peak": fp32_peak,
                          "unit": "TFLOP/s", "frac": roll_tflops / fp32_peak if fp32_peak else None,
                          "traffic": NCU_TRAFFIC.get(a.config, (None, None))[0] if world == 1 else None,
                          "traffic_source": "profiles/r01_ncu_*.md (ncu --set full, per launch)",
                          "flop_per_sample_step": F,
+                         "frac_in_graph": None if g_us is None or not fp32_peak else local_units * F / (g_us[0] * 1e-6) / 1e12 / fp32_peak,
                          "peak_source": "FFMA-chain probe measured in this run (mppi_measure_fp32_peak)"},
             "roofline_update": {"kernel": "update_kernel", "bound": "hbm", "achieved": upd_gbs, "peak": peaks.get("hbm_gbs"),
                                 "unit": "GB/s", "frac": upd_gbs / peaks["hbm_gbs"],

@@ -94,7 +94,7 @@ struct mppi_handle {
   mppi::PeerWindow** d_peers = nullptr;          // device copy of peer_ptr
   bool p2p = false;                              // exchange in-kernel over peer memory instead of NCCL
   // profiling
-  cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // step begin | rollout end | update end | finalize end | step end | inputs staged
   int profiling = 0;   // 0 off | 1 eager launches bracketed by events | 2 graph replay, kernels stamp %globaltimer
   float us[4] = {0, 0, 0, 0};
   int64_t launches = 0;

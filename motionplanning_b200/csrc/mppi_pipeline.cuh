@@ -75,6 +75,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   if (v & V_ADOPT)
     MPPI_CUDA(h, cudaMemcpyAsync(h->d_in + size_t(B) * MPPI_MAX_NX, h->d_res + size_t(B) * RES_SCALARS,
                                  size_t(B) * 2 * N * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  if (timed == 1) MPPI_CUDA(h, cudaEventRecord(h->ev[5], s));   // the rollout's interval starts after the inputs are staged
   if (v & V_LOCAL) {
     bool launched = false;
     if constexpr (std::is_same<R, float>::value) {

@@ -4,7 +4,7 @@ import motionplanning_b200 as m
 from motionplanning_b200 import scenarios as sc
 capi=m.capi
 args,kw,circles,blocks=sc.config(1)
-kw.update(precision=capi.FP32, noise_mode=capi.NOISE_PHILOX)
+kw.update(precision=capi.FP32, noise_mode=capi.NOISE_PHILOX, use_cuda_graph=int(os.environ.get('PROBE_GRAPH', '1')))
 mp=m.defineMPPI(*args,**kw); m.defineMPPIobs(mp,circles)
 m.MPPIPlan(mp)
 for _ in range(4): mp.step_async(adopt=True)

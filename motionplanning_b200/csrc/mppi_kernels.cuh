@@ -173,8 +173,11 @@ __device__ __forceinline__ void rollout_horizon(const StaticParams<typename Math
 // packed FP32 pipe (K_local must be even; chosen by the host for large sample counts).
 // One-sample FP32 threads are capped at 146 registers (7 CTAs of 64 per SM = 448 threads) so that
 // 65,536 samples fit ONE wave on 148 SMs; a second, nearly empty wave would cost a full CTA time.
+#ifndef MPPI_PACKED_KIN_MINB
+#define MPPI_PACKED_KIN_MINB 7
+#endif
 template <class V, class Model, int SRC>
-__global__ void __launch_bounds__(ROLLOUT_BS, sizeof(typename Math<V>::S) == 8 ? 1 : (Math<V>::LANES == 1 ? 7 : 5))
+__global__ void __launch_bounds__(ROLLOUT_BS, sizeof(typename Math<V>::S) == 8 ? 1 : (Math<V>::LANES == 1 ? 7 : (Model::NX == 5 ? MPPI_PACKED_KIN_MINB : 5)))
 rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, const Buffers<typename Math<V>::S> buf) {
   using M = Math<V>;
   using R = typename M::S;

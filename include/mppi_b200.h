@@ -191,6 +191,32 @@ int32_t mppi_get_noise(mppi_handle_t* h, void* eps);
  * float [n_samples][N+1][2]; re-rolls those samples on device */
 int32_t mppi_get_sample_xy(mppi_handle_t* h, int32_t stride, float* xy, int32_t* n_samples);
 
+/* ---- closed loop on the device ------------------------
+ * The driver loop of OptimalControl/MPPI/main.jl:45-47,58-83 without host round trips: every MPC
+ * iteration (ShiftInitialCondition + defineMPPINominalControl! + MPPIPlan, :59-62) is followed on
+ * the same stream by a plant kernel that holds U_new with zero order (Constant{Previous}
+ * interpolation of U_new over time_serial = range(0, T, N) sampled at range(0, update_time,
+ * plant_steps), :45-46,65-67) and integrates VehicleDynamics with explicit Euler for plant_steps
+ * steps of plant_dt in FP64 (:76-78), appends [t; states] to the history (:79), stops the episode
+ * inside goal_radius of the goal (:80-82) and hands the new state to the next iteration as X0. */
+typedef struct mppi_closed_loop {
+  uint32_t struct_size;
+  int32_t max_iters;     /* MPC iterations; main.jl:58 runs floor(15/dt_plant)/plant_steps = 150 */
+  int32_t plant_steps;   /* update_idx = floor(update_time / plant_dt) = 100 (main.jl:20) */
+  int32_t shift_nominal; /* 0: NominalControls = mppi.r.Control as the reference does (:62);
+                            k > 0: conventional warm start, U_nom[j] = U_new[min(j + k, N - 1)] */
+  double plant_dt;       /* dt of the plant, 1e-3 (main.jl:19) */
+  double update_time;    /* 0.1 (main.jl:18) */
+  double goal_radius;    /* 6 (main.jl:80) */
+} mppi_closed_loop_t;
+int32_t mppi_closed_loop_default(mppi_closed_loop_t* opt);
+/* Runs from the handle's current X0 / nominal.  states_his: (1 + n_x) x (1 + max_iters * plant_steps)
+ * col-major, column = [t; states] = one row of MPPITrajectory.csv (main.jl:87), first column
+ * [0; X0] (:48); *n_cols = columns written.  iter_log (may be NULL): 4 x max_iters col-major
+ * {nominal cost, feasible, RolloutCount, rho} per iteration; *n_iters = iterations that ran. */
+int32_t mppi_run_closed_loop(mppi_handle_t* h, const mppi_closed_loop_t* opt, double* states_his,
+                             int32_t* n_cols, double* iter_log, int32_t* n_iters);
+
 /* batched multi-instance step (config 5): x0s n_x x B, Us N x m x B in,
  * Us_out N x m x B, costs_out B (nominal rollout cost), feasible_out B */
 int32_t mppi_step_batched(mppi_handle_t* h, const double* x0s, const double* Us,

@@ -16,7 +16,7 @@
 module MPPIB200
 
 export defineMPPI, defineMPPIobs!, defineMPPIblocks!, defineMPPINominalControl!,
-       ShiftInitialCondition, MPPIPlan, MPPISearcher
+       ShiftInitialCondition, MPPIPlan, MPPISearcher, MPPIClosedLoop
 
 const LIB = get(ENV, "MPPI_B200_LIB", joinpath(@__DIR__, "..", "motionplanning_b200", "csrc", "libmppi_b200.so"))
 const MAX_NX = 8
@@ -148,6 +148,32 @@ function MPPIPlan(mppi::MPPISearcher; noise = nothing)                          
     r.cost = c.cost; r.RolloutCount = c.rollout_count; r.FeasibleTrajCount = c.feasible_count
     r.time = c.time_s                                                                  # :199-200
     return nothing
+end
+
+# mppi_closed_loop_t
+struct ClosedLoop
+    struct_size::UInt32
+    max_iters::Int32; plant_steps::Int32; shift_nominal::Int32
+    plant_dt::Float64; update_time::Float64; goal_radius::Float64
+end
+
+# The whole driver loop of main.jl:58-83 in one call: returns states_his exactly as main.jl builds it
+# ((1 + numStates) x columns, column = [t; states]; CSV.write(..., Tables.table(states_his')) as :87)
+# and the per-iteration log (4 x iterations: nominal cost, feasible, RolloutCount, rho).
+function MPPIClosedLoop(mppi::MPPISearcher; max_iters = nothing, shift_nominal = 0)
+    d = Ref{ClosedLoop}()
+    ccall((:mppi_closed_loop_default, LIB), Int32, (Ref{ClosedLoop},), d)
+    o = d[]
+    iters = max_iters === nothing ? o.max_iters : Int32(max_iters)
+    o = ClosedLoop(o.struct_size, iters, o.plant_steps, Int32(shift_nominal), o.plant_dt, o.update_time, o.goal_radius)
+    his = zeros(1 + mppi.s.numStates, 1 + iters * o.plant_steps)
+    log = zeros(4, iters)
+    ncols = Ref{Int32}(0); niters = Ref{Int32}(0)
+    check(mppi.h, ccall((:mppi_run_closed_loop, LIB), Int32,
+                        (Ptr{Cvoid}, Ref{ClosedLoop}, Ptr{Float64}, Ref{Int32}, Ptr{Float64}, Ref{Int32}),
+                        mppi.h, o, his, ncols, log, niters))
+    mppi.s.X0 = his[2:end, ncols[]]
+    return his[:, 1:ncols[]], log[:, 1:niters[]]
 end
 
 end # module

@@ -15,4 +15,5 @@ from .mppi import (  # noqa: F401
     defineMPPIblocks,
     defineMPPINominalControl,
     defineMPPIobs,
+    write_trajectory_csv,
 )

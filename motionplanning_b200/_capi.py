@@ -73,6 +73,15 @@ class Partial(C.Structure):
     ]
 
 
+class ClosedLoop(C.Structure):
+    """mppi_closed_loop_t"""
+
+    _fields_ = [
+        ("struct_size", C.c_uint32), ("max_iters", _i), ("plant_steps", _i), ("shift_nominal", _i),
+        ("plant_dt", _d), ("update_time", _d), ("goal_radius", _d),
+    ]
+
+
 _P = C.POINTER
 _H = C.c_void_p
 
@@ -94,6 +103,8 @@ SIGNATURES = {
     "mppi_adopt_nominal": (_i, [_H]),
     "mppi_step_async": (_i, [_H, _i]),
     "mppi_sync": (_i, [_H]),
+    "mppi_closed_loop_default": (_i, [_P(ClosedLoop)]),
+    "mppi_run_closed_loop": (_i, [_H, _P(ClosedLoop), _P(_d), _P(_i), _P(_d), _P(_i)]),
     "mppi_fetch_result": (_i, [_H, _P(Result)]),
     "mppi_get_costs": (_i, [_H, _P(_d)]),
     "mppi_get_flags": (_i, [_H, _P(C.c_uint8)]),

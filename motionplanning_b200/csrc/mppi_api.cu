@@ -99,9 +99,9 @@ int32_t mppi_destroy(mppi_handle_t* h) {
   if (h->d_window) cudaFree(h->d_window);
   if (h->d_peers) cudaFree(h->d_peers);
   void* dev[] = {h->d_in, h->d_eps, h->d_costs, h->d_flags, h->d_scratch, h->d_scratch_tmpl, h->d_iter, h->d_Spart,
-                 h->d_eta_part, h->d_partial, h->d_gathered, h->d_res, h->d_cand, h->d_dbg, h->d_seq};
+                 h->d_eta_part, h->d_partial, h->d_gathered, h->d_res, h->d_cand, h->d_dbg, h->d_seq, h->d_his, h->d_iterlog, h->d_pstate};
   for (void* p : dev) if (p) cudaFree(p);
-  void* host[] = {h->h_in, h->h_res, h->h_partial, h->h_gathered, h->h_seq, h->h_ll};
+  void* host[] = {h->h_in, h->h_res, h->h_partial, h->h_gathered, h->h_seq, h->h_ll, h->h_pdone};
   for (void* p : host) if (p) cudaFreeHost(p);
   for (auto& e : h->ev) if (e) cudaEventDestroy(e);
   if (h->stream) cudaStreamDestroy(h->stream);

@@ -120,6 +120,7 @@ struct Buffers {
   int n_ranks;
   int rank;
   PeerWindow* const* peers;   // [n_ranks] exchange windows of all ranks (own + IPC-mapped peers), or nullptr
+  const int* halt;      // closed loop: nonzero once the episode is over; the step's kernels then do nothing (nullptr otherwise)
   int trace;            // 1: kernels stamp %globaltimer at first-CTA start / last-CTA end into dbg[8..]
 };
 

@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "mppi_update.cuh"
+#include "mppi_plant.cuh"
 
 namespace mppi {
 
@@ -72,6 +73,11 @@ struct mppi_handle {
   unsigned long long* d_dbg = nullptr;   // [16] finalize phase clocks
   unsigned long long* d_seq = nullptr;   // completed-step counter
   unsigned long long* h_seq = nullptr;   // mapped pinned: completion flag written by finalize
+  // closed loop (mppi_run_closed_loop): plant kernel arguments baked into the V_PLANT graphs
+  mppi::PlantArgs plant = {};
+  int shift_k = 0;
+  double* d_his = nullptr; double* d_iterlog = nullptr; int* d_pstate = nullptr; int* h_pdone = nullptr;
+  int his_cap = 0, log_cap = 0;
   unsigned long long seq_launched = 0;   // steps (finalize<COMBINE>) enqueued so far
   // pinned host mirrors
   double* h_in = nullptr;
@@ -210,6 +216,7 @@ Buffers<R> make_buffers(const mppi_handle* h) {
   b.rank = h->rank;
   b.peers = h->p2p ? h->d_peers : nullptr;
   b.trace = h->profiling == 2 ? 1 : 0;
+  b.halt = nullptr;
   return b;
 }
 

@@ -192,6 +192,7 @@ rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, cons
   const int b = blockIdx.y;
   const int N = p.N;
   const int k = (blockIdx.x * ROLLOUT_BS + threadIdx.x) * LANES;   // first sample of this thread
+  if (buf.halt && *buf.halt) return;   // closed loop already at its goal (uniform across the grid)
   trace_begin(buf.dbg, buf.trace, 0);
   if (threadIdx.x == ROLLOUT_BS - 1) sHot.fill(p);
   for (int i = threadIdx.x; i < 8 * p.n_blocks; i += ROLLOUT_BS) sBlk[i] = (&p.blk[0][0])[i];
@@ -272,6 +273,7 @@ __global__ void __launch_bounds__(CUTOFF_BS) cutoff_kernel(const __grid_constant
   __shared__ unsigned int s_arg[CUTOFF_BS / 32];
   const int b = blockIdx.x, t = threadIdx.x;
   const int K = p.K_local;
+  if (buf.halt && *buf.halt) return;
   const uint8_t* fl = buf.flags + size_t(b) * K;
   const R* cs = buf.costs + size_t(b) * K;
   const int chunk = (K + CUTOFF_BS - 1) / CUTOFF_BS;

@@ -23,7 +23,9 @@ enum {
   V_H2D_X0 = 1024,      // pinned x0 only -> device
   V_H2D_U = 2048,       // pinned U_nom only -> device
   V_HOST_RES = 4096,    // B == 1: finalize writes the result block to mapped host memory (no D2H node)
-  V_XFINAL = 8192       // finalize<PARTIAL|XCHG|COMBINE>: softmin all-gather in-kernel over NVLink peer memory
+  V_XFINAL = 8192,      // finalize<PARTIAL|XCHG|COMBINE>: softmin all-gather in-kernel over NVLink peer memory
+  V_PLANT = 16384,      // closed loop: plant kernel behind finalize advances X0 on the device (mppi_plant.cuh)
+  V_SHIFT = 32768       // closed loop: U_nom <- U_new shifted by shift_k knots (instead of V_ADOPT's plain copy)
 };
 
 template <class R> const StaticParams<R>& params_of(const mppi_handle* h);
@@ -56,6 +58,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   const int B = h->cfg.B, N = h->cfg.N, K = h->K_local, nx = h->cfg.n_x;
   cudaStream_t s = h->stream;
   if ((v & V_HOST_RES) && B == 1) buf.host_res = reinterpret_cast<uint4*>(h->h_ll);
+  if (v & V_PLANT) buf.halt = h->d_pstate + 1;
   const size_t in_bytes = size_t(B) * (MPPI_MAX_NX + 2 * N) * sizeof(double);
   const size_t res_bytes = size_t(B) * (RES_SCALARS + 2 * N) * sizeof(double);
   const size_t smemU = (size_t(N) * 4 + size_t(8) * p.n_blocks) * sizeof(R);   // nominal + wall table
@@ -75,6 +78,10 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   if (v & V_ADOPT)
     MPPI_CUDA(h, cudaMemcpyAsync(h->d_in + size_t(B) * MPPI_MAX_NX, h->d_res + size_t(B) * RES_SCALARS,
                                  size_t(B) * 2 * N * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  if (v & V_SHIFT) {
+    shift_nominal_kernel<<<1, 256, 0, s>>>(h->d_in + size_t(B) * MPPI_MAX_NX, h->d_res + size_t(B) * RES_SCALARS, N, h->shift_k);
+    h->launches++;
+  }
   if (timed == 1) MPPI_CUDA(h, cudaEventRecord(h->ev[5], s));   // the rollout's interval starts after the inputs are staged
   if (v & V_LOCAL) {
     bool launched = false;
@@ -137,6 +144,10 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
     h->launches++;
   }
   if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[3], s));
+  if (v & V_PLANT) {
+    plant_kernel<typename Rebind<Model, double>::type><<<1, 32, 0, s>>>(h->pd, h->plant);
+    h->launches++;
+  }
   if (v & V_D2H_RES) {
     const size_t traj_bytes = (B == 1) ? size_t(N + 1) * nx * sizeof(double) : 0;   // contiguous with the scalars
     MPPI_CUDA(h, cudaMemcpyAsync(h->h_res, h->d_res, res_bytes + traj_bytes, cudaMemcpyDeviceToHost, s));
@@ -179,6 +190,8 @@ inline int kernels_in(const mppi_handle* h, int v) {
   if (v & V_XFINAL) n++;
   if (v & V_PARTIAL) n++;
   if (v & V_COMBINE) n++;
+  if (v & V_PLANT) n++;
+  if (v & V_SHIFT) n++;
   return n;
 }
 

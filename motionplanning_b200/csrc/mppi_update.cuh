@@ -44,6 +44,7 @@ __global__ void __launch_bounds__(UPDATE_BS) update_kernel(const __grid_constant
   R* s_red = reinterpret_cast<R*>(upd_smem);   // [local groups][NW][COLS]
   __shared__ R s_eta[NW];
   const int b = blockIdx.z, N = p.N, K = p.K_local;
+  if (buf.halt && *buf.halt) return;
   trace_begin(buf.dbg, buf.trace, 1);
   const Scratch sc = buf.scratch[b];
   const int keff = sc.k_eff;
@@ -269,6 +270,10 @@ __global__ void __launch_bounds__(BS) finalize_kernel(const __grid_constant__ St
   __shared__ double s_x0[MPPI_MAX_NX];
   __shared__ unsigned long long s_clk[8];
   double* part = buf.partial + size_t(b) * plen;
+  if (buf.halt && *buf.halt) {   // closed loop already at its goal: keep the step count in line with the host, nothing else
+    if (t == 0 && b == 0 && (PHASES & PH_COMBINE)) { const unsigned long long done = *buf.seq + 1ull; *buf.seq = done; *buf.host_seq = done; }
+    return;
+  }
   MPPI_STAMP(0);
   trace_begin(buf.dbg, buf.trace, 2);
   // loads that do not depend on this step's kernels go first, so their latency hides behind the partial tree

@@ -185,6 +185,28 @@ class MPPISearcher:  # types.jl:46-50
     def sync(self):
         self._check(self._lib.mppi_sync(self._h))
 
+    def run_closed_loop(self, max_iters=None, plant_steps=None, shift_nominal=0, plant_dt=None, update_time=None,
+                        goal_radius=None):
+        """The driver loop of OptimalControl/MPPI/main.jl:58-83 on the device: MPPIPlan, then the 1 ms
+        explicit-Euler plant under the zero-order-held new controls, until the goal radius or max_iters.
+        Returns (states_his, iter_log): states_his rows = [t, states...] = the rows of MPPITrajectory.csv
+        (main.jl:87), iter_log rows = [nominal cost, feasible, RolloutCount, rho] per MPC iteration."""
+        o = capi.ClosedLoop()
+        self._check(self._lib.mppi_closed_loop_default(C.byref(o)))
+        for k, v in (("max_iters", max_iters), ("plant_steps", plant_steps), ("plant_dt", plant_dt),
+                     ("update_time", update_time), ("goal_radius", goal_radius)):
+            if v is not None:
+                setattr(o, k, v)
+        o.shift_nominal = int(shift_nominal)
+        nx = self._cfg.n_x
+        his = np.zeros((1 + o.max_iters * o.plant_steps, 1 + nx), dtype=np.float64)   # C rows == col-major columns
+        log = np.zeros((o.max_iters, 4), dtype=np.float64)
+        n_cols, n_iters = C.c_int32(0), C.c_int32(0)
+        self._check(self._lib.mppi_run_closed_loop(self._h, C.byref(o), _dptr(his), C.byref(n_cols), _dptr(log),
+                                                   C.byref(n_iters)))
+        self.s.X0 = his[n_cols.value - 1, 1:].copy()
+        return his[:n_cols.value].copy(), log[:n_iters.value].copy()
+
     def adopt_nominal(self):
         self._check(self._lib.mppi_adopt_nominal(self._h))
 
@@ -447,3 +469,11 @@ def _store(mppi, res, ctrl, traj):
     r.FeasibleTrajCount = res.feasible_count  # :198
     r.time = res.time_s  # :200
     r.argmin, r.rho, r.eta = res.argmin_index, res.rho, res.eta
+
+
+def write_trajectory_csv(path, states_his):
+    """CSV.write("MPPITrajectory.csv", Tables.table(states_his'), writeheader=false) (main.jl:87):
+    one row per plant step, [t, states...], no header, shortest round-trip float formatting."""
+    with open(path, "w") as f:
+        for row in np.asarray(states_his, dtype=np.float64):
+            f.write(",".join(repr(float(v)) for v in row) + "\n")

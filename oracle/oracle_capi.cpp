@@ -149,6 +149,38 @@ int oracle_rungekutta2(const mppi_config_t* cfg, const double* x, const double* 
   return 0;
 }
 
+// The plant side of the closed loop, OptimalControl/MPPI/main.jl:45-47,65-67,76-83, for ONE MPC
+// iteration: controls = Constant{Previous} interpolation of U_new (N x m col-major) over
+// time_serial = range(0, T, length = N) sampled at fined_time_serial = range(0, update_time,
+// length = steps) (:45-46,65-67); then `steps` explicit-Euler steps of VehicleDynamics at plant_dt
+// (:76-78), each appended to the history as [time_idx * dt; states] (:79), stopping inside
+// goal_radius of the goal (:80-82).  x is advanced in place; his is (1 + n_x) x steps col-major.
+// Returns the number of columns written; *done = 1 if the goal test fired.
+int oracle_plant_advance(const mppi_config_t* cfg, double* x, const double* U_new, int steps, double plant_dt,
+                         double update_time, double goal_radius, int time_idx0, double* his, int* done) {
+  Params<double> p = make_params<double>(cfg, nullptr, 0, nullptr, 0);
+  const int N = cfg->N, nx = cfg->n_x;
+  const double knot = N > 1 ? cfg->T / double(N - 1) : 0.0;            // step of range(0, T, length = N)
+  const double fine = steps > 1 ? update_time / double(steps - 1) : 0.0;
+  int ncol = 0;
+  *done = 0;
+  for (int i = 0; i < steps; ++i) {
+    const double tf = double(i) * fine;                                // fined_time_serial[i + 1]
+    int j = 0;                                                         // searchsortedlast(time_serial, tf) - 1
+    while (j + 1 < N && double(j + 1) * knot <= tf) ++j;
+    const double u[2] = {U_new[j], U_new[N + j]};                      // :67 controls[i, :]
+    double dx[MPPI_MAX_NX], cons, cost;
+    vehicle_dynamics(p, x, u, dx, &cons, &cost);                       // :76
+    for (int q = 0; q < nx; ++q) x[q] = x[q] + dx[q] * plant_dt;       // :78
+    his[size_t(ncol) * (1 + nx)] = double(time_idx0 + i + 1) * plant_dt;   // :79
+    for (int q = 0; q < nx; ++q) his[size_t(ncol) * (1 + nx) + 1 + q] = x[q];
+    ++ncol;
+    const double gx = x[0] - cfg->goal[0], gy = x[1] - cfg->goal[1];
+    if (gx * gx + gy * gy <= goal_radius * goal_radius) { *done = 1; break; }   // :80-82
+  }
+  return ncol;
+}
+
 void oracle_get_rectangle_pts(const double* block, double* pts10) { get_rectangle_pts(block, pts10); }
 int oracle_sat(const double* base, int nb, const double* other, int no) {
   return separating_axis_theorem<double>(base, nb, other, no) ? 1 : 0;

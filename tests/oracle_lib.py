@@ -130,6 +130,19 @@ def rungekutta2(cfg, x, u):
     return xn, int(cc[0]), cc[1]
 
 
+def plant_advance(cfg, x, U_new, steps=100, plant_dt=1e-3, update_time=0.1, goal_radius=6.0, time_idx0=0):
+    """main.jl:65-67,76-82 for one MPC iteration: returns (x_next, history rows [t, states], done)."""
+    lib = load()
+    x = np.array(x, dtype=np.float64, copy=True)
+    U = np.asfortranarray(np.asarray(U_new, dtype=np.float64))
+    his = np.zeros((steps, 1 + cfg.n_x))
+    done = C.c_int(0)
+    lib.oracle_plant_advance.restype = C.c_int
+    n = lib.oracle_plant_advance(C.byref(cfg), _d(x), _d(U), C.c_int(steps), C.c_double(plant_dt), C.c_double(update_time),
+                                 C.c_double(goal_radius), C.c_int(time_idx0), _d(his), C.byref(done))
+    return x, his[:n].copy(), bool(done.value)
+
+
 def get_rectangle_pts(block):
     lib = load()
     b = np.ascontiguousarray(block, dtype=np.float64)

@@ -230,6 +230,71 @@ def test_closed_loop_device_resident_equals_host_loop(built):
     assert a.r.cost < 1e4 and a.r.Feasibility == "Feasible"
 
 
+@pytest.mark.parametrize("model_cfg,precision", [(0, capi.FP64), (0, capi.FP32), (3, capi.FP64)])
+def test_closed_loop_on_device_matches_host_loop_with_oracle_plant(built, model_cfg, precision):
+    """mppi_run_closed_loop (main.jl:58-83 as one chain of graph launches, plant kernel behind finalize)
+    against the same loop driven from the host: MPPIPlan per iteration + the ORACLE's plant
+    (oracle_plant_advance, pinned to the reference's MPPITrajectory.csv in test_oracle_golden.py)."""
+    iters, steps = 6, 100
+    args, kw, circles, blocks = sc.config(model_cfg, K=2048, N=30)
+    kw = dict(kw, precision=precision, noise_mode=capi.NOISE_PHILOX)
+    dev = make(args, kw, circles, blocks)
+    host = make(args, kw, circles, blocks)
+    his, log = dev.run_closed_loop(max_iters=iters, plant_steps=steps)
+    cfg = host._cfg
+    x = np.array(args[3], dtype=np.float64)
+    rows = [np.concatenate([[0.0], x])]
+    U = np.zeros((cfg.N, 2))
+    costs = []
+    for it in range(iters):
+        m.ShiftInitialCondition(host, x)
+        m.defineMPPINominalControl(host, U)
+        m.MPPIPlan(host)
+        U = np.array(host.r.Control, copy=True)
+        costs.append(host.r.cost)
+        x, h, done = orc.plant_advance(cfg, x, U, steps=steps, time_idx0=it * steps)
+        rows.extend(h)
+        if done:
+            break
+    ref = np.array(rows)
+    assert his.shape == ref.shape == (1 + iters * steps, 1 + cfg.n_x)
+    assert np.array_equal(his[:, 0], ref[:, 0])
+    scale = np.maximum(1.0, np.abs(ref[:, 1:]).max(axis=0))
+    assert (np.abs(his[:, 1:] - ref[:, 1:]) / scale).max() <= 1e-9
+    assert np.allclose(log[:, 0], costs, rtol=1e-12) and (log[:, 2] == 2048 + 1).all()
+    # the handle carries on from the episode's end state, host mirrors included
+    assert np.abs(np.asarray(dev.s.X0) - ref[-1, 1:]).max() <= 1e-9 * scale.max()
+    m.MPPIPlan(dev)
+    m.ShiftInitialCondition(host, x)
+    m.defineMPPINominalControl(host, U)
+    m.MPPIPlan(host)
+    assert np.abs(dev.r.Control - host.r.Control).max() <= 1e-6
+
+
+def test_closed_loop_stops_at_goal_and_shift_option(built, tmp_path):
+    """Goal test (main.jl:80-82) ends the episode on the device; the history is a valid
+    MPPITrajectory.csv; the optional warm-start shift changes the plan but not the contract."""
+    args, kw, circles, blocks = sc.config(0, K=4096, N=20)
+    kw = dict(kw, noise_mode=capi.NOISE_PHILOX)
+    start = np.array(args[3], dtype=np.float64)
+    start[0] = 95.0                     # 15 m from the goal (110, 0) at 5 m/s: ~1.8 s
+    a = make((args[0], args[1], args[2], start) + tuple(args[4:]), kw, circles, blocks)
+    his, log = a.run_closed_loop(max_iters=40)
+    assert 5 <= len(log) < 40 and len(his) <= 1 + len(log) * 100
+    gx, gy = his[-1, 1] - 110.0, his[-1, 2]
+    assert gx * gx + gy * gy <= 36.0 and ((his[:-1, 1] - 110.0) ** 2 + his[:-1, 2] ** 2 > 36.0).all()
+    assert np.allclose(np.diff(his[:, 0]), 1e-3, atol=1e-12)
+    path = tmp_path / "MPPITrajectory.csv"
+    m.write_trajectory_csv(path, his)
+    back = np.loadtxt(path, delimiter=",")
+    assert np.array_equal(back, his)
+    b = make((args[0], args[1], args[2], start) + tuple(args[4:]), kw, circles, blocks)
+    his_s, log_s = b.run_closed_loop(max_iters=40, shift_nominal=1)
+    assert len(log_s) >= 5 and not np.array_equal(his_s[:len(his)], his[:len(his_s)])
+    g2 = (his_s[-1, 1] - 110.0) ** 2 + his_s[-1, 2] ** 2
+    assert g2 <= 36.0
+
+
 @pytest.mark.parametrize("cfg_idx,K,N", [(1, 65536, 50), (2, 262144, 80), (3, 131072, 100)])
 def test_full_size_properties(built, cfg_idx, K, N):
     """BASELINE.json sizes (cfg4 at the 8-GPU per-rank shard), checked through size-independent

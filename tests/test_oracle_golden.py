@@ -94,3 +94,45 @@ def test_heun_step(built):
     xn, cons, pc = orc.rungekutta2(cfg, x, u)
     np.testing.assert_allclose(xn, x + dt * (k1 + k2) / 2, rtol=0, atol=1e-15)
     assert cons == 1 and pc == c1
+
+
+def test_plant_advance_reproduces_reference_log_rows(built):
+    """oracle_plant_advance (main.jl:65-67,76-79) against the reference's MPPITrajectory.csv rows: one
+    plant step from row k with the controls the log implies gives row k+1, stamped (k+1) * 1 ms."""
+    cfg = capi.default_config()
+    ks, xk, xk1 = _pairs("mppi_plant_pairs.csv")
+    for k, x, xn in list(zip(ks, xk, xk1))[:120]:
+        sr, ax = (xn[6] - x[6]) / DT, (xn[5] - x[5]) / DT
+        U = np.tile([sr, ax], (cfg.N, 1))
+        x1, his, done = orc.plant_advance(cfg, x, U, steps=1, time_idx0=int(k))
+        assert np.abs(x1 - xn).max() <= 1e-12
+        assert his.shape == (1, 8) and his[0, 0] == (int(k) + 1) * DT and np.array_equal(his[0, 1:], x1)
+        assert not done
+
+
+def test_plant_zero_order_hold_and_goal_stop(built):
+    """Constant{Previous} interpolation over time_serial = range(0, T, N) (main.jl:45,65-67) and the
+    6 m goal test (:80-82), against a direct numpy restatement."""
+    cfg = capi.default_config()
+    N, T = cfg.N, cfg.T
+    rng = np.random.default_rng(7)
+    U = np.column_stack([rng.uniform(-0.3, 0.3, N), rng.uniform(-2, 2, N)])
+    x0 = np.array([0.0, 0.0, 0.0, 0.0, 0.0, 5.0, 0.0])
+    steps, upd = 400, 1.0     # long enough to cross several knots of time_serial
+    x1, his, done = orc.plant_advance(cfg, x0, U, steps=steps, update_time=upd)
+    knots = np.linspace(0.0, T, N)
+    fine = np.linspace(0.0, upd, steps)
+    x = x0.copy()
+    for i in range(steps):
+        j = int(np.searchsorted(knots, fine[i], side="right")) - 1
+        dx, _, _ = orc.vehicle_dynamics(cfg, x, U[j])
+        x = x + dx * DT
+        assert np.abs(his[i, 1:] - x).max() <= 1e-12
+    assert len(np.unique([int(np.searchsorted(knots, t, side="right")) - 1 for t in fine])) > 3
+    assert not done and np.abs(x1 - x).max() <= 1e-12
+    # start 6.5 m short of the goal at 5 m/s: the goal test fires after ~0.1 s and cuts the block short
+    near = np.array([cfg.goal[0] - 6.5, cfg.goal[1], 0.0, 0.0, 0.0, 5.0, 0.0])
+    x2, his2, done2 = orc.plant_advance(cfg, near, np.zeros((N, 2)), steps=400)
+    assert done2 and 90 <= len(his2) <= 110
+    assert (his2[-1, 1] - cfg.goal[0]) ** 2 + (his2[-1, 2] - cfg.goal[1]) ** 2 <= 36.0
+    assert (his2[-2, 1] - cfg.goal[0]) ** 2 + (his2[-2, 2] - cfg.goal[1]) ** 2 > 36.0

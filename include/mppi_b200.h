@@ -32,6 +32,7 @@ extern "C" {
 #define MPPI_MAX_NX 8
 #define MPPI_MAX_CIRCLES 64
 #define MPPI_MAX_BLOCKS 32
+#define MPPI_MAX_REF 1024 /* reference-path points (mppi_set_reference_path) */
 #define MPPI_MAX_N 256
 
 /* status codes (the reference's only error path is error(...) in setup.jl:19-39) */
@@ -190,6 +191,14 @@ int32_t mppi_get_noise(mppi_handle_t* h, void* eps);
 /* plot support (MPPIUtils.jl:221-223): xy of every `stride`-th sampled trajectory,
  * float [n_samples][N+1][2]; re-rolls those samples on device */
 int32_t mppi_get_sample_xy(mppi_handle_t* h, int32_t stride, float* xy, int32_t* n_samples);
+
+/* ---- reference-path tracking term (an extension) -------
+ * The reference's MPPI tracks the implicit lane y = 0 (`10*y^2`, vehicledynamics.jl:52, stage_w[5]).
+ * This adds weight * (squared distance to the nearest point of a polyline) to every stage cost,
+ * the nearest point searched in a window [idx, idx + window] that moves forward with the vehicle,
+ * as the reference's tracker does (HybridAstar/src/tracker_utils.jl:36-41, main_Tracker.jl:82-83).
+ * xy: 2 x n col-major, n <= MPPI_MAX_REF; n = 0 removes the term.  MPPI planner: PHILOX noise only. */
+int32_t mppi_set_reference_path(mppi_handle_t* h, const double* xy, int32_t n, double weight, int32_t window);
 
 /* ---- closed loop on the device ------------------------
  * The driver loop of OptimalControl/MPPI/main.jl:45-47,58-83 without host round trips: every MPC

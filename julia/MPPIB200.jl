@@ -16,7 +16,7 @@
 module MPPIB200
 
 export defineMPPI, defineMPPIobs!, defineMPPIblocks!, defineMPPINominalControl!,
-       ShiftInitialCondition, MPPIPlan, MPPISearcher, MPPIClosedLoop
+       ShiftInitialCondition, MPPIPlan, MPPISearcher, MPPIClosedLoop, defineMPPIrefpath!
 
 const LIB = get(ENV, "MPPI_B200_LIB", joinpath(@__DIR__, "..", "motionplanning_b200", "csrc", "libmppi_b200.so"))
 const MAX_NX = 8
@@ -118,6 +118,13 @@ end
 function defineMPPIblocks!(mppi::MPPISearcher, block_list)
     b = Float64[o[i] for i in 1:5, o in block_list]
     check(mppi.h, ccall((:mppi_set_blocks, LIB), Int32, (Ptr{Cvoid}, Ptr{Float64}, Int32), mppi.h, b, size(b, 2)))
+end
+
+# reference polyline for the tracking term: pts is n x 2 [x y] (as ref_pts in main_Tracker.jl:47); empty removes it
+function defineMPPIrefpath!(mppi::MPPISearcher, pts::Matrix{Float64}; weight = 10.0, window = 16)
+    xy = Matrix(transpose(pts))                                                       # 2 x n col-major
+    check(mppi.h, ccall((:mppi_set_reference_path, LIB), Int32, (Ptr{Cvoid}, Ptr{Float64}, Int32, Float64, Int32),
+                        mppi.h, xy, size(xy, 2), weight, window))
 end
 
 function defineMPPINominalControl!(mppi::MPPISearcher, U::Matrix{Float64})            # setup.jl:70-73

@@ -15,5 +15,6 @@ from .mppi import (  # noqa: F401
     defineMPPIblocks,
     defineMPPINominalControl,
     defineMPPIobs,
+    defineMPPIrefpath,
     write_trajectory_csv,
 )

@@ -98,6 +98,7 @@ SIGNATURES = {
     "mppi_set_circles": (_i, [_H, _P(_d), _i]),
     "mppi_set_blocks": (_i, [_H, _P(_d), _i]),
     "mppi_set_goal": (_i, [_H, _P(_d)]),
+    "mppi_set_reference_path": (_i, [_H, _P(_d), _i, _d, _i]),
     "mppi_set_candidates": (_i, [_H, _P(_d), _i, _i]),
     "mppi_step": (_i, [_H, C.c_void_p, _P(Result)]),
     "mppi_adopt_nominal": (_i, [_H]),

@@ -99,7 +99,7 @@ int32_t mppi_destroy(mppi_handle_t* h) {
   if (h->d_window) cudaFree(h->d_window);
   if (h->d_peers) cudaFree(h->d_peers);
   void* dev[] = {h->d_in, h->d_eps, h->d_costs, h->d_flags, h->d_scratch, h->d_scratch_tmpl, h->d_iter, h->d_Spart,
-                 h->d_eta_part, h->d_partial, h->d_gathered, h->d_res, h->d_cand, h->d_dbg, h->d_seq, h->d_his, h->d_iterlog, h->d_pstate};
+                 h->d_eta_part, h->d_partial, h->d_gathered, h->d_res, h->d_cand, h->d_dbg, h->d_seq, h->d_his, h->d_iterlog, h->d_pstate, h->d_ref};
   for (void* p : dev) if (p) cudaFree(p);
   void* host[] = {h->h_in, h->h_res, h->h_partial, h->h_gathered, h->h_seq, h->h_ll, h->h_pdone};
   for (void* p : host) if (p) cudaFreeHost(p);
@@ -274,6 +274,31 @@ int32_t mppi_set_goal(mppi_handle_t* h, const double* goal2) {
   if (!goal2) return fail(h, MPPI_EINVAL, "null goal");
   int rc = quiesce(h); if (rc) return rc;
   h->cfg.goal[0] = goal2[0]; h->cfg.goal[1] = goal2[1];
+  rebuild_params(h);
+  drop_graphs(h);
+  return MPPI_OK;
+}
+
+int32_t mppi_set_reference_path(mppi_handle_t* h, const double* xy, int32_t n, double weight, int32_t window) {
+  H_CHECK(h);
+  if (n < 0 || n > MPPI_MAX_REF) { char b[96]; snprintf(b, sizeof b, "reference path: n (%d) must be in 0..%d", n, MPPI_MAX_REF); return fail(h, MPPI_EINVAL, b); }
+  if (n > 0 && (!xy || !(weight >= 0) || window < 1)) return fail(h, MPPI_EINVAL, "reference path: null points, negative weight or window < 1");
+  if (n > 0 && h->cfg.planner == MPPI_PLANNER_MPPI && h->cfg.noise_mode != MPPI_NOISE_PHILOX)
+    return fail(h, MPPI_EINVAL, "a reference path needs PHILOX noise (the tracking rollout is not built for supplied noise)");
+  int rc = quiesce(h); if (rc) return rc;
+  h->ref_path.assign(xy, xy + size_t(2) * n);
+  h->ref_w = n > 0 ? weight : 0.0;
+  h->ref_window = n > 0 ? window : 0;
+  if (n > 0) {
+    if (!h->d_ref) MPPI_CUDA(h, cudaMalloc(&h->d_ref, size_t(2) * MPPI_MAX_REF * sizeof(double)));
+    if (h->cfg.precision == MPPI_FP64) {
+      MPPI_CUDA(h, cudaMemcpy(h->d_ref, xy, size_t(2) * n * sizeof(double), cudaMemcpyHostToDevice));
+    } else {
+      std::vector<float> f(size_t(2) * n);
+      for (size_t i = 0; i < f.size(); ++i) f[i] = float(xy[i]);
+      MPPI_CUDA(h, cudaMemcpy(h->d_ref, f.data(), f.size() * sizeof(float), cudaMemcpyHostToDevice));
+    }
+  }
   rebuild_params(h);
   drop_graphs(h);
   return MPPI_OK;

@@ -34,6 +34,8 @@ template <class R>
 struct StaticParams {
   int K, K_local, k_offset, N, B;
   int n_circles, n_blocks, planner;
+  int n_ref, ref_window;   // reference-path tracking term (mppi_track.cuh); n_ref == 0: off
+  R ref_w;
   int feasibility_count, n_x;
   uint32_t seed_lo, seed_hi;
   R dt, half_dt, lambda, inv_lambda;
@@ -112,6 +114,7 @@ struct Buffers {
   double* res_control;  // [B][2*N]  col-major N x m
   double* res_traj;     // [B][(N+1)*n_x] col-major (N+1) x n_x
   const double* cand;   // DWA: [K][2] col-major K x m candidates
+  const R* ref;         // [n_ref][2] reference polyline (tracking term)
   uint4* host_res;          // mapped pinned host mirror of the result block (B == 1) as LL lines {lo, flag, hi, flag}, or nullptr
   unsigned long long* seq;  // device count of completed steps
   volatile unsigned long long* host_seq;  // mapped pinned host copy of *seq: the completion flag the host spins on

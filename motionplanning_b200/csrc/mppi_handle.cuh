@@ -74,6 +74,9 @@ struct mppi_handle {
   unsigned long long* d_seq = nullptr;   // completed-step counter
   unsigned long long* h_seq = nullptr;   // mapped pinned: completion flag written by finalize
   // closed loop (mppi_run_closed_loop): plant kernel arguments baked into the V_PLANT graphs
+  std::vector<double> ref_path;   // 2 per point; tracking term
+  double ref_w = 0.0; int ref_window = 0;
+  void* d_ref = nullptr;          // the polyline in the handle's precision
   mppi::PlantArgs plant = {};
   int shift_k = 0;
   double* d_his = nullptr; double* d_iterlog = nullptr; int* d_pstate = nullptr; int* h_pdone = nullptr;
@@ -131,6 +134,7 @@ void build_params(const mppi_handle* h, StaticParams<R>* p) {
   memset(p, 0, sizeof(*p));
   p->K = c.K; p->K_local = h->K_local; p->k_offset = c.k_offset; p->N = c.N; p->B = c.B;
   p->n_circles = int(h->circles.size() / 3); p->n_blocks = int(h->blocks.size() / 5);
+  p->n_ref = int(h->ref_path.size() / 2); p->ref_window = h->ref_window; p->ref_w = R(h->ref_w);
   p->planner = c.planner; p->feasibility_count = c.feasibility_count; p->n_x = c.n_x;
   p->seed_lo = uint32_t(c.seed); p->seed_hi = uint32_t(c.seed >> 32);
   const double dt = c.T / c.N;   // setup.jl:53
@@ -217,6 +221,7 @@ Buffers<R> make_buffers(const mppi_handle* h) {
   b.peers = h->p2p ? h->d_peers : nullptr;
   b.trace = h->profiling == 2 ? 1 : 0;
   b.halt = nullptr;
+  b.ref = static_cast<const R*>(h->d_ref);
   return b;
 }
 

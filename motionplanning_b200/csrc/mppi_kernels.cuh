@@ -6,6 +6,7 @@
 //   finalize_kernel  partial -> (multi-rank) combine -> U_new -> nominal rollout
 #pragma once
 #include "mppi_models.cuh"
+#include "mppi_track.cuh"
 
 namespace mppi {
 
@@ -76,10 +77,10 @@ template <class R, class V> struct Rebind<Dyn7<R>, V> { using type = Dyn7<V>; };
 
 // The horizon loop for the LANES samples of one thread, specialised on the number of circle
 // quads held in registers (NQ >= 0) or reading the circle table (NQ < 0).
-template <class V, class Model, int SRC, int NQ>
+template <class V, class Model, int SRC, int NQ, bool TRACK>
 __device__ __forceinline__ void rollout_horizon(const StaticParams<typename Math<V>::S>& p, const Buffers<typename Math<V>::S>& buf,
                                                 Model& veh, RolloutAcc<V>& acc, const HotParams<typename Math<V>::S, Model::NX>* sHot,
-                                                const typename Math<V>::S* sU, const typename Math<V>::S* sBlk, int b, int k) {
+                                                const typename Math<V>::S* sU, const typename Math<V>::S* sBlk, int b, int k, Tracker<V, TRACK>& trk) {
   using M = Math<V>;
   using S = typename M::S;
   using S2 = typename Vec2<S>::type;
@@ -117,6 +118,7 @@ __device__ __forceinline__ void rollout_horizon(const StaticParams<typename Math
       acc.stage += M::fma(V(nu.z), u0 - V(nu.x), V(nu.w) * (u1 - V(nu.y)));   // lambda*U_nom'*inv(Sigma)*(u-U_nom) (:45)
     }
     acc.stage += veh.stage_cost(hp, u0, u1);       // VehicleDynamics cost at the pre-step state
+    trk.add(acc.stage, veh.s[0], veh.s[1]);        // + tracking term (nothing unless TRACK)
     veh.step(hp, u0, u1);                          // Rungekutta2 (:76-90)
     if (NQ >= 0) acc.hits += circle_hits_regs<V, (NQ > 0 ? NQ : 0)>(hp, veh.s[0], veh.s[1]);   // x_{j+1}: ObstacleEvaluation
     else acc.hits += circle_hits<V>(p, veh.s[0], veh.s[1]);
@@ -176,7 +178,7 @@ __device__ __forceinline__ void rollout_horizon(const StaticParams<typename Math
 #ifndef MPPI_PACKED_KIN_MINB
 #define MPPI_PACKED_KIN_MINB 7
 #endif
-template <class V, class Model, int SRC>
+template <class V, class Model, int SRC, bool TRACK = false>
 __global__ void __launch_bounds__(ROLLOUT_BS, sizeof(typename Math<V>::S) == 8 ? 1 : (Math<V>::LANES == 1 ? 7 : (Model::NX == 5 ? MPPI_PACKED_KIN_MINB : 5)))
 rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, const Buffers<typename Math<V>::S> buf) {
   using M = Math<V>;
@@ -185,6 +187,7 @@ rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, cons
   extern __shared__ __align__(16) unsigned char smem_raw[];
   R* sU = reinterpret_cast<R*>(smem_raw);  // [N][4]: u0, u1, g0, g1
   R* sBlk = sU + 4 * p.N;                  // [n_blocks][8]: wall table
+  R* sRef = sBlk + 8 * p.n_blocks;         // [n_ref][2]: reference polyline (TRACK)
   __shared__ unsigned long long s_key[ROLLOUT_BS / 32];
   __shared__ int s_feas[ROLLOUT_BS / 32];
   __shared__ __align__(16) HotParams<R, Model::NX> sHot;
@@ -196,6 +199,7 @@ rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, cons
   trace_begin(buf.dbg, buf.trace, 0);
   if (threadIdx.x == ROLLOUT_BS - 1) sHot.fill(p);
   for (int i = threadIdx.x; i < 8 * p.n_blocks; i += ROLLOUT_BS) sBlk[i] = (&p.blk[0][0])[i];
+  if (TRACK) for (int i = threadIdx.x; i < 2 * p.n_ref; i += ROLLOUT_BS) sRef[i] = buf.ref[i];
   const bool active = k < p.K_local;
   const double* Ub = buf.U + size_t(b) * 2 * N;
   if (SRC != SRC_DWA) {
@@ -208,6 +212,16 @@ rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, cons
     }
   }
   __syncthreads();
+  Tracker<V, TRACK> trk;
+  if constexpr (TRACK) {   // every sample of the instance starts its window at the point closest to x0
+    __shared__ R s_td[ROLLOUT_BS / 32];
+    __shared__ int s_ti[ROLLOUT_BS / 32];
+    const double* x0t = buf.x0 + size_t(b) * MPPI_MAX_NX;
+    const int i0 = track_start(sRef, p.n_ref, R(x0t[0]), R(x0t[1]), s_td, s_ti);
+    trk.ref = sRef; trk.n = p.n_ref; trk.W = p.ref_window; trk.w = p.ref_w;
+#pragma unroll
+    for (int l = 0; l < LANES; ++l) trk.idx[l] = i0;
+  }
 
   unsigned long long key = 0xFFFFFFFFFFFFFFFFull;
   int n_feas = 0;
@@ -219,12 +233,16 @@ rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, cons
     const V gx0 = veh.s[0] - V(p.goal[0]), gy0 = veh.s[1] - V(p.goal[1]);
     const V d0 = M::fma(gx0, gx0, gy0 * gy0);
     const int nq = (p.n_circles + 3) >> 2;   // warp-uniform: the whole horizon loop is specialised
-    if (sizeof(R) == 8) rollout_horizon<V, Model, SRC, -1>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
-    else if (nq == 0) rollout_horizon<V, Model, SRC, 0>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
-    else if (nq == 1) rollout_horizon<V, Model, SRC, 1>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
-    else if (nq == 2) rollout_horizon<V, Model, SRC, 2>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
-    else rollout_horizon<V, Model, SRC, -1>(p, buf, veh, acc, &sHot, sU, sBlk, b, k);
+    if constexpr (TRACK || sizeof(R) == 8) {
+      rollout_horizon<V, Model, SRC, -1, TRACK>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
+    } else {
+      if (nq == 0) rollout_horizon<V, Model, SRC, 0, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
+      else if (nq == 1) rollout_horizon<V, Model, SRC, 1, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
+      else if (nq == 2) rollout_horizon<V, Model, SRC, 2, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
+      else rollout_horizon<V, Model, SRC, -1, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
+    }
     acc.stage += veh.stage_cost(p, V(0), V(0));      // terminal slot: VehicleDynamics(x_N, [0,0]) (:49,:53)
+    trk.add(acc.stage, veh.s[0], veh.s[1]);
     const V gx = veh.s[0] - V(p.goal[0]), gy = veh.s[1] - V(p.goal[1]);
     const V term = M::div(M::fma(gx, gx, gy * gy), d0) * V(p.term_scale);   // (:54)
     const V cost = M::fma(V(p.slack), acc.viol, M::fma(V(p.obs_pen), M::to_real(acc.hits), acc.stage)) + term;

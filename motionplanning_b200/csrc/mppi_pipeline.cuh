@@ -61,7 +61,9 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   if (v & V_PLANT) buf.halt = h->d_pstate + 1;
   const size_t in_bytes = size_t(B) * (MPPI_MAX_NX + 2 * N) * sizeof(double);
   const size_t res_bytes = size_t(B) * (RES_SCALARS + 2 * N) * sizeof(double);
-  const size_t smemU = (size_t(N) * 4 + size_t(8) * p.n_blocks) * sizeof(R);   // nominal + wall table
+  const size_t smemU = (size_t(N) * 4 + size_t(8) * p.n_blocks + size_t(2) * p.n_ref) * sizeof(R);   // nominal + wall table + reference polyline
+  const bool track = p.n_ref > 0;
+  if (track && SRC == SRC_SUPPLIED) { h->err = "a reference path needs PHILOX noise (the tracking rollout is not built for supplied noise)"; return MPPI_EINVAL; }
 
   if (timed == 1) MPPI_CUDA(h, cudaEventRecord(h->ev[0], s));
   if (v & (V_H2D_IN | V_H2D_X0 | V_H2D_U)) {
@@ -88,13 +90,19 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
     if constexpr (std::is_same<R, float>::value) {
       if (h->packed) {   // two samples per thread on the packed FP32 pipe (mppi_pack.cuh)
         dim3 grid((K + 2 * ROLLOUT_BS - 1) / (2 * ROLLOUT_BS), B);
-        rollout_kernel<f32x2, typename Rebind<Model, f32x2>::type, SRC><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
+        if constexpr (SRC != SRC_SUPPLIED) {
+          if (track) rollout_kernel<f32x2, typename Rebind<Model, f32x2>::type, SRC, true><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
+        }
+        if (!track) rollout_kernel<f32x2, typename Rebind<Model, f32x2>::type, SRC><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
         launched = true;
       }
     }
     if (!launched) {
       dim3 grid((K + ROLLOUT_BS - 1) / ROLLOUT_BS, B);
-      rollout_kernel<R, Model, SRC><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
+      if constexpr (SRC != SRC_SUPPLIED) {
+        if (track) rollout_kernel<R, Model, SRC, true><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
+      }
+      if (!track) rollout_kernel<R, Model, SRC><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
     }
     h->launches++;
     if (h->cutoff && SRC != SRC_DWA) {
@@ -115,7 +123,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   // exchange) in double, then nominal controls, states and per-step costs in R
   const size_t plen = PART_HDR + 2 * size_t(N);
   const size_t smemF = (RES_SCALARS + 2 * size_t(N) + size_t(N + 1) * Model::NX + plen) * sizeof(double) +
-                       (size_t(N) * 6 + size_t(N + 1) * (Model::NX + 2 + 3)) * sizeof(R);
+                       (size_t(N) * 6 + size_t(N + 1) * (Model::NX + 2 + 3 + 1) + size_t(2) * p.n_ref) * sizeof(R);
   const size_t smemX = smemF + size_t(h->n_ranks) * plen * sizeof(double);
   if (v & V_FUSED_FINAL) {
     MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_PARTIAL | PH_COMBINE>(B, smemF, s, p, buf)));

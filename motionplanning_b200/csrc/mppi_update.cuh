@@ -455,7 +455,21 @@ __global__ void __launch_bounds__(BS) finalize_kernel(const __grid_constant__ St
   // exported in parallel and summed in horizon order.
   R* sX = sNew + 2 * N;                 // [N+1][ROW]
   R* sC = sX + (N + 1) * ROW;           // [N+1][3]: stage+control cost, bound violation, hits
+  R* sTrk = sC + 3 * (N + 1);           // [N+1]: tracking term (only with a reference path)
+  R* sRef = sTrk + (N + 1);             // [n_ref][2]
+  const bool track = p.n_ref > 0;
+  if (track) for (int i = t; i < 2 * p.n_ref; i += BS) sRef[i] = buf.ref[i];   // barrier: inside run()
   NominalStates<Model>::run(p, s_x0, sNew, sX, sC, N, t);
+  if (track) {   // the window index is sequential along the horizon: one thread walks it (N+1 scans of W+1 points)
+    __shared__ R s_td[32];
+    __shared__ int s_ti[32];
+    const int i0 = track_start(sRef, p.n_ref, R(s_x0[0]), R(s_x0[1]), s_td, s_ti);
+    if (t == 0) {
+      int idx = i0;
+      for (int j = 0; j <= N; ++j) sTrk[j] = p.ref_w * track_scan(sRef, p.n_ref, p.ref_window, sX[j * ROW], sX[j * ROW + 1], idx);
+    }
+    __syncthreads();
+  }
   MPPI_STAMP(4);
   for (int j = t; j <= N; j += BS) {
     const R* row = sX + j * ROW;
@@ -471,6 +485,7 @@ __global__ void __launch_bounds__(BS) finalize_kernel(const __grid_constant__ St
     } else {
       c = veh.stage_cost(p, R(0), R(0));   // terminal slot (:49,:53)
     }
+    if (track) c += sTrk[j];
     if (j > 0) {   // x_0 is never tested (:40-41)
       hits = circle_hits(p, row[0], row[1]) + block_hits(p, row[0], row[1], row[NX], row[NX + 1]);
       v = bound_violation<R, NX>(p, row);

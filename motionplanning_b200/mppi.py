@@ -402,6 +402,14 @@ def defineMPPIblocks(mppi, block_list):
     mppi._check(mppi._lib.mppi_set_blocks(mppi._h, _dptr(a), a.shape[0]))
 
 
+def defineMPPIrefpath(mppi, pts, weight=10.0, window=16):
+    """Reference-path tracking term (SURVEY.md 8(f) rank 3): `pts` is (n, 2) [x, y] (None / empty removes it);
+    every stage cost gains weight * squared distance to the nearest point of a forward-moving window."""
+    a = np.zeros((0, 2)) if pts is None else np.ascontiguousarray(np.asarray(pts, dtype=np.float64).reshape(-1, 2))
+    mppi.s.ref_path = a
+    mppi._check(mppi._lib.mppi_set_reference_path(mppi._h, _dptr(a), a.shape[0], float(weight), int(window)))
+
+
 def defineMPPINominalControl(mppi, *args):
     """defineMPPINominalControl! (setup.jl:70-80): (U) or (U, Sigma)."""
     U = np.asarray(args[0], dtype=np.float64)

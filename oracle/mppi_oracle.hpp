@@ -61,7 +61,44 @@ struct Params {
   std::vector<R> circles;  // 3 per circle: x, y, r
   std::vector<R> blocks;   // 5 per block: cx, cy, psi, half_len, half_wid
   std::vector<R> wall_pts; // Block2Pts(blocks): 10 per block, [2][5] col-major
+  // reference-path tracking term (an extension, absent from the reference's MPPI)
+  std::vector<R> ref;      // 2 per point: x, y
+  R ref_w = 0;
+  int ref_window = 0;
 };
+
+// ---- tracking term: squared distance to the nearest polyline point inside a moving window -------
+// The reference's MPPI has only the implicit lane y = 0 (`10*y^2`, vehicledynamics.jl:52); its path
+// tracker finds the reference point as the closest of ref_pts[least_idx:maximum_idx], least_idx being
+// the previous closest index (PathPlanning/HybridAstar/src/tracker_utils.jl:36-41, main_Tracker.jl:82-83).
+// Here: window [idx, min(idx + W, n - 1)], first minimum wins (argmin), idx moves to it.
+template <class R>
+R track_scan(const Params<R>& p, R x, R y, int* idx) {
+  const int n = int(p.ref.size() / 2);
+  const int hi = std::min(*idx + p.ref_window, n - 1);
+  R best = std::numeric_limits<R>::infinity();
+  int bi = *idx;
+  for (int i = *idx; i <= hi; ++i) {
+    const R dx = x - p.ref[2 * i], dy = y - p.ref[2 * i + 1];
+    const R d = dx * dx + dy * dy;
+    if (d < best) { best = d; bi = i; }
+  }
+  *idx = bi;
+  return best;
+}
+// the window starts at the point closest to x0 over the WHOLE path (findclosest with the full range)
+template <class R>
+int track_start(const Params<R>& p, R x, R y) {
+  const int n = int(p.ref.size() / 2);
+  R best = std::numeric_limits<R>::infinity();
+  int bi = 0;
+  for (int i = 0; i < n; ++i) {
+    const R dx = x - p.ref[2 * i], dy = y - p.ref[2 * i + 1];
+    const R d = dx * dx + dy * dy;
+    if (d < best) { best = d; bi = i; }
+  }
+  return bi;
+}
 
 // ---- a5: VehicleDynamics, 7-state dynamic bicycle --------------------------
 // OptimalControl/MPPI/src/vehicledynamics.jl:1-54.  State [x,y,v,r,psi,ux,sa],

@@ -17,6 +17,11 @@ struct Rollout {
   R cost_total = 0;
 };
 
+template <class R>
+void d_cost_extra(const Params<R>& p, const R* states, int* tidx, R* acc) {
+  *acc = p.ref_w * track_scan(p, states[0], states[1], tidx);
+}
+
 // ---- a3: TrajectoryRollout — MPPIUtils.jl:31-57 ------------------------------
 // ctrl_list: N x m, row j at [j*m] (already clamped by the caller, :8,:176).
 // nominal:   N x m, same layout (MPPI.s.NominalControl).
@@ -34,6 +39,8 @@ void trajectory_rollout(const Params<R>& p, const R* x0, const R* ctrl_list, con
   for (int i = 0; i < nx; ++i) states[i] = x0[i];  // :37
   if (keep_traj) for (int i = 0; i < nx; ++i) out->states_his[i] = states[i];  // :38
   int hit = 0, boundhit = 0;
+  const bool track = !p.ref.empty();
+  int tidx = track ? track_start(p, states[0], states[1]) : 0;
   // inv(Σ) for the 2x2 case, closed form (MPPIUtils.jl:45 calls inv every step)
   R inv[4] = {0, 0, 0, 0};
   if (p.planner == MPPI_PLANNER_MPPI) {
@@ -50,6 +57,8 @@ void trajectory_rollout(const Params<R>& p, const R* x0, const R* ctrl_list, con
       if (!b_cons) boundhit = 1;
     }
     const R* u = (p.planner == MPPI_PLANNER_DWA) ? ctrl_list : ctrl_list + size_t(j) * p.m;
+    R t_cost = 0;   // tracking term rides with the stage cost, at the pre-step state
+    if (track) d_cost_extra(p, states, &tidx, &t_cost);
     rungekutta2(p, states, u, dt, next, &d_cons, &d_cost);  // :42
     for (int i = 0; i < nx; ++i) states[i] = next[i];        // :43
     constraint_his[j] = d_cons * c_cons * b_cons;            // :44
@@ -62,7 +71,7 @@ void trajectory_rollout(const Params<R>& p, const R* x0, const R* ctrl_list, con
       const R t1 = r0 * inv[2] + r1 * inv[3];  // row * column 2
       ctrl_term = t0 * (u[0] - un[0]) + t1 * (u[1] - un[1]);
     }
-    cost_his[j] = d_cost + b_cost + c_cost + ctrl_term;      // :45
+    cost_his[j] = d_cost + b_cost + c_cost + ctrl_term + t_cost;      // :45 (+ tracking extension)
     if (keep_traj) for (int i = 0; i < nx; ++i) out->states_his[size_t(j + 1) * nx + i] = states[i];  // :46
   }
   {  // terminal slot, :49-53
@@ -70,6 +79,7 @@ void trajectory_rollout(const Params<R>& p, const R* x0, const R* ctrl_list, con
     int d_cons = 1, c_cons = 1, b_cons = 1;
     R d_cost = 0, c_cost = 0, b_cost = 0;
     rungekutta2(p, states, zero_u, dt, next, &d_cons, &d_cost);  // :49 (state discarded)
+    if (track) { R t = 0; d_cost_extra(p, states, &tidx, &t); d_cost = d_cost + t; }
     obstacle_evaluation(p, states, &c_cons, &c_cost, &hit, mg);  // :50
     bound_evaluation(p, states, &b_cons, &b_cost, mg);           // :51
     if (!b_cons) boundhit = 1;

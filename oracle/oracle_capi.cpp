@@ -5,6 +5,12 @@
 
 using namespace oracle;
 
+// reference path for the tracking extension: process-wide, set by oracle_set_reference_path and
+// picked up by every make_params until cleared (n = 0)
+static std::vector<double> g_ref;
+static double g_ref_w = 0.0;
+static int g_ref_window = 0;
+
 template <class R>
 static Params<R> make_params(const mppi_config_t* c, const double* circles, int Mc,
                              const double* blocks, int Mp) {
@@ -28,6 +34,9 @@ static Params<R> make_params(const mppi_config_t* c, const double* circles, int 
   for (int i = 0; i < 5 * Mp; ++i) p.blocks[i] = R(blocks[i]);
   p.wall_pts.resize(size_t(10) * Mp);
   for (int i = 0; i < Mp; ++i) get_rectangle_pts(&p.blocks[5 * i], &p.wall_pts[10 * i]);  // Block2Pts
+  p.ref.resize(g_ref.size());
+  for (size_t i = 0; i < g_ref.size(); ++i) p.ref[i] = R(g_ref[i]);
+  p.ref_w = R(g_ref_w); p.ref_window = g_ref_window;
   return p;
 }
 
@@ -179,6 +188,12 @@ int oracle_plant_advance(const mppi_config_t* cfg, double* x, const double* U_ne
     if (gx * gx + gy * gy <= goal_radius * goal_radius) { *done = 1; break; }   // :80-82
   }
   return ncol;
+}
+
+// xy: 2 x n col-major (x0, y0, x1, y1, ...); n = 0 clears
+void oracle_set_reference_path(const double* xy, int n, double weight, int window) {
+  g_ref.assign(xy, xy + size_t(2) * n);
+  g_ref_w = weight; g_ref_window = window;
 }
 
 void oracle_get_rectangle_pts(const double* block, double* pts10) { get_rectangle_pts(block, pts10); }

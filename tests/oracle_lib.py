@@ -143,6 +143,14 @@ def plant_advance(cfg, x, U_new, steps=100, plant_dt=1e-3, update_time=0.1, goal
     return x, his[:n].copy(), bool(done.value)
 
 
+def set_reference_path(pts=None, weight=10.0, window=16):
+    """Process-wide reference path of the oracle's tracking term; None clears it."""
+    lib = load()
+    a = np.zeros((0, 2)) if pts is None else np.ascontiguousarray(np.asarray(pts, dtype=np.float64).reshape(-1, 2))
+    lib.oracle_set_reference_path.restype = None
+    lib.oracle_set_reference_path(_d(a), C.c_int(a.shape[0]), C.c_double(weight), C.c_int(window))
+
+
 def get_rectangle_pts(block):
     lib = load()
     b = np.ascontiguousarray(block, dtype=np.float64)

@@ -230,6 +230,62 @@ def test_closed_loop_device_resident_equals_host_loop(built):
     assert a.r.cost < 1e4 and a.r.Feasibility == "Feasible"
 
 
+def _wavy_path(n=240):
+    x = np.linspace(-5.0, 115.0, n)
+    return np.column_stack([x, 1.5 * np.sin(x / 12.0)])
+
+
+@pytest.mark.parametrize("model_cfg,precision,variant", [(1, capi.FP64, 0), (1, capi.FP32, 1), (1, capi.FP32, 2),
+                                                          (3, capi.FP64, 0), (3, capi.FP32, 2)])
+def test_reference_path_tracking_term_matches_oracle(built, model_cfg, precision, variant):
+    """the windowed nearest-point tracking term, device (scalar and packed rollout,
+    finalize's nominal costing) against the oracle's restatement on the device's own Philox noise."""
+    K, N = 4096, 40
+    args, kw, circles, blocks = sc.config(model_cfg, K=K, N=N)
+    kw = dict(kw, precision=precision, noise_mode=capi.NOISE_PHILOX, rollout_variant=variant, stage_w=[1, 1, 5, 3, 2, 0.0])
+    U = warm_nominal(N)
+    path = _wavy_path()
+    mppi = make(args, kw, circles, blocks, U)
+    m.MPPIPlan(mppi)
+    plain_costs = mppi.p.costs.copy()
+    m.defineMPPIrefpath(mppi, path, weight=4.0, window=12)
+    m.defineMPPINominalControl(mppi, U)
+    m.MPPIPlan(mppi)
+    eps = mppi.noise()
+    assert (mppi.p.costs > plain_costs.min()).all() and not np.allclose(mppi.p.costs[:64], plain_costs[:64])
+    orc.set_reference_path(path, weight=4.0, window=12)
+    try:
+        ref = orc.plan(orc.make_config(args, kw), circles, blocks, args[3], U, eps.astype(np.float64), capi.FP64,
+                       threads=8, want_margin=True)
+    finally:
+        orc.set_reference_path(None)
+    check(mppi, ref, precision)
+    # removing the path restores the plain cost exactly
+    m.defineMPPIrefpath(mppi, None)
+    m.defineMPPINominalControl(mppi, U)
+    m.MPPIPlan(mppi)
+    assert mppi.r.rho > 0 and np.isfinite(mppi.p.costs).all()
+
+
+def test_reference_path_pulls_the_plan_and_rejects_supplied_noise(built):
+    """A path offset to y = +3 m with the lane term off: a few iterations move the nominal plan's
+    lateral position towards it; supplied-noise handles refuse the term."""
+    args, kw, circles, blocks = sc.config(1, K=16384, N=40)
+    kw = dict(kw, noise_mode=capi.NOISE_PHILOX, stage_w=[1, 1, 5, 3, 2, 0.0])
+    a = make(args, kw, [], [])
+    x = np.linspace(-5, 120, 200)
+    m.defineMPPIrefpath(a, np.column_stack([x, np.full_like(x, 3.0)]), weight=20.0, window=20)
+    for _ in range(12):
+        m.MPPIPlan(a)
+        m.defineMPPINominalControl(a, a.r.Control)
+    assert a.r.Traj[-1, 1] > 1.0            # started at y = 0, plain MPPI stays there
+    b = make(args, dict(kw, noise_mode=capi.NOISE_SUPPLIED), [], [])
+    with pytest.raises(m.MPPIError, match="PHILOX"):
+        m.defineMPPIrefpath(b, np.column_stack([x, x * 0]))
+    with pytest.raises(m.MPPIError):
+        m.defineMPPIrefpath(a, np.zeros((2000, 2)))
+
+
 @pytest.mark.parametrize("model_cfg,precision", [(0, capi.FP64), (0, capi.FP32), (3, capi.FP64)])
 def test_closed_loop_on_device_matches_host_loop_with_oracle_plant(built, model_cfg, precision):
     """mppi_run_closed_loop (main.jl:58-83 as one chain of graph launches, plant kernel behind finalize)

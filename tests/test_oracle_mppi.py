@@ -166,3 +166,33 @@ def test_dwa_plan_argmin(built):
     np.testing.assert_array_equal(ref["Control"], np.tile(cand[k], (20, 1)))
     one = orc.rollout(cfg, sc.CIRCLES, [], sc.X0_DYN, None, np.tile(cand[3], (20, 1)))
     assert one["cost"] == pytest.approx(ref["costs"][3], rel=1e-14)
+
+
+def test_tracking_term_against_numpy_restatement(built):
+    """Oracle's windowed nearest-point term (mppi_oracle.hpp track_scan / track_start) against a direct
+    numpy evaluation along the oracle's own nominal trajectory."""
+    from motionplanning_b200 import scenarios as sc
+    args, kw, circles, blocks = sc.config(0, K=8, N=25)
+    kw = dict(kw, stage_w=[1, 1, 5, 3, 2, 0.0])
+    cfg = orc.make_config(args, kw)
+    rng = np.random.default_rng(3)
+    ctrl = np.column_stack([rng.uniform(-0.3, 0.3, 25), rng.uniform(-1, 1, 25)])
+    base = orc.rollout(cfg, [], [], args[3], None, ctrl)
+    x = np.linspace(-2, 40, 90)
+    path = np.column_stack([x, 0.8 * np.cos(x / 5.0)])
+    W, w = 6, 3.0
+    orc.set_reference_path(path, weight=w, window=W)
+    try:
+        got = orc.rollout(cfg, [], [], args[3], None, ctrl)
+    finally:
+        orc.set_reference_path(None)
+    traj = base["Traj"]
+    idx = int(np.argmin(((path - traj[0, :2]) ** 2).sum(1)))
+    extra = 0.0
+    for j in range(26):
+        hi = min(idx + W, len(path) - 1)
+        d = ((path[idx:hi + 1] - traj[j, :2]) ** 2).sum(1)
+        idx += int(np.argmin(d))
+        extra += w * d.min()
+    assert np.array_equal(got["Traj"], traj)
+    assert got["cost"] - base["cost"] == pytest.approx(extra, rel=1e-12)

@@ -132,6 +132,7 @@ static int create_impl(mppi_handle* h) {
   {
     int variant = c.rollout_variant;
     if (const char* e = getenv("MPPI_ROLLOUT_VARIANT")) variant = atoi(e);
+    if (const char* e = getenv("MPPI_PDL")) h->pdl = atoi(e) != 0;
     const bool can_pack = c.precision == MPPI_FP32 && (h->K_local % 2) == 0;
     // auto: packing halves the warps, so it needs enough samples to keep every SM sub-partition busy
     const long long samples = (long long)h->K_local * c.B;

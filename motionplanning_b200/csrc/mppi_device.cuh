@@ -171,6 +171,13 @@ struct HotParams {
 // math traits
 // ---------------------------------------------------------------------------
 // kernel span tracing (profiling mode 2): dbg[8 + 2*slot] = min start, dbg[9 + 2*slot] = max end, in ns
+// Programmatic dependent launch (sm_90+): a kernel launched with the programmatic-stream-serialization
+// attribute may start while its predecessor still runs; it orders itself with pdl_wait() (returns when
+// the predecessor grid has completed and its writes are visible; a no-op without the attribute), and
+// the predecessor lets it go early with pdl_trigger().  Hides the ~0.8 us launch gap between kernels.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;"); }
+
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));

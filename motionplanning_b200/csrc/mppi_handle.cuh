@@ -77,6 +77,7 @@ struct mppi_handle {
   std::vector<double> ref_path;   // 2 per point; tracking term
   double ref_w = 0.0; int ref_window = 0;
   void* d_ref = nullptr;          // the polyline in the handle's precision
+  bool pdl = true;                // programmatic dependent launches inside the step (env MPPI_PDL=0 disables)
   mppi::PlantArgs plant = {};
   int shift_k = 0;
   double* d_his = nullptr; double* d_iterlog = nullptr; int* d_pstate = nullptr; int* h_pdone = nullptr;

@@ -275,6 +275,7 @@ rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, cons
     if (f) atomicAdd(&buf.scratch[b].feasible_count, f);
   }
   trace_end(buf.dbg, buf.trace, 0);
+  pdl_trigger();
 }
 
 // ---------------------------------------------------------------------------

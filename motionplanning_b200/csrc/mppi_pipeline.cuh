@@ -32,22 +32,35 @@ template <class R> const StaticParams<R>& params_of(const mppi_handle* h);
 template <> inline const StaticParams<float>& params_of<float>(const mppi_handle* h) { return h->pf; }
 template <> inline const StaticParams<double>& params_of<double>(const mppi_handle* h) { return h->pd; }
 
+// Launch `kernel`, optionally as a programmatic dependent of the kernel before it on the stream
+// (pdl_wait / pdl_trigger in mppi_device.cuh).
+template <class P, class Bf>
+cudaError_t launch_step_kernel(void (*kernel)(P, Bf), dim3 grid, dim3 block, size_t smem, cudaStream_t s, bool dependent,
+                               const P& p, const Bf& buf) {
+  cudaLaunchConfig_t lc = {};
+  lc.gridDim = grid; lc.blockDim = block; lc.dynamicSmemBytes = smem; lc.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  lc.attrs = at; lc.numAttrs = dependent ? 1 : 0;
+  return cudaLaunchKernelEx(&lc, kernel, p, buf);
+}
+
 // long horizons need more than the default 48 KB of dynamic shared memory: opt in once per instantiation
 template <class R, class Model, int SRC, int PHASES, int BS>
-cudaError_t launch_finalize_bs(int B, size_t smem, cudaStream_t s, const StaticParams<R>& p, const Buffers<R>& buf) {
+cudaError_t launch_finalize_bs(int B, size_t smem, cudaStream_t s, bool dependent, const StaticParams<R>& p, const Buffers<R>& buf) {
   static size_t allowed = 48 * 1024;
   if (smem > allowed) {
     cudaError_t e = cudaFuncSetAttribute(finalize_kernel<R, Model, SRC, PHASES, BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     if (e != cudaSuccess) return e;
     allowed = smem;
   }
-  finalize_kernel<R, Model, SRC, PHASES, BS><<<B, BS, smem, s>>>(p, buf);
-  return cudaSuccess;
+  return launch_step_kernel(finalize_kernel<R, Model, SRC, PHASES, BS>, dim3(B), dim3(BS), smem, s, dependent, p, buf);
 }
 template <class R, class Model, int SRC, int PHASES>
-cudaError_t launch_finalize(int B, size_t smem, cudaStream_t s, const StaticParams<R>& p, const Buffers<R>& buf) {
-  if ((PHASES & PH_XCHG) == 0 && B >= FINAL_BATCH_MIN_B) return launch_finalize_bs<R, Model, SRC, PHASES, FINAL_BS_BATCH>(B, smem, s, p, buf);
-  return launch_finalize_bs<R, Model, SRC, PHASES, FINAL_BS>(B, smem, s, p, buf);
+cudaError_t launch_finalize(int B, size_t smem, cudaStream_t s, bool dependent, const StaticParams<R>& p, const Buffers<R>& buf) {
+  if ((PHASES & PH_XCHG) == 0 && B >= FINAL_BATCH_MIN_B) return launch_finalize_bs<R, Model, SRC, PHASES, FINAL_BS_BATCH>(B, smem, s, dependent, p, buf);
+  return launch_finalize_bs<R, Model, SRC, PHASES, FINAL_BS>(B, smem, s, dependent, p, buf);
 }
 
 template <class R, class Model, int SRC>
@@ -63,6 +76,9 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   const size_t res_bytes = size_t(B) * (RES_SCALARS + 2 * N) * sizeof(double);
   const size_t smemU = (size_t(N) * 4 + size_t(8) * p.n_blocks + size_t(2) * p.n_ref) * sizeof(R);   // nominal + wall table + reference polyline
   const bool track = p.n_ref > 0;
+  // programmatic dependent launches between consecutive kernels of the step (not when events sit between them)
+  const bool pdl = h->pdl && !timed && (v & V_LOCAL);
+  const bool pdl_final = pdl && SRC != SRC_DWA;   // DWA: finalize follows the rollout directly and reads its scratch before any wait
   if (track && SRC == SRC_SUPPLIED) { h->err = "a reference path needs PHILOX noise (the tracking rollout is not built for supplied noise)"; return MPPI_EINVAL; }
 
   if (timed == 1) MPPI_CUDA(h, cudaEventRecord(h->ev[0], s));
@@ -114,7 +130,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
       const int ngroups = (N + UPDATE_JG - 1) / UPDATE_JG;
       dim3 ug(h->ksplit, h->jsplit, B);
       const size_t smemR = size_t((ngroups + h->jsplit - 1) / h->jsplit) * (UPDATE_BS / 32) * 2 * UPDATE_JG * sizeof(R);
-      update_kernel<R><<<ug, UPDATE_BS, smemR, s>>>(p, buf);
+      MPPI_CUDA(h, launch_step_kernel(update_kernel<R>, ug, dim3(UPDATE_BS), smemR, s, pdl, p, buf));   // rollout (or cut-off) -> update
       h->launches++;
     }
     if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[2], s));
@@ -126,15 +142,15 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
                        (size_t(N) * 6 + size_t(N + 1) * (Model::NX + 2 + 3 + 1) + size_t(2) * p.n_ref) * sizeof(R);
   const size_t smemX = smemF + size_t(h->n_ranks) * plen * sizeof(double);
   if (v & V_FUSED_FINAL) {
-    MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_PARTIAL | PH_COMBINE>(B, smemF, s, p, buf)));
+    MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_PARTIAL | PH_COMBINE>(B, smemF, s, pdl_final, p, buf)));
     h->launches++;
   }
   if (v & V_XFINAL) {
-    MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_PARTIAL | PH_XCHG | PH_COMBINE>(B, smemX, s, p, buf)));
+    MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_PARTIAL | PH_XCHG | PH_COMBINE>(B, smemX, s, pdl_final, p, buf)));
     h->launches++;
   }
   if (v & V_PARTIAL) {
-    MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_PARTIAL>(B, smemF, s, p, buf)));
+    MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_PARTIAL>(B, smemF, s, pdl_final, p, buf)));
     h->launches++;
   }
   if (v & V_D2H_PARTIAL)
@@ -148,7 +164,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
     if (r != ncclSuccess) { h->err = std::string("ncclAllGather: ") + api.GetErrorString(r); return MPPI_ENCCL; }
   }
   if (v & V_COMBINE) {
-    MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_COMBINE>(B, smemF, s, p, buf)));
+    MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_COMBINE>(B, smemF, s, false, p, buf)));
     h->launches++;
   }
   if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[3], s));

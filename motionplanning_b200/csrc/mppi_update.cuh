@@ -45,6 +45,7 @@ __global__ void __launch_bounds__(UPDATE_BS) update_kernel(const __grid_constant
   __shared__ R s_eta[NW];
   const int b = blockIdx.z, N = p.N, K = p.K_local;
   if (buf.halt && *buf.halt) return;
+  pdl_wait();   // everything below reads what the rollout wrote
   trace_begin(buf.dbg, buf.trace, 1);
   const Scratch sc = buf.scratch[b];
   const int keff = sc.k_eff;
@@ -133,6 +134,7 @@ __global__ void __launch_bounds__(UPDATE_BS) update_kernel(const __grid_constant
     buf.eta_part[size_t(b) * gridDim.x + blockIdx.x] = s;
   }
   trace_end(buf.dbg, buf.trace, 1);
+  pdl_trigger();
 }
 
 // ---------------------------------------------------------------------------
@@ -277,7 +279,6 @@ __global__ void __launch_bounds__(BS) finalize_kernel(const __grid_constant__ St
   MPPI_STAMP(0);
   trace_begin(buf.dbg, buf.trace, 2);
   // loads that do not depend on this step's kernels go first, so their latency hides behind the partial tree
-  const Scratch sc = buf.scratch[b];
   unsigned long long seq0 = 0;
   unsigned int iter0 = 0;
   if (t == 0) { seq0 = *buf.seq; iter0 = *buf.iter; }
@@ -294,6 +295,8 @@ __global__ void __launch_bounds__(BS) finalize_kernel(const __grid_constant__ St
       sU[4 * j + 3] = p.G10 * u0 + p.G11 * u1;
     }
   }
+  pdl_wait();   // the loads above do not depend on the update kernel; everything below does
+  const Scratch sc = buf.scratch[b];
   constexpr bool PART_TO_GLOBAL = !(PHASES & PH_COMBINE);   // only a partial-only launch has a consumer outside this block
   double* pdst = PART_TO_GLOBAL ? part : sOwn;
 

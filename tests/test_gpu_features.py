@@ -177,6 +177,31 @@ def test_batched_instances_match_single_instance_oracle(built):
     assert not np.array_equal(eps[0], eps[1])     # instances draw independent noise
 
 
+def test_batched_many_instances_small_blocks_path(built, monkeypatch):
+    """B >= 64 switches finalize to 128-thread blocks and the update kernel to one block per instance
+    walking all horizon groups; both must give what the single-instance kernels give (FP32, bitwise:
+    same operations in the same order for an instance whatever B is)."""
+    B, K, N = 80, 1024, 50
+    args, kw, circles, blocks = sc.config(4, K=K)
+    x0s = sc.jittered_x0(B)
+    Us = np.stack([warm_nominal(N, seed=b) for b in range(B)], axis=2)
+    big = make(args[:3] + (x0s,) + args[4:], dict(kw, B=B), circles, blocks)
+    Uout, costs, feas = big.step_batched(x0s, Us)
+    small_B = 4
+    small = make(args[:3] + (x0s[:, :small_B],) + args[4:], dict(kw, B=small_B), circles, blocks)
+    Uo2, c2, f2 = small.step_batched(x0s[:, :small_B], Us[:, :, :small_B])
+    # instance b draws noise from counter (k, j, iter, b): the first instances see identical noise in both handles
+    assert np.allclose(Uout[:, :, :small_B], Uo2, rtol=2e-6, atol=1e-7)
+    assert np.allclose(costs[:small_B], c2, rtol=1e-6) and np.array_equal(feas[:small_B], f2)
+    # update-kernel grid shapes: forced one-group-per-block and one-block-per-instance agree
+    for js in ("1", "13"):
+        monkeypatch.setenv("MPPI_UPDATE_JSPLIT", js)
+        alt = make(args[:3] + (x0s[:, :small_B],) + args[4:], dict(kw, B=small_B), circles, blocks)
+        Uo3, c3, _ = alt.step_batched(x0s[:, :small_B], Us[:, :, :small_B])
+        assert np.allclose(Uo3, Uo2, rtol=2e-6, atol=1e-7) and np.allclose(c3, c2, rtol=1e-6)
+    monkeypatch.delenv("MPPI_UPDATE_JSPLIT")
+
+
 def test_sample_xy_export(built):
     args, kw, circles, blocks = sc.config(0)
     kw = dict(kw, precision=capi.FP64)

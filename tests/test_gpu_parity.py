@@ -150,6 +150,16 @@ def test_odd_sizes_and_ragged_tail(built):
         check(mppi, ref, capi.FP64)
 
 
+@pytest.mark.parametrize("model_cfg,precision", [(0, capi.FP32), (3, capi.FP64), (3, capi.FP32)])
+def test_maximum_horizon(built, model_cfg, precision):
+    """N = MPPI_MAX_N = 256: the finalize kernel needs more than the default 48 KB of dynamic shared
+    memory (opt-in path), the update kernel walks 64 horizon groups, the nominal recurrence is long."""
+    args, kw, circles, blocks = sc.config(model_cfg, K=256, N=256)
+    args = args[:8] + (0.02 * 256,) + args[9:]          # keep the horizon inside the scene: T = 5.12 s
+    mppi, ref = run_pair(args, kw, circles, blocks, precision, Unom=0.3 * warm_nominal(256))
+    check(mppi, ref, precision)
+
+
 def test_no_obstacles_and_many_circles(built):
     args, kw, _, _ = sc.config(0, K=512, N=20)
     mppi, ref = run_pair(args, kw, [], [], capi.FP64)

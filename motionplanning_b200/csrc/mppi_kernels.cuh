@@ -76,7 +76,7 @@ template <class R, class V> struct Rebind<Kin5<R>, V> { using type = Kin5<V>; };
 template <class R, class V> struct Rebind<Dyn7<R>, V> { using type = Dyn7<V>; };
 
 // The horizon loop for the LANES samples of one thread, specialised on the number of circle
-// quads held in registers (NQ >= 0) or reading the circle table (NQ < 0).
+// circles held in registers (NQ = their number, padded entries never hit) or reading the circle table (NQ < 0).
 template <class V, class Model, int SRC, int NQ, bool TRACK>
 __device__ __forceinline__ void rollout_horizon(const StaticParams<typename Math<V>::S>& p, const Buffers<typename Math<V>::S>& buf,
                                                 Model& veh, RolloutAcc<V>& acc, const HotParams<typename Math<V>::S, Model::NX>* sHot,
@@ -232,13 +232,15 @@ rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, cons
     veh.init(p, x0);
     const V gx0 = veh.s[0] - V(p.goal[0]), gy0 = veh.s[1] - V(p.goal[1]);
     const V d0 = M::fma(gx0, gx0, gy0 * gy0);
-    const int nq = (p.n_circles + 3) >> 2;   // warp-uniform: the whole horizon loop is specialised
     if constexpr (TRACK || sizeof(R) == 8) {
       rollout_horizon<V, Model, SRC, -1, TRACK>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
     } else {
-      if (nq == 0) rollout_horizon<V, Model, SRC, 0, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
-      else if (nq == 1) rollout_horizon<V, Model, SRC, 1, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
-      else if (nq == 2) rollout_horizon<V, Model, SRC, 2, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
+      // specialised on the circle count: none, the reference scene's three (main.jl:30), up to four, up to eight
+      const int nc = p.n_circles;
+      if (nc == 0) rollout_horizon<V, Model, SRC, 0, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
+      else if (nc <= 3) rollout_horizon<V, Model, SRC, 3, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
+      else if (nc == 4) rollout_horizon<V, Model, SRC, 4, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
+      else if (nc <= 8) rollout_horizon<V, Model, SRC, 8, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
       else rollout_horizon<V, Model, SRC, -1, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
     }
     acc.stage += veh.stage_cost(p, V(0), V(0));      // terminal slot: VehicleDynamics(x_N, [0,0]) (:49,:53)

@@ -150,13 +150,13 @@ __device__ __forceinline__ typename Math<V>::Count circle_hits_quads(const Stati
   }
   return hits;
 }
-// the first 4*Q circles of a register-resident table (horizon loop of the rollout kernel)
-template <class V, int Q, class P>
+// the first NC circles of a register-resident table (horizon loop of the rollout kernel)
+template <class V, int NC, class P>
 __device__ __forceinline__ typename Math<V>::Count circle_hits_regs(const P& hp, V px, V py) {
   using M = Math<V>;
   typename M::Count h = M::count(M::lt(V(1), V(0)));
 #pragma unroll
-  for (int o = 0; o < 4 * Q; ++o) {
+  for (int o = 0; o < NC; ++o) {
     const V dx = px - V(hp.circ[o][0]), dy = py - V(hp.circ[o][1]);
     h += M::count(M::le(M::fma(dx, dx, dy * dy), V(hp.circ[o][2])));
   }

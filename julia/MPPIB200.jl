@@ -16,7 +16,8 @@
 module MPPIB200
 
 export defineMPPI, defineMPPIobs!, defineMPPIblocks!, defineMPPINominalControl!,
-       ShiftInitialCondition, MPPIPlan, MPPISearcher, MPPIClosedLoop, defineMPPIrefpath!
+       ShiftInitialCondition, MPPIPlan, MPPISearcher, MPPIClosedLoop, defineMPPIrefpath!,
+       defineDWA, defineDWAobs!, DWAPlan
 
 const LIB = get(ENV, "MPPI_B200_LIB", joinpath(@__DIR__, "..", "motionplanning_b200", "csrc", "libmppi_b200.so"))
 const MAX_NX = 8
@@ -79,7 +80,7 @@ pad8(v) = ntuple(i -> i <= length(v) ? Float64(v[i]) : 0.0, 8)
 
 function defineMPPI(numStates, numControls, lambda, X0, goal, SamplingNumber, Σ, N, T, XL, XU, CL, CU;
                     model = numStates == 7 ? 0 : 1, precision = 0, noise_mode = 1, seed = 0x5EED0001,
-                    device = 0, FeasibilityCount = 1300)
+                    device = 0, FeasibilityCount = 1300, planner = 0, obstacle_penalty = nothing)
     numControls > 0 || error("Controls ($numControls) must be > 0")                 # setup.jl:19-21
     numStates > 0 || error("States ($numStates) must be > 0")                       # :22-24
     length(X0) == numStates || error("Length of X0 ($(length(X0))) must match number of states ($numStates)")
@@ -90,10 +91,11 @@ function defineMPPI(numStates, numControls, lambda, X0, goal, SamplingNumber, Σ
     d = Ref{Config}()
     ccall((:mppi_config_default, LIB), Int32, (Ref{Config},), d)
     c = d[]
-    cfg = Config(c.struct_size, model, numStates, numControls, SamplingNumber, N, 1, precision, noise_mode, 0,
+    cfg = Config(c.struct_size, model, numStates, numControls, SamplingNumber, N, 1, precision, noise_mode, planner,
                  FeasibilityCount, 1, device, 0, 0, 0, seed, T, lambda,
                  (Σ[1, 1], Σ[2, 1], Σ[1, 2], Σ[2, 2]), pad8(X0), (goal[1], goal[2]), pad8(XL), pad8(XU),
-                 (CL[1], CL[2]), (CU[1], CU[2]), c.slack_penalty, c.obstacle_penalty, c.terminal_scale,
+                 (CL[1], CL[2]), (CU[1], CU[2]), c.slack_penalty,
+                 obstacle_penalty === nothing ? c.obstacle_penalty : Float64(obstacle_penalty), c.terminal_scale,
                  c.la, c.lb, c.mass, c.Izz, c.g, c.mu, c.KFZF, c.KFZR, c.KFZX, c.tire, c.stage_w,
                  c.veh_L, c.veh_W, c.veh_center_offset)
     hp = Ref{Ptr{Cvoid}}(C_NULL)
@@ -154,6 +156,32 @@ function MPPIPlan(mppi::MPPISearcher; noise = nothing)                          
     r.Feasibility = c.feasible != 0 ? :Feasible : :InFeasible                          # :195
     r.cost = c.cost; r.RolloutCount = c.rollout_count; r.FeasibleTrajCount = c.feasible_count
     r.time = c.time_s                                                                  # :199-200
+    return nothing
+end
+
+# ---- the DynamicWindow sibling (OptimalControl/DynamicWindow/src/setup.jl, DWAUtils.jl) -------------------
+# Replace include("src/DWAUtils.jl") (DynamicWindow/main.jl:1); lines 26-27 and 49-53 run unchanged; the plant
+# step of :61 keeps using the reference's own VehicleDynamics.
+function defineDWA(numStates, numControls, X0, goal, SampleNumber, T, XL, XU, CL, CU; precision = 0, device = 0)  # setup.jl:3-52
+    K = prod(SampleNumber)
+    dwa = defineMPPI(numStates, numControls, 1.0, X0, goal, K, [1.0 0.0; 0.0 1.0], 20, T, XL, XU, CL, CU;   # types.jl:24 N = 20
+                     precision = precision, device = device, FeasibilityCount = K, planner = 1,
+                     obstacle_penalty = 10000.0 * 712.5)                                                      # DWAUtils.jl:112
+    # defineDWAcontrols! (setup.jl:59-85): first control is the slowest index
+    g1 = collect(LinRange(CL[1], CU[1], SampleNumber[1])); g2 = collect(LinRange(CL[2], CU[2], SampleNumber[2]))
+    cand = Matrix{Float64}(undef, K, 2)
+    for i in 1:SampleNumber[1], j in 1:SampleNumber[2]
+        cand[(i - 1) * SampleNumber[2] + j, :] = [g1[i], g2[j]]
+    end
+    check(dwa.h, ccall((:mppi_set_candidates, LIB), Int32, (Ptr{Cvoid}, Ptr{Float64}, Int32, Int32), dwa.h, cand, K, 2))
+    return dwa
+end
+
+defineDWAobs!(dwa::MPPISearcher, obstacle_list) = defineMPPIobs!(dwa, obstacle_list)    # setup.jl:54-57
+
+function DWAPlan(dwa::MPPISearcher)                                                    # DWAUtils.jl:141-163
+    MPPIPlan(dwa)
+    dwa.r.Control = reshape(dwa.r.Control[1, :], 1, :)   # BestCand.Control is the constant control of the candidate (:156)
     return nothing
 end
 

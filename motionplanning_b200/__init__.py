@@ -6,6 +6,7 @@ Julia API (OptimalControl/MPPI/src/setup.jl, MPPIUtils.jl); see julia/MPPIB200.j
 the `ccall` twin.
 """
 from . import _capi as capi  # noqa: F401
+from .dwa import DWAPlan, defineDWA, defineDWAcontrols, defineDWAobs  # noqa: F401
 from .mppi import (  # noqa: F401
     MPPIError,
     MPPIPlan,

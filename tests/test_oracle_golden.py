@@ -136,3 +136,80 @@ def test_plant_zero_order_hold_and_goal_stop(built):
     assert done2 and 90 <= len(his2) <= 110
     assert (his2[-1, 1] - cfg.goal[0]) ** 2 + (his2[-1, 2] - cfg.goal[1]) ** 2 <= 36.0
     assert (his2[-2, 1] - cfg.goal[0]) ** 2 + (his2[-2, 2] - cfg.goal[1]) ** 2 > 36.0
+
+
+# ---------------------------------------------------------------------------------------------------
+# The whole plan, pinned on the reference's own output.  DynamicWindow/main.jl has no random sampling:
+# every DWAPlan of the committed run can be replayed, and the control it selected can be read back from
+# the log (tests/golden/make_golden.py: dwa_plan_cases).  One case exercises the candidate grid
+# (setup.jl:59-95), TrajectoryRollout (DWAUtils.jl:16-42), Rungekutta2 (:61-75), VehicleDynamics,
+# ObstacleEvaluation (:105-118), BoundEvaluation (:121-137), the terminal term (:39,98-101) and the
+# arg-min selection (:152) -- rows a3..a10 of SURVEY.md 8(a), which MPPIPlan shares line for line.
+# ---------------------------------------------------------------------------------------------------
+def _dwa_cases():
+    a = np.loadtxt(os.path.join(GOLD, "dwa_plan_cases.csv"), delimiter=",", comments="#")
+    return a[:-1], a[-1]
+
+
+def _dwa_scene(**over):
+    from motionplanning_b200 import defineDWAcontrols
+    from motionplanning_b200 import scenarios as sc
+    CLd, CUd = [-0.3, -2.5], [0.3, 2.5]                       # DynamicWindow/main.jl:10-11
+    cand = defineDWAcontrols([31, 41], CLd, CUd)              # main.jl:25
+    K = len(cand)
+    T = over.pop("T", 3.0)
+    args = (7, 2, 25.0, sc.X0_DYN, [110, 0], K, sc.SIGMA, 20, T, sc.XL_DYN, sc.XU_DYN, CLd, CUd)   # main.jl:7-9,14,20,26
+    kw = dict(planner=capi.PLANNER_DWA, obstacle_penalty=10000.0 * 712.5, FeasibilityCount=K)
+    kw.update(over)
+    return orc.make_config(args, kw), cand
+
+
+DWA_CIRCLES = [[50.0, 1, 2.5], [70.0, -1, 2.5], [90.0, 1, 2.5]]   # DynamicWindow/main.jl:27
+
+
+def _dwa_mismatches(cfg, cand, circles, cases):
+    bad = 0
+    for row in cases:
+        got = orc.plan(cfg, circles, [], row[2:9], None, cand)["Control"][0]
+        bad += not np.allclose(got, row[9:11], rtol=0, atol=1e-9)
+    return bad
+
+
+def test_dwa_plan_reproduces_every_selection_of_the_reference_log(built):
+    cases, last = _dwa_cases()
+    assert len(cases) == 127 and int(last[0]) == 12632
+    cfg, cand = _dwa_scene()
+    assert cand.shape == (31 * 41, 2)
+    assert _dwa_mismatches(cfg, cand, DWA_CIRCLES, cases) == 0
+
+
+def test_dwa_pin_has_teeth(built):
+    """The same replay with one ingredient changed must disagree with the log, i.e. the 127 selections
+    really constrain obstacles, horizon, dynamics and the terminal term."""
+    cases, _ = _dwa_cases()
+    cfg, cand = _dwa_scene()
+    assert _dwa_mismatches(cfg, cand, [], cases) >= 40                                    # no obstacles
+    assert _dwa_mismatches(cfg, cand, [[x, y, 2.4] for x, y, _ in DWA_CIRCLES], cases) >= 10
+    assert _dwa_mismatches(*_dwa_scene(T=2.9), DWA_CIRCLES, cases) >= 40                  # dt = T / N
+    assert _dwa_mismatches(*_dwa_scene(la=1.6), DWA_CIRCLES, cases) >= 10                 # tyre model geometry
+    assert _dwa_mismatches(*_dwa_scene(terminal_scale=5000.0), DWA_CIRCLES, cases) >= 10  # DWAUtils.jl:39
+
+
+def test_dwa_closed_loop_reproduces_the_reference_log(built):
+    """DynamicWindow/main.jl:46-67 replayed end to end with the oracle (plan, then 100 Euler plant steps
+    under the held control, goal radius 7.2): every 100th row and the final row of DWATrajectory.csv."""
+    cases, last = _dwa_cases()
+    cfg, cand = _dwa_scene()
+    x = np.array(cases[0, 2:9])
+    worst, k = 0.0, 0
+    for i in range(200):
+        assert np.abs(x - cases[i, 2:9]).max() <= 1e-9 and k == int(cases[i, 0])
+        u = orc.plan(cfg, DWA_CIRCLES, [], x, None, cand)["Control"]
+        x, his, done = orc.plant_advance(cfg, x, u, steps=100, goal_radius=7.2, time_idx0=k)
+        k += len(his)
+        worst = max(worst, np.abs(x - (cases[i + 1, 2:9] if i + 1 < len(cases) else last[2:9])).max()) if not done else worst
+        if done:
+            break
+    assert done and k == int(last[0])
+    assert np.abs(x - last[2:9]).max() <= 1e-9 and his[-1, 0] == pytest.approx(last[1], abs=1e-12)
+    assert worst <= 1e-9

@@ -180,6 +180,7 @@ end
 defineDWAobs!(dwa::MPPISearcher, obstacle_list) = defineMPPIobs!(dwa, obstacle_list)    # setup.jl:54-57
 
 function DWAPlan(dwa::MPPISearcher)                                                    # DWAUtils.jl:141-163
+    dwa.r.Control = zeros(dwa.s.N, dwa.s.numControls)    # mppi_step writes the N x m (constant) sequence
     MPPIPlan(dwa)
     dwa.r.Control = reshape(dwa.r.Control[1, :], 1, :)   # BestCand.Control is the constant control of the candidate (:156)
     return nothing

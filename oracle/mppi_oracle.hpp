@@ -16,12 +16,20 @@
 //   OptimalControl/DynamicWindow/src/DWAUtils.jl:16-42,105-118,141-163 (DWA mode)
 //
 // Parity pinning: the reference (Julia) cannot run in the build container and
-// ships no tests.  The only reference-owned golden data on this path are the
-// two closed-loop CSV logs (MPPITrajectory.csv, DWATrajectory.csv); rows k,k+1
-// pin the *derivative* output of VehicleDynamics (tests/golden/, residual
-// <= 1e-12).  Everything else (stage cost, cost assembly, penalties, SAT,
-// softmin weights, update, cut-off, kinematic model composition) is
-// "parity unpinned": it rests on this file being a line-by-line restatement.
+// ships no tests.  The reference-owned golden data on this path are the two
+// closed-loop CSV logs (MPPITrajectory.csv, DWATrajectory.csv).
+//   PINNED  (1) rows k,k+1 of both logs pin the derivative output of
+//               VehicleDynamics (tests/golden/*_plant_pairs.csv, <= 1e-12);
+//           (2) the DWA run is deterministic: all 127 DWAPlan selections and
+//               all 12,633 rows of DWATrajectory.csv are reproduced by this
+//               restatement (tests/golden/dwa_plan_cases.csv,
+//               tests/test_oracle_golden.py).  That pins rollout, Heun step,
+//               stage cost, obstacle / bound / terminal terms and arg-min
+//               selection, which DWAPlan shares with MPPIPlan.
+//   "parity unpinned": the lambda term of the cost, softmin weights, weighted
+//           update, cut-off, SAT walls and the kinematic model composition
+//           (MPPI samples from an unseeded RNG; no artefact exists): these
+//           rest on this file being a line-by-line restatement.
 //
 // Build: g++ -O2 -ffp-contract=off (no FMA contraction: Julia does not contract
 // a*b+c), evaluation order as in the cited lines, sums left to right.

@@ -93,7 +93,9 @@ typedef struct mppi_config {
   int32_t k_offset;          /* first global sample id owned by this handle */
   int32_t K_local;           /* samples owned by this handle (0 => K) */
   int32_t rollout_variant;   /* 0 auto | 1 one sample per thread | 2 two samples per thread (packed FP32x2;
-                              * FP32 and even K_local only).  Environment MPPI_ROLLOUT_VARIANT overrides. */
+                              * FP32 and even K_local only) | 3 one sample per thread with the Philox noise
+                              * always drawn inside the rollout (no pre-generated noise).
+                              * Environment MPPI_ROLLOUT_VARIANT overrides. */
   uint64_t seed;             /* Philox key */
   double T;                  /* horizon seconds; dt = T/N (setup.jl:53) */
   double lambda;             /* types.jl:28 */

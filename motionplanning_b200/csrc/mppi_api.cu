@@ -104,6 +104,9 @@ int32_t mppi_destroy(mppi_handle_t* h) {
   void* host[] = {h->h_in, h->h_res, h->h_partial, h->h_gathered, h->h_seq, h->h_ll, h->h_pdone};
   for (void* p : host) if (p) cudaFreeHost(p);
   for (auto& e : h->ev) if (e) cudaEventDestroy(e);
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  if (h->ev_join) cudaEventDestroy(h->ev_join);
+  if (h->stream2) cudaStreamDestroy(h->stream2);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
   return MPPI_OK;
@@ -117,6 +120,9 @@ static int create_impl(mppi_handle* h) {
   MPPI_CUDA(h, cudaSetDevice(c.device));
   MPPI_CUDA(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   for (auto& e : h->ev) MPPI_CUDA(h, cudaEventCreate(&e));
+  MPPI_CUDA(h, cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking));
+  MPPI_CUDA(h, cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+  MPPI_CUDA(h, cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
   const size_t B = c.B, N = c.N, K = h->K_local, rs = real_size(h);
   h->plen = PART_HDR + 2 * c.N;
   int ks = (h->K_local + 2047) / 2048;
@@ -137,6 +143,8 @@ static int create_impl(mppi_handle* h) {
     // auto: packing halves the warps, so it needs enough samples to keep every SM sub-partition busy
     const long long samples = (long long)h->K_local * c.B;
     h->packed = can_pack && (variant == 2 || (variant == 0 && samples >= MPPI_PACK_MIN_SAMPLES));
+    h->pregen_ok = c.planner == MPPI_PLANNER_MPPI && c.noise_mode == MPPI_NOISE_PHILOX && c.B == 1 && variant != 3;
+    if (const char* e = getenv("MPPI_PREGEN")) h->pregen_ok = h->pregen_ok && atoi(e) != 0;
   }
   MPPI_CUDA(h, cudaMalloc(&h->d_in, B * (MPPI_MAX_NX + 2 * N) * sizeof(double)));
   if (c.planner == MPPI_PLANNER_MPPI) MPPI_CUDA(h, cudaMalloc(&h->d_eps, B * N * K * 2 * rs));
@@ -144,7 +152,7 @@ static int create_impl(mppi_handle* h) {
   MPPI_CUDA(h, cudaMalloc(&h->d_flags, B * K));
   MPPI_CUDA(h, cudaMalloc(&h->d_scratch, B * sizeof(Scratch)));
   MPPI_CUDA(h, cudaMalloc(&h->d_scratch_tmpl, B * sizeof(Scratch)));
-  MPPI_CUDA(h, cudaMalloc(&h->d_iter, sizeof(unsigned int)));
+  MPPI_CUDA(h, cudaMalloc(&h->d_iter, 2 * sizeof(unsigned int)));   // [0] iteration counter, [1] = [0] + 1 published by the rollout
   MPPI_CUDA(h, cudaMalloc(&h->d_Spart, B * h->ksplit * N * 2 * rs));
   MPPI_CUDA(h, cudaMalloc(&h->d_eta_part, B * h->ksplit * rs));
   MPPI_CUDA(h, cudaMalloc(&h->d_partial, (B + 8) * h->plen * sizeof(double)));   // + room for the peers' copies (in-kernel exchange)
@@ -179,7 +187,7 @@ static int create_impl(mppi_handle* h) {
   for (auto& s : tmpl) { s.rho_key = ~0ull; s.argmin = ~0u; s.feasible_count = 0; s.k_eff = h->K_local; s.pad = 0; }
   MPPI_CUDA(h, cudaMemcpy(h->d_scratch_tmpl, tmpl.data(), B * sizeof(Scratch), cudaMemcpyHostToDevice));
   MPPI_CUDA(h, cudaMemcpy(h->d_scratch, tmpl.data(), B * sizeof(Scratch), cudaMemcpyHostToDevice));
-  MPPI_CUDA(h, cudaMemset(h->d_iter, 0, sizeof(unsigned int)));
+  MPPI_CUDA(h, cudaMemset(h->d_iter, 0, 2 * sizeof(unsigned int)));
   MPPI_CUDA(h, cudaMemset(h->d_res, 0, B * (RES_SCALARS + 2 * N) * sizeof(double)));
   rebuild_params(h);
   return MPPI_OK;
@@ -247,6 +255,7 @@ int32_t mppi_set_sigma_lambda(mppi_handle_t* h, const double* Sigma, double lamb
   h->cfg.lambda = lambda;
   rebuild_params(h);
   drop_graphs(h);
+  h->noise_ready = false;   // pre-generated eps was drawn with the old chol(Sigma)
   return MPPI_OK;
 }
 

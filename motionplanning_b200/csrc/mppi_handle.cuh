@@ -78,6 +78,11 @@ struct mppi_handle {
   double ref_w = 0.0; int ref_window = 0;
   void* d_ref = nullptr;          // the polyline in the handle's precision
   bool pdl = true;                // programmatic dependent launches inside the step (env MPPI_PDL=0 disables)
+  // pre-generated noise (V_PREGEN): second capture branch for noise_kernel, and whether d_eps already holds
+  // the noise of the iteration the device counter points at
+  bool pregen_ok = false, noise_ready = false;
+  cudaStream_t stream2 = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   mppi::PlantArgs plant = {};
   int shift_k = 0;
   double* d_his = nullptr; double* d_iterlog = nullptr; int* d_pstate = nullptr; int* h_pdone = nullptr;
@@ -222,6 +227,7 @@ Buffers<R> make_buffers(const mppi_handle* h) {
   b.peers = h->p2p ? h->d_peers : nullptr;
   b.trace = h->profiling == 2 ? 1 : 0;
   b.halt = nullptr;
+  b.eps_stage = 0;
   b.ref = static_cast<const R*>(h->d_ref);
   return b;
 }

@@ -11,6 +11,9 @@
 namespace mppi {
 
 enum { SRC_SUPPLIED = 0, SRC_PHILOX = 1, SRC_DWA = 2 };
+constexpr int EPS_GROUP = 8;         // horizon rows per mbarrier when the eps slab is staged in shared memory
+constexpr int EPS_MAX_GROUPS = 16;
+constexpr int EPS_SLAB_MAX = 32 * 1024;   // bytes per block: 7 blocks per SM must still fit (FP32, N <= 64)
 constexpr int ROLLOUT_BS = 64;   // 65,536 samples = 1024 CTAs = 6.9 per SM: one balanced wave on 148 SMs
 constexpr int UPDATE_BS = 256;
 constexpr int UPDATE_JG = 4;
@@ -80,7 +83,8 @@ template <class R, class V> struct Rebind<Dyn7<R>, V> { using type = Dyn7<V>; };
 template <class V, class Model, int SRC, int NQ, bool TRACK>
 __device__ __forceinline__ void rollout_horizon(const StaticParams<typename Math<V>::S>& p, const Buffers<typename Math<V>::S>& buf,
                                                 Model& veh, RolloutAcc<V>& acc, const HotParams<typename Math<V>::S, Model::NX>* sHot,
-                                                const typename Math<V>::S* sU, const typename Math<V>::S* sBlk, int b, int k, Tracker<V, TRACK>& trk) {
+                                                const typename Math<V>::S* sU, const typename Math<V>::S* sBlk, int b, int k, Tracker<V, TRACK>& trk,
+                                                const void* sEps = nullptr, uint64_t* sBar = nullptr) {
   using M = Math<V>;
   using S = typename M::S;
   using S2 = typename Vec2<S>::type;
@@ -158,17 +162,62 @@ __device__ __forceinline__ void rollout_horizon(const StaticParams<typename Math
       }
       eps += 2 * estride;
     }
-  } else if (SRC == SRC_SUPPLIED) {
-    Ctl<V> e_next = load_eps(eps);
+  } else if (SRC == SRC_SUPPLIED && sEps != nullptr) {
+    // eps slab of this block staged in shared memory by bulk copies (rollout_kernel): row j = the block's samples at
+    // horizon step j, EPS_GROUP rows per mbarrier; a thread waits once per group and reads its own samples
+    const S2* row = reinterpret_cast<const S2*>(sEps) + threadIdx.x * LANES;
     for (int j = 0; j < N; ++j) {
-      const Ctl<V> e = e_next;
+      if ((j % EPS_GROUP) == 0) mbar_wait(sBar + j / EPS_GROUP, 0);
+      advance(nu_p[j], load_eps(row));
+      row += ROLLOUT_BS * LANES;
+    }
+  } else if (SRC == SRC_SUPPLIED) {
+    // eps comes from memory (host-supplied, or pre-generated by noise_kernel): a 3-deep register queue
+    // keeps the loads of steps j+1..j+3 in flight, enough to cover an HBM miss (~1.5 steps at cfg 2)
+    Ctl<V> q0 = load_eps(eps), q1 = q0, q2 = q0;
+    if (1 < N) q1 = load_eps(eps + estride);
+    if (2 < N) q2 = load_eps(eps + 2 * estride);
+    eps += 3 * estride;
+    for (int j = 0; j < N; ++j) {
+      const Ctl<V> e = q0;
+      q0 = q1; q1 = q2;
+      if (j + 3 < N) q2 = load_eps(eps);
       eps += estride;
-      if (j + 1 < N) e_next = load_eps(eps);   // prefetch next step's noise
       advance(nu_p[j], e);
     }
   } else {
     for (int j = 0; j < N; ++j) advance(S4{S(0), S(0), S(0), S(0)}, Ctl<V>{V(0), V(0)});
   }
+}
+
+// ---------------------------------------------------------------------------
+// Pre-generated noise (step variant V_PREGEN, mppi_pipeline.cuh).  Philox is counter based, so the eps
+// tensor of iteration i+1 depends on nothing iteration i computes: it is drawn by this kernel on a
+// second graph branch while the one-block finalize of iteration i leaves 147 SMs idle, and the rollout
+// of iteration i+1 reads it back (SRC_SUPPLIED instantiation) instead of spending ~60 of its ~150 issue
+// slots per sample-step on Philox rounds and Box-Muller.  Same counters, same arithmetic, same bits as
+// the in-rollout generator (`draw` above): one thread = one Philox call = two horizon steps of one sample.
+// *iter_ptr is the iteration to draw for: the handle's counter itself when the kernel runs ahead of the
+// rollout in the same stream, or the slot the rollout publishes (iter[1] = iter[0] + 1) when it runs
+// beside finalize, which increments iter[0] at an unknown moment.
+// ---------------------------------------------------------------------------
+constexpr int NOISE_BS = 256;
+template <class R>
+__global__ void __launch_bounds__(NOISE_BS) noise_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf,
+                                                         const unsigned int* __restrict__ iter_ptr, int delta) {
+  using R2 = typename Vec2<R>::type;
+  const int k = blockIdx.x * NOISE_BS + threadIdx.x, j = 2 * blockIdx.y, b = blockIdx.z;
+  const int K = p.K_local, N = p.N;
+  if (k >= K) return;
+  const uint32_t iter = *iter_ptr + uint32_t(delta);
+  const uint4 rnd = philox4x32_10(make_uint4(uint32_t(p.k_offset + k), uint32_t(j >> 1), iter, uint32_t(b)), p.seed_lo, p.seed_hi);
+  float a0, a1, b0, b1;
+  box_muller(rnd.x, rnd.y, &a0, &a1);
+  box_muller(rnd.z, rnd.w, &b0, &b1);
+  R2* eps = reinterpret_cast<R2*>(buf.eps) + (size_t(b) * N + j) * size_t(K) + k;
+  const R L00 = p.L00, L10 = p.L10, L11 = p.L11;
+  eps[0] = R2{L00 * R(a0), Math<R>::fma(L11, R(a1), L10 * R(a0))};
+  if (j + 1 < N) eps[K] = R2{L00 * R(b0), Math<R>::fma(L11, R(b1), L10 * R(b0))};
 }
 
 // V = float / double: one sample per thread.  V = f32x2: two adjacent samples per thread on the
@@ -197,6 +246,18 @@ rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, cons
   const int k = (blockIdx.x * ROLLOUT_BS + threadIdx.x) * LANES;   // first sample of this thread
   if (buf.halt && *buf.halt) return;   // closed loop already at its goal (uniform across the grid)
   trace_begin(buf.dbg, buf.trace, 0);
+  __shared__ __align__(8) uint64_t s_bar[EPS_MAX_GROUPS];
+  const unsigned char* sEps = nullptr;
+  if (SRC == SRC_SUPPLIED) {
+    if ((blockIdx.x | blockIdx.y | threadIdx.x) == 0) buf.iter[1] = buf.iter[0] + 1u;   // for noise_kernel beside finalize
+    if (buf.eps_stage) {
+      sEps = smem_raw + ((size_t(4 * N + 8 * p.n_blocks + 2 * p.n_ref) * sizeof(R) + 127) & ~size_t(127));
+      if (threadIdx.x == 0) {
+        for (int g = 0; g * EPS_GROUP < N; ++g) mbar_init(&s_bar[g], 1);
+        mbar_init_fence();
+      }
+    }
+  }
   if (threadIdx.x == ROLLOUT_BS - 1) sHot.fill(p);
   for (int i = threadIdx.x; i < 8 * p.n_blocks; i += ROLLOUT_BS) sBlk[i] = (&p.blk[0][0])[i];
   if (TRACK) for (int i = threadIdx.x; i < 2 * p.n_ref; i += ROLLOUT_BS) sRef[i] = buf.ref[i];
@@ -212,6 +273,21 @@ rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, cons
     }
   }
   __syncthreads();
+  if (SRC == SRC_SUPPLIED && sEps != nullptr && threadIdx.x == 0) {
+    // One thread asks for the whole slab up front: N bulk copies (TMA), one per horizon row, in horizon order.
+    // Every HBM miss of the block is in flight at once; the horizon loop starts as soon as the first group landed.
+    using R2 = typename Vec2<R>::type;
+    const int k0 = blockIdx.x * ROLLOUT_BS * LANES;
+    const int n_here = min(ROLLOUT_BS * LANES, p.K_local - k0);
+    const uint32_t row_bytes = uint32_t(n_here) * sizeof(R2);
+    const R2* src = reinterpret_cast<const R2*>(buf.eps) + size_t(b) * N * p.K_local + k0;
+    for (int g = 0; g * EPS_GROUP < N; ++g) {
+      const int j0 = g * EPS_GROUP, j1 = min(j0 + EPS_GROUP, N);
+      mbar_arrive_expect_tx(&s_bar[g], row_bytes * uint32_t(j1 - j0));
+      for (int j = j0; j < j1; ++j)
+        bulk_load(const_cast<unsigned char*>(sEps) + size_t(j) * ROLLOUT_BS * LANES * sizeof(R2), src + size_t(j) * p.K_local, row_bytes, &s_bar[g]);
+    }
+  }
   Tracker<V, TRACK> trk;
   if constexpr (TRACK) {   // every sample of the instance starts its window at the point closest to x0
     __shared__ R s_td[ROLLOUT_BS / 32];
@@ -233,15 +309,15 @@ rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, cons
     const V gx0 = veh.s[0] - V(p.goal[0]), gy0 = veh.s[1] - V(p.goal[1]);
     const V d0 = M::fma(gx0, gx0, gy0 * gy0);
     if constexpr (TRACK || sizeof(R) == 8) {
-      rollout_horizon<V, Model, SRC, -1, TRACK>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
+      rollout_horizon<V, Model, SRC, -1, TRACK>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk, sEps, s_bar);
     } else {
       // specialised on the circle count: none, the reference scene's three (main.jl:30), up to four, up to eight
       const int nc = p.n_circles;
-      if (nc == 0) rollout_horizon<V, Model, SRC, 0, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
-      else if (nc <= 3) rollout_horizon<V, Model, SRC, 3, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
-      else if (nc == 4) rollout_horizon<V, Model, SRC, 4, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
-      else if (nc <= 8) rollout_horizon<V, Model, SRC, 8, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
-      else rollout_horizon<V, Model, SRC, -1, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk);
+      if (nc == 0) rollout_horizon<V, Model, SRC, 0, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk, sEps, s_bar);
+      else if (nc <= 3) rollout_horizon<V, Model, SRC, 3, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk, sEps, s_bar);
+      else if (nc == 4) rollout_horizon<V, Model, SRC, 4, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk, sEps, s_bar);
+      else if (nc <= 8) rollout_horizon<V, Model, SRC, 8, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk, sEps, s_bar);
+      else rollout_horizon<V, Model, SRC, -1, false>(p, buf, veh, acc, &sHot, sU, sBlk, b, k, trk, sEps, s_bar);
     }
     acc.stage += veh.stage_cost(p, V(0), V(0));      // terminal slot: VehicleDynamics(x_N, [0,0]) (:49,:53)
     trk.add(acc.stage, veh.s[0], veh.s[1]);

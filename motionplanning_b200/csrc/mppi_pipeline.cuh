@@ -25,7 +25,11 @@ enum {
   V_HOST_RES = 4096,    // B == 1: finalize writes the result block to mapped host memory (no D2H node)
   V_XFINAL = 8192,      // finalize<PARTIAL|XCHG|COMBINE>: softmin all-gather in-kernel over NVLink peer memory
   V_PLANT = 16384,      // closed loop: plant kernel behind finalize advances X0 on the device (mppi_plant.cuh)
-  V_SHIFT = 32768       // closed loop: U_nom <- U_new shifted by shift_k knots (instead of V_ADOPT's plain copy)
+  V_SHIFT = 32768,      // closed loop: U_nom <- U_new shifted by shift_k knots (instead of V_ADOPT's plain copy)
+  // bits 16..19 carry n_ranks (variant_key), bit 24 the tracing flag
+  V_PREGEN = 1 << 20,   // rollout reads pre-generated Philox noise; noise_kernel for the NEXT iteration runs beside finalize
+  V_NOISE_NOW = 1 << 21,   // ... and the buffer does not hold this iteration's noise yet: draw it ahead of the rollout
+  V_ENQ_MASK = 0xFFFF | V_PREGEN | V_NOISE_NOW
 };
 
 template <class R> const StaticParams<R>& params_of(const mppi_handle* h);
@@ -45,6 +49,10 @@ cudaError_t launch_step_kernel(void (*kernel)(P, Bf), dim3 grid, dim3 block, siz
   lc.attrs = at; lc.numAttrs = dependent ? 1 : 0;
   return cudaLaunchKernelEx(&lc, kernel, p, buf);
 }
+
+// a kernel whose blocks each stage tens of KB wants the SM's shared-memory carve-out at its maximum (once per instantiation)
+template <class K>
+void prefer_shared_carveout(K kernel) { cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); }
 
 // long horizons need more than the default 48 KB of dynamic shared memory: opt in once per instantiation
 template <class R, class Model, int SRC, int PHASES, int BS>
@@ -100,16 +108,40 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
     shift_nominal_kernel<<<1, 256, 0, s>>>(h->d_in + size_t(B) * MPPI_MAX_NX, h->d_res + size_t(B) * RES_SCALARS, N, h->shift_k);
     h->launches++;
   }
+  const bool pregen = SRC == SRC_PHILOX && (v & V_PREGEN) && (v & V_LOCAL);
+  // A rollout that READS eps (host-supplied or pre-generated) stages its block's slab in shared memory by bulk
+  // copies when the slab is small enough to keep the occupancy: N rows of ROLLOUT_BS * LANES samples.
+  size_t smemE = 0;
+  if ((SRC == SRC_SUPPLIED || pregen) && (v & V_LOCAL)) {
+    const int lanes = (h->packed && !pregen && sizeof(R) == 4) ? 2 : 1;
+    const size_t slab = size_t(N) * ROLLOUT_BS * lanes * 2 * sizeof(R);
+    const bool aligned = sizeof(R) == 8 || (K % 2) == 0;   // rows start and end on 16-byte boundaries
+    if (slab <= size_t(EPS_SLAB_MAX) && aligned && N <= EPS_GROUP * EPS_MAX_GROUPS && !getenv("MPPI_NO_EPS_STAGE")) {
+      buf.eps_stage = 1;
+      smemE = ((smemU + 127) & ~size_t(127)) - smemU + slab;
+    }
+  }
+  const dim3 noise_grid((K + NOISE_BS - 1) / NOISE_BS, (N + 1) / 2, B);
+  if (pregen && (v & V_NOISE_NOW)) {
+    noise_kernel<R><<<noise_grid, NOISE_BS, 0, s>>>(p, buf, h->d_iter, 0);
+    h->launches++;
+  }
   if (timed == 1) MPPI_CUDA(h, cudaEventRecord(h->ev[5], s));   // the rollout's interval starts after the inputs are staged
   if (v & V_LOCAL) {
-    bool launched = false;
+    bool launched = pregen;
+    if (pregen) {   // one-sample threads, eps read back (the host keeps V_PREGEN off for packed / tracking handles)
+      dim3 grid((K + ROLLOUT_BS - 1) / ROLLOUT_BS, B);
+      static bool carved = false;
+      if (!carved) { prefer_shared_carveout(rollout_kernel<R, Model, SRC_SUPPLIED>); carved = true; }
+      rollout_kernel<R, Model, SRC_SUPPLIED><<<grid, ROLLOUT_BS, smemU + smemE, s>>>(p, buf);
+    }
     if constexpr (std::is_same<R, float>::value) {
-      if (h->packed) {   // two samples per thread on the packed FP32 pipe (mppi_pack.cuh)
+      if (h->packed && !pregen) {   // two samples per thread on the packed FP32 pipe (mppi_pack.cuh)
         dim3 grid((K + 2 * ROLLOUT_BS - 1) / (2 * ROLLOUT_BS), B);
         if constexpr (SRC != SRC_SUPPLIED) {
           if (track) rollout_kernel<f32x2, typename Rebind<Model, f32x2>::type, SRC, true><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
         }
-        if (!track) rollout_kernel<f32x2, typename Rebind<Model, f32x2>::type, SRC><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
+        if (!track) rollout_kernel<f32x2, typename Rebind<Model, f32x2>::type, SRC><<<grid, ROLLOUT_BS, smemU + smemE, s>>>(p, buf);
         launched = true;
       }
     }
@@ -118,7 +150,11 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
       if constexpr (SRC != SRC_SUPPLIED) {
         if (track) rollout_kernel<R, Model, SRC, true><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
       }
-      if (!track) rollout_kernel<R, Model, SRC><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
+      if (!track) {
+        static bool carved = false;
+        if (SRC == SRC_SUPPLIED && !carved) { prefer_shared_carveout(rollout_kernel<R, Model, SRC>); carved = true; }
+        rollout_kernel<R, Model, SRC><<<grid, ROLLOUT_BS, smemU + smemE, s>>>(p, buf);
+      }
     }
     h->launches++;
     if (h->cutoff && SRC != SRC_DWA) {
@@ -131,6 +167,13 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
       dim3 ug(h->ksplit, h->jsplit, B);
       const size_t smemR = size_t((ngroups + h->jsplit - 1) / h->jsplit) * (UPDATE_BS / 32) * 2 * UPDATE_JG * sizeof(R);
       MPPI_CUDA(h, launch_step_kernel(update_kernel<R>, ug, dim3(UPDATE_BS), smemR, s, pdl, p, buf));   // rollout (or cut-off) -> update
+      h->launches++;
+    }
+    if (pregen) {   // fork: the next iteration's noise may overwrite eps as soon as the update has streamed it
+      MPPI_CUDA(h, cudaEventRecord(h->ev_fork, s));
+      MPPI_CUDA(h, cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
+      noise_kernel<R><<<noise_grid, NOISE_BS, 0, h->stream2>>>(p, buf, h->d_iter + 1, 0);
+      MPPI_CUDA(h, cudaEventRecord(h->ev_join, h->stream2));
       h->launches++;
     }
     if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[2], s));
@@ -168,6 +211,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
     h->launches++;
   }
   if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[3], s));
+  if (pregen) MPPI_CUDA(h, cudaStreamWaitEvent(s, h->ev_join, 0));   // join
   if (v & V_PLANT) {
     plant_kernel<typename Rebind<Model, double>::type><<<1, 32, 0, s>>>(h->pd, h->plant);
     h->launches++;
@@ -196,11 +240,15 @@ int enqueue_src(mppi_handle* h, int v, int timed) {
 }
 template <class R>
 int enqueue_model(mppi_handle* h, int v, int timed) {
+#ifndef MPPI_DEV_FAST   // development builds (make FAST=1): FP32 kinematic instantiations only, a quarter of the compile time
   if (h->cfg.model == MPPI_MODEL_DYNAMIC7) return enqueue_src<R, Dyn7<R>>(h, v, timed);
+#endif
   return enqueue_src<R, Kin5<R>>(h, v, timed);
 }
 inline int enqueue(mppi_handle* h, int v, int timed) {
+#ifndef MPPI_DEV_FAST
   if (h->cfg.precision == MPPI_FP64) return enqueue_model<double>(h, v, timed);
+#endif
   return enqueue_model<float>(h, v, timed);
 }
 
@@ -210,6 +258,7 @@ inline int kernels_in(const mppi_handle* h, int v) {
   const bool dwa = h->cfg.planner == MPPI_PLANNER_DWA;
   if ((v & (V_H2D_IN | V_H2D_X0 | V_H2D_U)) && h->cfg.B == 1) n++;
   if (v & V_LOCAL) n += 1 + ((h->cutoff && !dwa) ? 1 : 0) + (dwa ? 0 : 1);
+  if ((v & V_LOCAL) && (v & V_PREGEN)) n += 1 + ((v & V_NOISE_NOW) ? 1 : 0);
   if (v & V_FUSED_FINAL) n++;
   if (v & V_XFINAL) n++;
   if (v & V_PARTIAL) n++;
@@ -217,6 +266,14 @@ inline int kernels_in(const mppi_handle* h, int v) {
   if (v & V_PLANT) n++;
   if (v & V_SHIFT) n++;
   return n;
+}
+
+// Pre-generated noise applies to single-instance Philox MPPI steps with one-sample rollout threads: the
+// latency-bound regime, where the rollout's issue slots are the step's critical path.  Large sample
+// counts (packed rollout) are throughput-bound: the same instructions cost the same wherever they run.
+inline int noise_bits(const mppi_handle* h) {
+  if (!h->pregen_ok || h->packed || !h->ref_path.empty()) return 0;
+  return V_PREGEN | (h->noise_ready ? 0 : V_NOISE_NOW);
 }
 
 // pending host-side input changes -> the H2D node(s) the next step must carry
@@ -273,7 +330,8 @@ inline int run_variant(mppi_handle* h, int v) {
   if (!use_graph) {
     h->in_flight = h->inputs_busy = true;
     if (v & (V_COMBINE | V_FUSED_FINAL | V_XFINAL)) h->seq_launched++;
-    return enqueue(h, v & 0xFFFF, h->profiling ? 1 : 0);
+    h->noise_ready = (v & V_PREGEN) != 0;
+    return enqueue(h, v & V_ENQ_MASK, h->profiling ? 1 : 0);
   }
   const bool inner = false;
   if (h->profiling == 2) v |= 1 << 24;   // graphs whose kernels trace %globaltimer are cached separately
@@ -282,7 +340,7 @@ inline int run_variant(mppi_handle* h, int v) {
     cudaGraph_t g = nullptr;
     const int64_t before = h->launches;
     MPPI_CUDA(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
-    int rc = enqueue(h, v & 0xFFFF, inner ? 2 : 0);
+    int rc = enqueue(h, v & V_ENQ_MASK, inner ? 2 : 0);
     cudaError_t e = cudaStreamEndCapture(h->stream, &g);
     h->launches = before;
     if (rc != MPPI_OK) { if (g) cudaGraphDestroy(g); return rc; }
@@ -298,7 +356,8 @@ inline int run_variant(mppi_handle* h, int v) {
   MPPI_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
   MPPI_CUDA(h, cudaGraphLaunch(it->second, h->stream));
   MPPI_CUDA(h, cudaEventRecord(h->ev[4], h->stream));
-  h->launches += kernels_in(h, v & 0xFFFF);
+  h->launches += kernels_in(h, v & V_ENQ_MASK);
+  h->noise_ready = (v & V_PREGEN) != 0;   // any other step leaves this iteration's own noise (or none) in eps
   if (v & (V_COMBINE | V_FUSED_FINAL | V_XFINAL)) h->seq_launched++;
   h->in_flight = h->inputs_busy = true;
   return MPPI_OK;

@@ -405,3 +405,49 @@ def test_full_size_properties(built, cfg_idx, K, N):
     ok = sub["margins"] > GUARD
     rel = np.abs(costs[idx] - sub["costs"]) / np.abs(sub["costs"])
     assert rel[ok].max() <= FP32_TOL and np.array_equal(flags[idx][ok], sub["flags"][ok])
+
+
+@pytest.mark.parametrize("precision", [capi.FP64, capi.FP32])
+@pytest.mark.parametrize("model_cfg", [0, 3])
+def test_pregenerated_noise_is_bit_identical_to_in_rollout_philox(built, precision, model_cfg):
+    """Step variant V_PREGEN (noise_kernel draws iteration i+1's eps beside finalize of iteration i, the
+    rollout reads it back) against rollout_variant = 3 (Philox inside the rollout): same counters, same
+    arithmetic, so costs, flags, U_new and the dumped eps agree bit for bit over a chain of iterations,
+    across mppi_get_noise (which redraws the consumed eps and forces the next step to draw its own) and
+    across a change of Sigma (which invalidates the pre-generated buffer)."""
+    args, kw, circles, blocks = sc.config(model_cfg, K=4096 + 64, N=31)     # odd horizon: last Philox pair half used
+    kw = dict(kw, precision=precision, noise_mode=capi.NOISE_PHILOX)
+    ref = make(args, dict(kw, rollout_variant=3), circles, blocks)
+    pre = make(args, dict(kw, rollout_variant=1), circles, blocks)
+    assert pre.launch_count() == ref.launch_count() == 0
+
+    def both(f):
+        f(ref), f(pre)
+
+    def same():
+        assert np.array_equal(ref.p.costs, pre.p.costs) and np.array_equal(ref.p.flags, pre.p.flags)
+        assert np.array_equal(ref.r.Control, pre.r.Control) and np.array_equal(ref.r.Traj, pre.r.Traj)
+        assert (ref.r.argmin, ref.r.cost, ref.r.rho, ref.r.eta) == (pre.r.argmin, pre.r.cost, pre.r.rho, pre.r.eta)
+
+    for it in range(5):
+        both(m.MPPIPlan)
+        same()
+        if it in (1, 2):
+            assert np.array_equal(ref.noise(), pre.noise())
+        if it == 3:
+            xy_r, xy_p = ref.p.sample_xy(64), pre.p.sample_xy(64)
+            assert np.array_equal(xy_r, xy_p)
+        both(lambda s: m.defineMPPINominalControl(s, s.r.Control.copy()))
+    Sigma2 = np.array([[0.08, 0.01], [0.01, 0.05]])
+    both(lambda s: m.defineMPPINominalControl(s, s.r.Control.copy(), Sigma2))
+    both(m.MPPIPlan)
+    same()
+    assert np.array_equal(ref.noise(), pre.noise())
+    # asynchronous chain (mppi_step_async with adopt): U_nom <- U_new on the device
+    for _ in range(3):
+        both(lambda s: s.step_async(adopt=True))
+    both(lambda s: s.sync())
+    both(lambda s: s.fetch_result())
+    same()
+    # the pre-generating handle launched one extra kernel per step (+ one when it had to draw ahead of the rollout)
+    assert pre.launch_count() > ref.launch_count()

@@ -92,10 +92,11 @@ typedef struct mppi_config {
   int32_t device;            /* CUDA device ordinal of this handle */
   int32_t k_offset;          /* first global sample id owned by this handle */
   int32_t K_local;           /* samples owned by this handle (0 => K) */
-  int32_t rollout_variant;   /* 0 auto | 1 one sample per thread | 2 two samples per thread (packed FP32x2;
-                              * FP32 and even K_local only) | 3 one sample per thread with the Philox noise
-                              * always drawn inside the rollout (no pre-generated noise).
-                              * Environment MPPI_ROLLOUT_VARIANT overrides. */
+  int32_t rollout_variant;   /* 0 auto | 1 one sample per thread | 2 two samples per thread (packed FP32x2; FP32 and
+                              * even K_local only) | 3, 4 = 1, 2 with the Philox noise always drawn inside the
+                              * rollout.  0-2 pre-generate the next iteration's noise beside finalize whenever the
+                              * step is a single-instance Philox MPPI step.
+                              * Environment MPPI_ROLLOUT_VARIANT overrides; MPPI_PREGEN=0 disables pre-generation. */
   uint64_t seed;             /* Philox key */
   double T;                  /* horizon seconds; dt = T/N (setup.jl:53) */
   double lambda;             /* types.jl:28 */

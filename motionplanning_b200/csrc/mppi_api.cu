@@ -10,6 +10,9 @@ using namespace mppi;
 #ifndef MPPI_PACK_MIN_SAMPLES
 #define MPPI_PACK_MIN_SAMPLES 262144
 #endif
+#ifndef MPPI_PACK_MIN_SAMPLES_PREGEN
+#define MPPI_PACK_MIN_SAMPLES_PREGEN 65536
+#endif
 
 #define H_CHECK(h)            \
   if (!(h)) return MPPI_EINVAL; \
@@ -78,6 +81,7 @@ static int validate(const mppi_config_t* c, std::string* why) {
   if (c->precision != MPPI_FP32 && c->precision != MPPI_FP64) { *why = "unknown precision"; return MPPI_EINVAL; }
   if (c->noise_mode != MPPI_NOISE_SUPPLIED && c->noise_mode != MPPI_NOISE_PHILOX) { *why = "unknown noise_mode"; return MPPI_EINVAL; }
   if (c->planner != MPPI_PLANNER_MPPI && c->planner != MPPI_PLANNER_DWA) { *why = "unknown planner"; return MPPI_EINVAL; }
+  if (c->rollout_variant < 0 || c->rollout_variant > 4) { *why = "rollout_variant must be 0..4"; return MPPI_EINVAL; }
   const int Kl = c->K_local > 0 ? c->K_local : c->K;
   if (c->k_offset < 0 || c->k_offset + Kl > c->K) { *why = "sample shard [k_offset, k_offset+K_local) must lie inside [0, K)"; return MPPI_EINVAL; }
   const double det = c->Sigma[0] * c->Sigma[3] - c->Sigma[1] * c->Sigma[2];
@@ -140,11 +144,14 @@ static int create_impl(mppi_handle* h) {
     if (const char* e = getenv("MPPI_ROLLOUT_VARIANT")) variant = atoi(e);
     if (const char* e = getenv("MPPI_PDL")) h->pdl = atoi(e) != 0;
     const bool can_pack = c.precision == MPPI_FP32 && (h->K_local % 2) == 0;
-    // auto: packing halves the warps, so it needs enough samples to keep every SM sub-partition busy
-    const long long samples = (long long)h->K_local * c.B;
-    h->packed = can_pack && (variant == 2 || (variant == 0 && samples >= MPPI_PACK_MIN_SAMPLES));
-    h->pregen_ok = c.planner == MPPI_PLANNER_MPPI && c.noise_mode == MPPI_NOISE_PHILOX && c.B == 1 && variant != 3;
+    // pre-generated noise (variants 0-2): single-instance Philox MPPI steps; 3 / 4 keep Philox inside the rollout
+    h->pregen_ok = c.planner == MPPI_PLANNER_MPPI && c.noise_mode == MPPI_NOISE_PHILOX && c.B == 1 && variant != 3 && variant != 4;
     if (const char* e = getenv("MPPI_PREGEN")) h->pregen_ok = h->pregen_ok && atoi(e) != 0;
+    // auto: packing halves the warps, so it needs enough samples to keep every SM sub-partition busy; with the
+    // per-lane Philox / Box-Muller work out of the loop it pays from 65,536 samples (tools/sweep_pregen.py)
+    const long long samples = (long long)h->K_local * c.B;
+    const long long pack_min = h->pregen_ok ? MPPI_PACK_MIN_SAMPLES_PREGEN : MPPI_PACK_MIN_SAMPLES;
+    h->packed = can_pack && (variant == 2 || variant == 4 || (variant == 0 && samples >= pack_min));
   }
   MPPI_CUDA(h, cudaMalloc(&h->d_in, B * (MPPI_MAX_NX + 2 * N) * sizeof(double)));
   if (c.planner == MPPI_PLANNER_MPPI) MPPI_CUDA(h, cudaMalloc(&h->d_eps, B * N * K * 2 * rs));

@@ -13,7 +13,7 @@ namespace mppi {
 enum { SRC_SUPPLIED = 0, SRC_PHILOX = 1, SRC_DWA = 2 };
 constexpr int EPS_GROUP = 8;         // horizon rows per mbarrier when the eps slab is staged in shared memory
 constexpr int EPS_MAX_GROUPS = 16;
-constexpr int EPS_SLAB_MAX = 32 * 1024;   // bytes per block: 7 blocks per SM must still fit (FP32, N <= 64)
+constexpr int EPS_SLAB_MAX = 52 * 1024;   // bytes per block, packed threads (4 blocks per SM); one-sample threads stage up to 32 KB (7 per SM)
 constexpr int ROLLOUT_BS = 64;   // 65,536 samples = 1024 CTAs = 6.9 per SM: one balanced wave on 148 SMs
 constexpr int UPDATE_BS = 256;
 constexpr int UPDATE_JG = 4;

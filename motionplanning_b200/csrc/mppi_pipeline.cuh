@@ -113,10 +113,10 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   // copies when the slab is small enough to keep the occupancy: N rows of ROLLOUT_BS * LANES samples.
   size_t smemE = 0;
   if ((SRC == SRC_SUPPLIED || pregen) && (v & V_LOCAL)) {
-    const int lanes = (h->packed && !pregen && sizeof(R) == 4) ? 2 : 1;
+    const int lanes = (h->packed && sizeof(R) == 4) ? 2 : 1;
     const size_t slab = size_t(N) * ROLLOUT_BS * lanes * 2 * sizeof(R);
     const bool aligned = sizeof(R) == 8 || (K % 2) == 0;   // rows start and end on 16-byte boundaries
-    if (slab <= size_t(EPS_SLAB_MAX) && aligned && N <= EPS_GROUP * EPS_MAX_GROUPS && !getenv("MPPI_NO_EPS_STAGE")) {
+    if (slab <= size_t(lanes == 2 ? EPS_SLAB_MAX : 32 * 1024) && aligned && N <= EPS_GROUP * EPS_MAX_GROUPS && !getenv("MPPI_NO_EPS_STAGE")) {
       buf.eps_stage = 1;
       smemE = ((smemU + 127) & ~size_t(127)) - smemU + slab;
     }
@@ -129,11 +129,28 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   if (timed == 1) MPPI_CUDA(h, cudaEventRecord(h->ev[5], s));   // the rollout's interval starts after the inputs are staged
   if (v & V_LOCAL) {
     bool launched = pregen;
-    if (pregen) {   // one-sample threads, eps read back (the host keeps V_PREGEN off for packed / tracking handles)
-      dim3 grid((K + ROLLOUT_BS - 1) / ROLLOUT_BS, B);
-      static bool carved = false;
-      if (!carved) { prefer_shared_carveout(rollout_kernel<R, Model, SRC_SUPPLIED>); carved = true; }
-      rollout_kernel<R, Model, SRC_SUPPLIED><<<grid, ROLLOUT_BS, smemU + smemE, s>>>(p, buf);
+    if (pregen) {   // eps read back (the host keeps V_PREGEN off for tracking handles)
+      bool done = false;
+      if constexpr (std::is_same<R, float>::value) {
+        if (h->packed) {
+          using PK = typename Rebind<Model, f32x2>::type;
+          dim3 grid((K + 2 * ROLLOUT_BS - 1) / (2 * ROLLOUT_BS), B);
+          static bool carved = false;
+          if (!carved) {
+            prefer_shared_carveout(rollout_kernel<f32x2, PK, SRC_SUPPLIED>);
+            cudaFuncSetAttribute(rollout_kernel<f32x2, PK, SRC_SUPPLIED>, cudaFuncAttributeMaxDynamicSharedMemorySize, EPS_SLAB_MAX + 8192);
+            carved = true;
+          }
+          rollout_kernel<f32x2, PK, SRC_SUPPLIED><<<grid, ROLLOUT_BS, smemU + smemE, s>>>(p, buf);
+          done = true;
+        }
+      }
+      if (!done) {
+        dim3 grid((K + ROLLOUT_BS - 1) / ROLLOUT_BS, B);
+        static bool carved = false;
+        if (!carved) { prefer_shared_carveout(rollout_kernel<R, Model, SRC_SUPPLIED>); carved = true; }
+        rollout_kernel<R, Model, SRC_SUPPLIED><<<grid, ROLLOUT_BS, smemU + smemE, s>>>(p, buf);
+      }
     }
     if constexpr (std::is_same<R, float>::value) {
       if (h->packed && !pregen) {   // two samples per thread on the packed FP32 pipe (mppi_pack.cuh)
@@ -272,7 +289,7 @@ inline int kernels_in(const mppi_handle* h, int v) {
 // latency-bound regime, where the rollout's issue slots are the step's critical path.  Large sample
 // counts (packed rollout) are throughput-bound: the same instructions cost the same wherever they run.
 inline int noise_bits(const mppi_handle* h) {
-  if (!h->pregen_ok || h->packed || !h->ref_path.empty()) return 0;
+  if (!h->pregen_ok || !h->ref_path.empty()) return 0;
   return V_PREGEN | (h->noise_ready ? 0 : V_NOISE_NOW);
 }
 

@@ -407,18 +407,18 @@ def test_full_size_properties(built, cfg_idx, K, N):
     assert rel[ok].max() <= FP32_TOL and np.array_equal(flags[idx][ok], sub["flags"][ok])
 
 
-@pytest.mark.parametrize("precision", [capi.FP64, capi.FP32])
+@pytest.mark.parametrize("precision,variants", [(capi.FP64, (3, 1)), (capi.FP32, (3, 1)), (capi.FP32, (4, 2))])
 @pytest.mark.parametrize("model_cfg", [0, 3])
-def test_pregenerated_noise_is_bit_identical_to_in_rollout_philox(built, precision, model_cfg):
+def test_pregenerated_noise_is_bit_identical_to_in_rollout_philox(built, precision, variants, model_cfg):
     """Step variant V_PREGEN (noise_kernel draws iteration i+1's eps beside finalize of iteration i, the
-    rollout reads it back) against rollout_variant = 3 (Philox inside the rollout): same counters, same
+    rollout reads it back) against rollout_variant = 3 / 4 (Philox inside the one-sample / packed rollout): same counters, same
     arithmetic, so costs, flags, U_new and the dumped eps agree bit for bit over a chain of iterations,
     across mppi_get_noise (which redraws the consumed eps and forces the next step to draw its own) and
     across a change of Sigma (which invalidates the pre-generated buffer)."""
     args, kw, circles, blocks = sc.config(model_cfg, K=4096 + 64, N=31)     # odd horizon: last Philox pair half used
     kw = dict(kw, precision=precision, noise_mode=capi.NOISE_PHILOX)
-    ref = make(args, dict(kw, rollout_variant=3), circles, blocks)
-    pre = make(args, dict(kw, rollout_variant=1), circles, blocks)
+    ref = make(args, dict(kw, rollout_variant=variants[0]), circles, blocks)      # Philox inside the rollout (3 scalar, 4 packed)
+    pre = make(args, dict(kw, rollout_variant=variants[1]), circles, blocks)      # pre-generated noise
     assert pre.launch_count() == ref.launch_count() == 0
 
     def both(f):

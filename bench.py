@@ -357,7 +357,9 @@ def run_ours(a, rank, world, local_rank):
             mppi.sync()
             c = mppi.phase_clocks()
             if i >= 2:
-                spans.append([(c[9 + 2 * j] - c[8 + 2 * j]) * 1e-3 for j in range(3)] + [(c[13] - c[8]) * 1e-3])
+                noise = c[15] > 0 and c[14] < 2 ** 63   # noise_kernel for the next iteration ran beside finalize (V_PREGEN)
+                spans.append([(c[9 + 2 * j] - c[8 + 2 * j]) * 1e-3 for j in range(3)] + [(c[13] - c[8]) * 1e-3] +
+                             ([(c[15] - c[14]) * 1e-3, (max(c[13], c[15]) - c[8]) * 1e-3] if noise else [0.0, (c[13] - c[8]) * 1e-3]))
         mppi.set_profiling(0)
         g_us = np.median(np.array(spans), axis=0)
     fp32_peak = mppi.measure_fp32_peak()
@@ -375,7 +377,9 @@ def run_ours(a, rank, world, local_rank):
             "ms_per_step": total_s / a.steps * 1e3, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOADS[a.config], "K_total": K if not batched else K, "K_per_gpu": kl, "N": N,
-                       "instances": B * (world if batched else 1), "noise": "philox4x32-10 in-kernel",
+                       "instances": B * (world if batched else 1), "noise": ("philox4x32-10 on the device, one tensor drawn per step inside the timed region: noise_kernel draws the next "
+                                 "iteration's tensor on a graph branch beside finalize, the rollout reads it back (TMA-staged)"
+                                 if not batched else "philox4x32-10 inside the rollout kernel"),
                        "parallelism": (f"samples sharded x{world}, softmin all-gather in the finalize kernel over NVLink peer memory"
                                        if exchange == "peer" else f"samples sharded x{world}, one NCCL all-gather per step") if world > 1 and not batched
                        else ("instances sharded, no collective" if batched and world > 1 else "1 GPU"),
@@ -393,6 +397,7 @@ def run_ours(a, rank, world, local_rank):
             "kernels_us_in_graph": None if g_us is None else {
                 "rollout_cost": float(g_us[0]), "softmin_update": float(g_us[1]), "finalize_nominal": float(g_us[2]),
                 "rollout_start_to_finalize_end": float(g_us[3]),
+                "noise_next_iteration": float(g_us[4]), "rollout_start_to_last_kernel_end": float(g_us[5]),
                 "source": "%globaltimer spans written by the kernels themselves inside the replayed graph (mppi_set_profiling(2))"},
             "roofline": {"kernel": "rollout_kernel", "bound": "fp32", "achieved": roll_tflops, "peak": fp32_peak,
                          "unit": "TFLOP/s", "frac": roll_tflops / fp32_peak if fp32_peak else None,
@@ -406,8 +411,8 @@ def run_ours(a, rank, world, local_rank):
                                 "traffic": NCU_TRAFFIC.get(a.config, (None, None))[1] if world == 1 else None,
                                 "bytes_per_launch": upd_bytes, "peak_source": f"MEASURED_PEAKS.json ({peak_src})",
                                 "frac_in_graph": None if g_us is None else upd_bytes / (g_us[1] * 1e-6) / 1e9 / peaks["hbm_gbs"],
-                                "note": "eps is produced by the rollout kernel in the same step; when it fits the 126 MB L2 "
-                                        "the stream is served from L2 and can exceed the HBM peak"},
+                                "note": "eps was read (or produced) by the rollout kernel earlier in the same step; when it fits the "
+                                        "126 MB L2 the stream is served from L2 and can exceed the HBM peak"},
             "clocks": clocks.summary(),
         }
         if not a.no_cpu_baseline:

@@ -202,22 +202,31 @@ __device__ __forceinline__ void rollout_horizon(const StaticParams<typename Math
 // beside finalize, which increments iter[0] at an unknown moment.
 // ---------------------------------------------------------------------------
 constexpr int NOISE_BS = 256;
+constexpr int NOISE_PAIRS = 2;   // Philox calls per thread: the index / parameter prologue is a fifth of a one-call thread
 template <class R>
 __global__ void __launch_bounds__(NOISE_BS) noise_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf,
                                                          const unsigned int* __restrict__ iter_ptr, int delta) {
   using R2 = typename Vec2<R>::type;
-  const int k = blockIdx.x * NOISE_BS + threadIdx.x, j = 2 * blockIdx.y, b = blockIdx.z;
+  const int k = blockIdx.x * NOISE_BS + threadIdx.x, b = blockIdx.z;
   const int K = p.K_local, N = p.N;
+  trace_begin(buf.dbg, buf.trace, 3);
   if (k >= K) return;
   const uint32_t iter = *iter_ptr + uint32_t(delta);
-  const uint4 rnd = philox4x32_10(make_uint4(uint32_t(p.k_offset + k), uint32_t(j >> 1), iter, uint32_t(b)), p.seed_lo, p.seed_hi);
-  float a0, a1, b0, b1;
-  box_muller(rnd.x, rnd.y, &a0, &a1);
-  box_muller(rnd.z, rnd.w, &b0, &b1);
-  R2* eps = reinterpret_cast<R2*>(buf.eps) + (size_t(b) * N + j) * size_t(K) + k;
   const R L00 = p.L00, L10 = p.L10, L11 = p.L11;
-  eps[0] = R2{L00 * R(a0), Math<R>::fma(L11, R(a1), L10 * R(a0))};
-  if (j + 1 < N) eps[K] = R2{L00 * R(b0), Math<R>::fma(L11, R(b1), L10 * R(b0))};
+#pragma unroll
+  for (int q = 0; q < NOISE_PAIRS; ++q) {
+    const int j = 2 * (blockIdx.y * NOISE_PAIRS + q);
+    if (j < N) {
+      const uint4 rnd = philox4x32_10(make_uint4(uint32_t(p.k_offset + k), uint32_t(j >> 1), iter, uint32_t(b)), p.seed_lo, p.seed_hi);
+      float a0, a1, b0, b1;
+      box_muller(rnd.x, rnd.y, &a0, &a1);
+      box_muller(rnd.z, rnd.w, &b0, &b1);
+      R2* eps = reinterpret_cast<R2*>(buf.eps) + (size_t(b) * N + j) * size_t(K) + k;
+      eps[0] = R2{L00 * R(a0), Math<R>::fma(L11, R(a1), L10 * R(a0))};
+      if (j + 1 < N) eps[K] = R2{L00 * R(b0), Math<R>::fma(L11, R(b1), L10 * R(b0))};
+    }
+  }
+  trace_end(buf.dbg, buf.trace, 3);
 }
 
 // V = float / double: one sample per thread.  V = f32x2: two adjacent samples per thread on the

@@ -121,7 +121,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
       smemE = ((smemU + 127) & ~size_t(127)) - smemU + slab;
     }
   }
-  const dim3 noise_grid((K + NOISE_BS - 1) / NOISE_BS, (N + 1) / 2, B);
+  const dim3 noise_grid((K + NOISE_BS - 1) / NOISE_BS, (N + 2 * NOISE_PAIRS - 1) / (2 * NOISE_PAIRS), B);
   if (pregen && (v & V_NOISE_NOW)) {
     noise_kernel<R><<<noise_grid, NOISE_BS, 0, s>>>(p, buf, h->d_iter, 0);
     h->launches++;

@@ -40,9 +40,9 @@ WORKLOADS = {
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu captures
 # (profiles/r01_ncu_*.md), keyed by --config: (rollout kernel, update kernel); N = 1 only.
 NCU_TRAFFIC = {
-    1: (72_704 + 0, 26_488_320 + 1_536),
-    2: (76_032 + 112_857_856, 168_833_792 + 3_384_064),
-    3: (2_141_696 + 788_885_760, 843_071_232 + 3_948_288),
+    1: (26_285_824 + 0, 26_491_136 + 0),                        # rollout reads the pre-generated eps (26.2 MB algorithmic)
+    2: (167_845_632 + 4_443_136, 168_838_656 + 3_827_200),
+    3: (839_461_376 + 9_430_784, 843_085_056 + 3_552_768),
 }
 
 

@@ -125,6 +125,7 @@ static int create_impl(mppi_handle* h) {
   MPPI_CUDA(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   for (auto& e : h->ev) MPPI_CUDA(h, cudaEventCreate(&e));
   MPPI_CUDA(h, cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking));
+  MPPI_CUDA(h, cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, c.device));
   MPPI_CUDA(h, cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
   MPPI_CUDA(h, cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
   const size_t B = c.B, N = c.N, K = h->K_local, rs = real_size(h);

@@ -81,6 +81,7 @@ struct mppi_handle {
   // pre-generated noise (V_PREGEN): second capture branch for noise_kernel, and whether d_eps already holds
   // the noise of the iteration the device counter points at
   bool pregen_ok = false, noise_ready = false;
+  int sm_count = 148;
   cudaStream_t stream2 = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   mppi::PlantArgs plant = {};

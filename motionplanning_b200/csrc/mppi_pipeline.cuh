@@ -53,11 +53,22 @@ cudaError_t launch_step_kernel(void (*kernel)(P, Bf), dim3 grid, dim3 block, siz
 // a kernel whose blocks each stage tens of KB wants the SM's shared-memory carve-out at its maximum (once per instantiation)
 template <class K>
 void prefer_shared_carveout(K kernel) { cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); }
+// true the first time it is called for this call site's `mask` on the current device (function attributes are per device)
+inline bool first_on_device(unsigned long long& mask) {
+  int dev = 0; cudaGetDevice(&dev);
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (mask & bit) return false;
+  mask |= bit;
+  return true;
+}
 
 // long horizons need more than the default 48 KB of dynamic shared memory: opt in once per instantiation
 template <class R, class Model, int SRC, int PHASES, int BS>
 cudaError_t launch_finalize_bs(int B, size_t smem, cudaStream_t s, bool dependent, const StaticParams<R>& p, const Buffers<R>& buf) {
-  static size_t allowed = 48 * 1024;
+  static size_t allowed_dev[64];   // function attributes are per device: one process may hold handles on several
+  int dev = 0; cudaGetDevice(&dev);
+  size_t& allowed = allowed_dev[dev & 63];
+  if (allowed == 0) allowed = 48 * 1024;
   if (smem > allowed) {
     cudaError_t e = cudaFuncSetAttribute(finalize_kernel<R, Model, SRC, PHASES, BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     if (e != cudaSuccess) return e;
@@ -135,11 +146,10 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
         if (h->packed) {
           using PK = typename Rebind<Model, f32x2>::type;
           dim3 grid((K + 2 * ROLLOUT_BS - 1) / (2 * ROLLOUT_BS), B);
-          static bool carved = false;
-          if (!carved) {
+          static unsigned long long carved = 0;
+          if (first_on_device(carved)) {
             prefer_shared_carveout(rollout_kernel<f32x2, PK, SRC_SUPPLIED>);
             cudaFuncSetAttribute(rollout_kernel<f32x2, PK, SRC_SUPPLIED>, cudaFuncAttributeMaxDynamicSharedMemorySize, EPS_SLAB_MAX + 8192);
-            carved = true;
           }
           rollout_kernel<f32x2, PK, SRC_SUPPLIED><<<grid, ROLLOUT_BS, smemU + smemE, s>>>(p, buf);
           done = true;
@@ -147,8 +157,8 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
       }
       if (!done) {
         dim3 grid((K + ROLLOUT_BS - 1) / ROLLOUT_BS, B);
-        static bool carved = false;
-        if (!carved) { prefer_shared_carveout(rollout_kernel<R, Model, SRC_SUPPLIED>); carved = true; }
+        static unsigned long long carved = 0;
+        if (first_on_device(carved)) prefer_shared_carveout(rollout_kernel<R, Model, SRC_SUPPLIED>);
         rollout_kernel<R, Model, SRC_SUPPLIED><<<grid, ROLLOUT_BS, smemU + smemE, s>>>(p, buf);
       }
     }
@@ -158,7 +168,15 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
         if constexpr (SRC != SRC_SUPPLIED) {
           if (track) rollout_kernel<f32x2, typename Rebind<Model, f32x2>::type, SRC, true><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
         }
-        if (!track) rollout_kernel<f32x2, typename Rebind<Model, f32x2>::type, SRC><<<grid, ROLLOUT_BS, smemU + smemE, s>>>(p, buf);
+        if (!track) {
+          using PK = typename Rebind<Model, f32x2>::type;
+          static unsigned long long carved = 0;
+          if (SRC == SRC_SUPPLIED && first_on_device(carved)) {   // host-supplied eps, slab staged in shared memory (up to EPS_SLAB_MAX > 48 KB)
+            prefer_shared_carveout(rollout_kernel<f32x2, PK, SRC>);
+            cudaFuncSetAttribute(rollout_kernel<f32x2, PK, SRC>, cudaFuncAttributeMaxDynamicSharedMemorySize, EPS_SLAB_MAX + 8192);
+          }
+          rollout_kernel<f32x2, PK, SRC><<<grid, ROLLOUT_BS, smemU + smemE, s>>>(p, buf);
+        }
         launched = true;
       }
     }
@@ -168,8 +186,8 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
         if (track) rollout_kernel<R, Model, SRC, true><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
       }
       if (!track) {
-        static bool carved = false;
-        if (SRC == SRC_SUPPLIED && !carved) { prefer_shared_carveout(rollout_kernel<R, Model, SRC>); carved = true; }
+        static unsigned long long carved = 0;
+        if (SRC == SRC_SUPPLIED && first_on_device(carved)) prefer_shared_carveout(rollout_kernel<R, Model, SRC>);
         rollout_kernel<R, Model, SRC><<<grid, ROLLOUT_BS, smemU + smemE, s>>>(p, buf);
       }
     }

@@ -60,6 +60,7 @@ __device__ __forceinline__ double key_cost(unsigned long long key, double) { ret
 // Step prologue for B == 1: pull the caller's x0 / U_nom (mapped pinned host memory, read over
 // PCIe by one small CTA) into the device input block.  Replaces an H2D memcpy node in the graph.
 __global__ void __launch_bounds__(128) begin_kernel(const double* __restrict__ host_in, double* __restrict__ dev_in, int first, int count) {
+  pdl_trigger();   // the rollout may start its input-independent prologue (parameters, eps slab) while the PCIe read is in flight
   for (int i = threadIdx.x; i < count; i += 128) dev_in[first + i] = host_in[first + i];
 }
 
@@ -229,6 +230,26 @@ __global__ void __launch_bounds__(NOISE_BS) noise_kernel(const __grid_constant__
   trace_end(buf.dbg, buf.trace, 3);
 }
 
+// Bulk copies (TMA) of the block's eps slab into shared memory: one copy per horizon row (the block's samples at step j,
+// contiguous in the [N][K][2] tensor), EPS_GROUP rows per mbarrier, groups [g0, g1).  Called by ONE thread.  All HBM misses
+// of the block are in flight together; the horizon loop starts as soon as its first group has landed.
+template <class R, int LANES>
+__device__ __forceinline__ void issue_eps_rows(const Buffers<R>& buf, const StaticParams<R>& p, int b, const unsigned char* sEps,
+                                               uint64_t* s_bar, int g0, int g1) {
+  using R2 = typename Vec2<R>::type;
+  const int N = p.N;
+  const int k0 = blockIdx.x * ROLLOUT_BS * LANES;
+  const int n_here = min(ROLLOUT_BS * LANES, p.K_local - k0);
+  const uint32_t row_bytes = uint32_t(n_here) * sizeof(R2);
+  const R2* src = reinterpret_cast<const R2*>(buf.eps) + size_t(b) * N * p.K_local + k0;
+  for (int g = g0; g < g1 && g * EPS_GROUP < N; ++g) {
+    const int j0 = g * EPS_GROUP, j1 = min(j0 + EPS_GROUP, N);
+    mbar_arrive_expect_tx(&s_bar[g], row_bytes * uint32_t(j1 - j0));
+    for (int j = j0; j < j1; ++j)
+      bulk_load(const_cast<unsigned char*>(sEps) + size_t(j) * ROLLOUT_BS * LANES * sizeof(R2), src + size_t(j) * p.K_local, row_bytes, &s_bar[g]);
+  }
+}
+
 // V = float / double: one sample per thread.  V = f32x2: two adjacent samples per thread on the
 // packed FP32 pipe (K_local must be even; chosen by the host for large sample counts).
 // One-sample FP32 threads are capped at 146 registers (7 CTAs of 64 per SM = 448 threads) so that
@@ -264,6 +285,9 @@ rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, cons
       if (threadIdx.x == 0) {
         for (int g = 0; g * EPS_GROUP < N; ++g) mbar_init(&s_bar[g], 1);
         mbar_init_fence();
+        // The same thread asks for the first group of rows right away (the other threads first wait on a barrier
+        // after the __syncthreads below, so they see it initialised); the rest of the slab follows after that barrier.
+        issue_eps_rows<R, LANES>(buf, p, b, sEps, s_bar, 0, 1);
       }
     }
   }
@@ -272,6 +296,7 @@ rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, cons
   if (TRACK) for (int i = threadIdx.x; i < 2 * p.n_ref; i += ROLLOUT_BS) sRef[i] = buf.ref[i];
   const bool active = k < p.K_local;
   const double* Ub = buf.U + size_t(b) * 2 * N;
+  pdl_wait();   // launched as a programmatic dependent of begin_kernel: x0 / U_nom are read from here on (a no-op otherwise)
   if (SRC != SRC_DWA) {
     for (int j = threadIdx.x; j < N; j += ROLLOUT_BS) {
       const R u0 = R(Ub[j]), u1 = R(Ub[N + j]);
@@ -282,21 +307,7 @@ rollout_kernel(const __grid_constant__ StaticParams<typename Math<V>::S> p, cons
     }
   }
   __syncthreads();
-  if (SRC == SRC_SUPPLIED && sEps != nullptr && threadIdx.x == 0) {
-    // One thread asks for the whole slab up front: N bulk copies (TMA), one per horizon row, in horizon order.
-    // Every HBM miss of the block is in flight at once; the horizon loop starts as soon as the first group landed.
-    using R2 = typename Vec2<R>::type;
-    const int k0 = blockIdx.x * ROLLOUT_BS * LANES;
-    const int n_here = min(ROLLOUT_BS * LANES, p.K_local - k0);
-    const uint32_t row_bytes = uint32_t(n_here) * sizeof(R2);
-    const R2* src = reinterpret_cast<const R2*>(buf.eps) + size_t(b) * N * p.K_local + k0;
-    for (int g = 0; g * EPS_GROUP < N; ++g) {
-      const int j0 = g * EPS_GROUP, j1 = min(j0 + EPS_GROUP, N);
-      mbar_arrive_expect_tx(&s_bar[g], row_bytes * uint32_t(j1 - j0));
-      for (int j = j0; j < j1; ++j)
-        bulk_load(const_cast<unsigned char*>(sEps) + size_t(j) * ROLLOUT_BS * LANES * sizeof(R2), src + size_t(j) * p.K_local, row_bytes, &s_bar[g]);
-    }
-  }
+  if (SRC == SRC_SUPPLIED && sEps != nullptr && threadIdx.x == 0) issue_eps_rows<R, LANES>(buf, p, b, sEps, s_bar, 1, EPS_MAX_GROUPS);
   Tracker<V, TRACK> trk;
   if constexpr (TRACK) {   // every sample of the instance starts its window at the point closest to x0
     __shared__ R s_td[ROLLOUT_BS / 32];

@@ -119,6 +119,8 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
     shift_nominal_kernel<<<1, 256, 0, s>>>(h->d_in + size_t(B) * MPPI_MAX_NX, h->d_res + size_t(B) * RES_SCALARS, N, h->shift_k);
     h->launches++;
   }
+  // the rollout as a programmatic dependent of begin_kernel (nothing else between them on the stream)
+  const bool pdl_in = h->pdl && !timed && B == 1 && (v & (V_H2D_IN | V_H2D_X0 | V_H2D_U)) && !(v & (V_ADOPT | V_SHIFT | V_NOISE_NOW)) && (v & V_LOCAL);
   const bool pregen = SRC == SRC_PHILOX && (v & V_PREGEN) && (v & V_LOCAL);
   // A rollout that READS eps (host-supplied or pre-generated) stages its block's slab in shared memory by bulk
   // copies when the slab is small enough to keep the occupancy: N rows of ROLLOUT_BS * LANES samples.
@@ -151,7 +153,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
             prefer_shared_carveout(rollout_kernel<f32x2, PK, SRC_SUPPLIED>);
             cudaFuncSetAttribute(rollout_kernel<f32x2, PK, SRC_SUPPLIED>, cudaFuncAttributeMaxDynamicSharedMemorySize, EPS_SLAB_MAX + 8192);
           }
-          rollout_kernel<f32x2, PK, SRC_SUPPLIED><<<grid, ROLLOUT_BS, smemU + smemE, s>>>(p, buf);
+          MPPI_CUDA(h, launch_step_kernel(rollout_kernel<f32x2, PK, SRC_SUPPLIED>, grid, dim3(ROLLOUT_BS), smemU + smemE, s, pdl_in, p, buf));
           done = true;
         }
       }
@@ -159,7 +161,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
         dim3 grid((K + ROLLOUT_BS - 1) / ROLLOUT_BS, B);
         static unsigned long long carved = 0;
         if (first_on_device(carved)) prefer_shared_carveout(rollout_kernel<R, Model, SRC_SUPPLIED>);
-        rollout_kernel<R, Model, SRC_SUPPLIED><<<grid, ROLLOUT_BS, smemU + smemE, s>>>(p, buf);
+        MPPI_CUDA(h, launch_step_kernel(rollout_kernel<R, Model, SRC_SUPPLIED>, grid, dim3(ROLLOUT_BS), smemU + smemE, s, pdl_in, p, buf));
       }
     }
     if constexpr (std::is_same<R, float>::value) {
@@ -175,7 +177,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
             prefer_shared_carveout(rollout_kernel<f32x2, PK, SRC>);
             cudaFuncSetAttribute(rollout_kernel<f32x2, PK, SRC>, cudaFuncAttributeMaxDynamicSharedMemorySize, EPS_SLAB_MAX + 8192);
           }
-          rollout_kernel<f32x2, PK, SRC><<<grid, ROLLOUT_BS, smemU + smemE, s>>>(p, buf);
+          MPPI_CUDA(h, launch_step_kernel(rollout_kernel<f32x2, PK, SRC>, grid, dim3(ROLLOUT_BS), smemU + smemE, s, pdl_in, p, buf));
         }
         launched = true;
       }
@@ -188,7 +190,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
       if (!track) {
         static unsigned long long carved = 0;
         if (SRC == SRC_SUPPLIED && first_on_device(carved)) prefer_shared_carveout(rollout_kernel<R, Model, SRC>);
-        rollout_kernel<R, Model, SRC><<<grid, ROLLOUT_BS, smemU + smemE, s>>>(p, buf);
+        MPPI_CUDA(h, launch_step_kernel(rollout_kernel<R, Model, SRC>, grid, dim3(ROLLOUT_BS), smemU + smemE, s, pdl_in, p, buf));
       }
     }
     h->launches++;

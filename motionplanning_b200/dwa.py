@@ -64,17 +64,13 @@ def defineDWAobs(dwa, obstacle_list):
 def DWAPlan(dwa):
     """DWAPlan (DWAUtils.jl:141-163): every candidate rolled out, BestCand = minimum by cost.
     r.Control is the selected candidate's control VECTOR (BestCand.Control = ctrl_list, :156)."""
-    cfg = dwa._cfg
-    N, nx = cfg.N, cfg.n_x
-    ctrl = np.empty((N, 2), dtype=np.float64, order="F")
-    traj = np.empty((N + 1, nx), dtype=np.float64, order="F")
     res = dwa._res
-    res.Control, res.Traj = ctrl.ctypes.data, traj.ctypes.data
+    res.Control, res.Traj = dwa._ctrl_ptr, dwa._traj_ptr           # staging arrays of the handle (addresses taken once)
     if dwa._f_step(dwa._hv, None, dwa._res_ptr):
         dwa._check(1)
     r = dwa.r
-    r.Traj = traj                                                   # :155
-    r.Control = ctrl[0].copy()                                      # :156  (constant over the horizon)
+    r.Traj = dwa._traj_buf.copy(order="F")                          # :155
+    r.Control = dwa._ctrl_buf[0].copy()                             # :156  (constant over the horizon)
     r.Feasibility = "Feasible" if res.feasible else "InFeasible"    # :157
     r.cost = res.cost                                               # :158
     r.time = res.time_s                                             # :160

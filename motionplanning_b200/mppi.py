@@ -112,6 +112,11 @@ class MPPISearcher:  # types.jl:46-50
         self._f_step = C.CFUNCTYPE(C.c_int32, vp, vp, vp)(("mppi_step", lib))
         self._res = capi.Result()
         self._res_ptr = C.addressof(self._res)
+        # result staging: the library fills these two arrays (addresses taken once: `ndarray.ctypes.data` costs
+        # 2 us a time, and it sits in FRONT of the step); every plan hands out fresh copies, like the reference
+        self._ctrl_buf = np.zeros((cfg.N, 2), dtype=np.float64, order="F")
+        self._traj_buf = np.zeros((cfg.N + 1, cfg.n_x), dtype=np.float64, order="F")
+        self._ctrl_ptr, self._traj_ptr = self._ctrl_buf.ctypes.data, self._traj_buf.ctypes.data
 
     # -- plumbing ---------------------------------------------------------
     def _check(self, rc):
@@ -447,15 +452,16 @@ def MPPIPlan(mppi, noise=None):
     """MPPIPlan (MPPIUtils.jl:169-203).  `noise` (N, K, m) only in SUPPLIED-noise mode."""
     cfg = mppi._cfg
     N, nx = cfg.N, cfg.n_x
-    ctrl = np.empty((N, 2), dtype=np.float64, order="F")
-    traj = np.empty((N + 1, nx), dtype=np.float64, order="F")
     res = mppi._res
-    res.Control, res.Traj = ctrl.ctypes.data, traj.ctypes.data
-    if noise is None:
+    if noise is None:   # the per-step call (main.jl:61)
+        res.Control, res.Traj = mppi._ctrl_ptr, mppi._traj_ptr
         if mppi._f_step(mppi._hv, None, mppi._res_ptr):
             mppi._check(1)
-        _store(mppi, res, ctrl, traj)
+        _store(mppi, res, mppi._ctrl_buf.copy(order="F"), mppi._traj_buf.copy(order="F"))
         return None
+    ctrl = np.empty((N, 2), dtype=np.float64, order="F")
+    traj = np.empty((N + 1, nx), dtype=np.float64, order="F")
+    res.Control, res.Traj = ctrl.ctypes.data, traj.ctypes.data
     nptr = None
     if noise is not None:
         want = np.float64 if cfg.precision == capi.FP64 else np.float32

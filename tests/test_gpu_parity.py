@@ -225,3 +225,25 @@ def test_packed_philox_stream_is_identical(built):
         m.MPPIPlan(mppi)
         eps.append(mppi.noise())
     assert np.array_equal(eps[0], eps[1])
+
+
+@pytest.mark.parametrize("precision,K,N,variant", [(capi.FP32, 130, 33, 1), (capi.FP32, 130, 33, 2), (capi.FP32, 64 * 3 + 6, 50, 1),
+                                                   (capi.FP32, 128 * 2 + 2, 50, 2), (capi.FP64, 129, 31, 1), (capi.FP64, 2, 5, 1)])
+def test_staged_eps_slab_ragged_blocks(built, precision, K, N, variant):
+    """Rollouts that READ eps stage their block's slab in shared memory with one bulk copy (TMA) per horizon row
+    (rollout_kernel).  Sizes whose last block holds only a few samples (row copies of 16 or 48 bytes),
+    horizons that are not a multiple of the 8-row barrier group, one-sample and packed threads; host-supplied noise
+    against the oracle, then the same scene with pre-generated Philox noise against Philox inside the rollout (bit for bit)."""
+    args, kw, circles, blocks = sc.config(0, K=K, N=N)
+    mppi, ref = run_pair(args, dict(kw, rollout_variant=variant), circles, blocks, precision, Unom=warm_nominal(N))
+    check(mppi, ref, precision)
+    kwp = dict(kw, precision=precision, noise_mode=capi.NOISE_PHILOX)
+    pair = []
+    for v in (variant, variant + 2):     # pre-generated noise (slab staged) | Philox inside the rollout
+        h = m.defineMPPI(*args, **dict(kwp, rollout_variant=v))
+        m.defineMPPIobs(h, circles)
+        m.defineMPPINominalControl(h, warm_nominal(N))
+        m.MPPIPlan(h), m.MPPIPlan(h)     # second plan: the rollout reads what noise_kernel drew beside the first finalize
+        pair.append((h.p.costs.copy(), h.p.flags.copy(), h.r.Control.copy(), h.noise()))
+    for a, b in zip(*pair):
+        assert np.array_equal(a, b)

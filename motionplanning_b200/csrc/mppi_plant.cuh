@@ -64,15 +64,21 @@ __global__ void plant_kernel(const __grid_constant__ StaticParams<double> p, con
 #pragma unroll
   for (int i = 0; i < NX; ++i) s[i] = a.x0[i];
   bool done = false;
+  // The held controls change at most a few times per block of plant steps: they are re-read from global memory only when
+  // the knot index moves (a dependent L2 round trip per step otherwise, a third of the step), and the knot index comes from
+  // a multiplication by the reciprocal spacing, made exact by the two corrections below.
+  const double inv_knot = a.knot_dt > 0.0 ? 1.0 / a.knot_dt : 0.0;
+  int jc = -1;
+  double sr = 0.0, ax = 0.0;
   for (int i = 0; i < a.steps && !done; ++i) {
     // controls[i, :] = Constant{Previous} interpolation of U_new at fined_time_serial[i] (:65-67):
     // the last knot of time_serial that is <= t
     const double tf = double(i) * a.fine_dt;
-    int j = a.knot_dt > 0.0 ? int(tf / a.knot_dt) : 0;
+    int j = int(tf * inv_knot);
     j = max(0, min(j, a.N - 1));
     while (j + 1 < a.N && double(j + 1) * a.knot_dt <= tf) ++j;
     while (j > 0 && double(j) * a.knot_dt > tf) --j;
-    const double sr = a.U[j], ax = a.U[a.N + j];
+    if (j != jc) { jc = j; sr = a.U[j]; ax = a.U[a.N + j]; }
     double d[NX];
     PlantDeriv<Model>::run(p, s, sr, ax, d);      // :76
 #pragma unroll

@@ -191,8 +191,12 @@ struct NominalStates<Kin5<R>> {
       carry = __shfl_sync(0xffffffffu, v, 31);
     }
   }
+  static __device__ __forceinline__ void sub_barrier() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
   static __device__ __forceinline__ void run(const StaticParams<R>& p, const double* x0, const R* sNew, R* sX, R* sT, int N, int t) {
-    const int nt = blockDim.x;
+    // At most 257 rows: four warps do all of it and meet on a NAMED barrier (bar.sync 1, 128); a block-wide barrier of
+    // 32 warps costs ~250 cycles and this routine needs six of them.  The other warps go straight to the closing barrier.
+    constexpr int nt = 128;
+    if (t < nt) {
     // scan 1: sa (warp 0) and ux (warp 1) are running sums of the controls: s + u*dt
     const int lane = t & 31;
     // (row 0 is written by a third warp: nvcc threads a lane-dependent `if` ahead of a scan into the
@@ -201,15 +205,15 @@ struct NominalStates<Kin5<R>> {
     if (t < 32) warp_scan(sNew, 2, p.dt, R(x0[4]), sX + 4, N, lane);
     else if (t < 64) warp_scan(sNew + 1, 2, p.dt, R(x0[3]), sX + 3, N, lane);
     else if (t < 64 + NX) sX[t - 64] = R(x0[t - 64]);
-    __syncthreads();
+    sub_barrier();
     for (int j = t; j <= N; j += nt) sT[3 * j] = M::over(M::tan(sX[j * ROW + 4]), p.Lwb, p.inv_Lwb);   // tan(sa_j)/L
-    __syncthreads();
+    sub_barrier();
     for (int j = t; j < N; j += nt)   // k1p + k2p of step j
       sT[3 * j + 1] = M::fma(sX[(j + 1) * ROW + 3], sT[3 * (j + 1)], sX[j * ROW + 3] * sT[3 * j]);
-    __syncthreads();
+    sub_barrier();
     // scan 2: psi_{j+1} = psi_j + dt/2 (k1p + k2p)
     if (t < 32) warp_scan(sT + 1, 3, p.half_dt, sX[2], sX + 2, N, lane);
-    __syncthreads();
+    sub_barrier();
     for (int j = t; j <= N; j += nt) {
       R* row = sX + j * ROW;
       M::sincos(row[2], &row[5], &row[6]);                         // carried sin/cos of psi_j
@@ -222,10 +226,11 @@ struct NominalStates<Kin5<R>> {
         sT[3 * j + 2] = M::fma(uxt, st, row[3] * row[5]);          // k1y + k2y
       }
     }
-    __syncthreads();
+    sub_barrier();
     // scan 3: x (warp 0) and y (warp 1)
     if (t < 32) warp_scan(sT + 1, 3, p.half_dt, sX[0], sX + 0, N, lane);
     else if (t < 64) warp_scan(sT + 2, 3, p.half_dt, sX[1], sX + 1, N, lane);
+    }
     __syncthreads();
   }
 };

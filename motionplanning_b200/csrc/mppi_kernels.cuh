@@ -203,7 +203,7 @@ __device__ __forceinline__ void rollout_horizon(const StaticParams<typename Math
 // beside finalize, which increments iter[0] at an unknown moment.
 // ---------------------------------------------------------------------------
 constexpr int NOISE_BS = 256;
-constexpr int NOISE_PAIRS = 2;   // Philox calls per thread: the index / parameter prologue is a fifth of a one-call thread
+constexpr int NOISE_PAIRS = 4;   // Philox calls per thread: the index / parameter prologue is a fifth of a one-call thread
 template <class R>
 __global__ void __launch_bounds__(NOISE_BS) noise_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf,
                                                          const unsigned int* __restrict__ iter_ptr, int delta) {

@@ -38,11 +38,8 @@ WORKLOADS = {
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu captures
-# (profiles/r01_ncu_*.md), keyed by --config: (rollout kernel, update kernel); N = 1 only.
-NCU_TRAFFIC = {
-    1: (26_285_824 + 0, 26_491_136 + 0),                        # rollout reads the pre-generated eps (26.2 MB algorithmic)
-    2: (167_845_632 + 4_443_136, 168_838_656 + 3_827_200),
-    3: (839_461_376 + 9_430_784, 843_085_056 + 3_552_768),
+# (profiles/r02_ncu_*.md): (rollout / scan kernel, update kernel); N = 1 only.
+NCU_TRAFFIC = {   # key: (--config, --walls)
 }
 
 
@@ -54,6 +51,9 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", type=int, default=1, help="index into BASELINE.json configs (default 1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--walls", type=int, default=0, help="cfg4 only: number of wall blocks M_p (default 3; SURVEY 8(d) asks for 3 and 16)")
+    ap.add_argument("--x0", default="", help="override the start state, comma separated (cfg4: a pose from which the walls are reached)")
+    ap.add_argument("--noise-policy", type=int, default=0, help="0 auto | 1 latency (pre-generated noise) | 2 throughput (Philox inside the rollout)")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="N > 1: softmin all-gather in-kernel over NVLink peer memory (default) or in-library NCCL")
     return ap.parse_args()
@@ -116,6 +116,43 @@ def host_cores():
         return os.cpu_count() or 1
 
 
+def load_scenarios():
+    """motionplanning_b200/scenarios.py loaded BY PATH: pure host data, and the CPU legs (cpu_baseline, --impl reference)
+    must not import the product package or map libmppi_b200.so."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("mppi_scenarios", os.path.join(ROOT, "motionplanning_b200", "scenarios.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def config_keys(cfg_idx, world):
+    """`config` of the JSON line: the workload and nothing else, identical in both arms."""
+    sc = load_scenarios()
+    args, kw, _, _ = sc.config(cfg_idx)
+    K, N, B = args[5], args[7], kw.get("B", 1)
+    if cfg_idx in (0, 1, 2):
+        K *= world          # sample-sharded, weak scaling: 65,536 (cfg2) per GPU
+    return {"workload": WORKLOADS[cfg_idx], "K_total": K, "N": N, "instances": B}
+
+
+def cpu_problem(cfg_idx):
+    """The bounded CPU sample of a workload: at most 65,536 samples of ONE instance, supplied noise, FP64."""
+    import oracle_lib as orc
+
+    sc = load_scenarios()
+    args, kw, circles, blocks = sc.config(cfg_idx)
+    K = min(args[5], 65536)
+    N = args[7]
+    args = args[:5] + (K,) + args[6:]
+    kw = dict(kw, precision=orc.FP64, noise_mode=orc.NOISE_SUPPLIED, FeasibilityCount=K)
+    kw.pop("B", None)
+    cfg = orc.make_config(args, kw)
+    eps = orc.generate_noise(args[6], sc.SEED, 0, K, N, orc.FP64)
+    return orc, cfg, circles, blocks, args, eps, K, N
+
+
 def workload(cfg_idx, world, rank):
     """defineMPPI arguments for this rank.  Sample-sharded configs keep the per-GPU shard fixed
     (weak scaling); cfg4's K = 1,048,576 is the TOTAL (strong scaling, as BASELINE.json states it);
@@ -145,73 +182,126 @@ def workload(cfg_idx, world, rank):
 def cpu_baseline(cfg_idx, budget_s=12.0, threads=None):
     """Time the CPU path (C++ oracle port of the reference's Julia MPPIPlan, FP64) on this box's
     host cores, on a bounded sample of the workload: at most 65,536 samples per repetition,
-    repeated until ~budget_s of wall time."""
-    import oracle_lib as orc
-    from motionplanning_b200 import _capi as capi
-    from motionplanning_b200 import scenarios as sc
-
+    repeated until ~budget_s of wall time.  Also: the same plan on ONE thread (the reference has no
+    threading; 4,096-sample slice) and the number of samples of the slice that sit inside the FP32
+    guard band (closest threshold comparison within 1e-4 relative of flipping)."""
+    orc, cfg, circles, blocks, args, eps, K, N = cpu_problem(cfg_idx)
     threads = threads or host_cores()
-    args, kw, circles, blocks = sc.config(cfg_idx)
-    K = min(args[5], 65536)
-    N = args[7]
-    args = args[:5] + (K,) + args[6:]
-    kw = dict(kw, precision=capi.FP64, noise_mode=capi.NOISE_SUPPLIED, FeasibilityCount=K)
-    kw.pop("B", None)
-    cfg = orc.make_config(args, kw)
-    eps = orc.generate_noise(args[6], sc.SEED, 0, K, N, capi.FP64)
     U = np.zeros((N, 2))
     secs, reps = [], 0
     t_end = time.perf_counter() + budget_s
     while reps < 2 or (time.perf_counter() < t_end and reps < 200):
-        r = orc.plan(cfg, circles, blocks, args[3], U, eps, capi.FP64, threads=threads)
+        r = orc.plan(cfg, circles, blocks, args[3], U, eps, orc.FP64, threads=threads)
         U = r["Control"]
         secs.append(r["seconds"])
         reps += 1
     best = float(np.median(secs))
+    # single thread, faithful to the reference's structure (serial K loop): a 4,096-sample slice, scaled per sample-step
+    K1 = min(K, 4096)
+    cfg1 = orc.make_config(args[:5] + (K1,) + args[6:], dict(model=cfg.model, precision=orc.FP64, noise_mode=orc.NOISE_SUPPLIED,
+                                                             FeasibilityCount=K1, veh_L=cfg.veh_L, veh_W=cfg.veh_W,
+                                                             veh_center_offset=cfg.veh_center_offset))
+    eps1 = np.ascontiguousarray(eps[:, :K1, :])
+    one = [orc.plan(cfg1, circles, blocks, args[3], U, eps1, orc.FP64, threads=1, want_margin=(i == 0)) for i in range(3)]
+    t1 = float(np.median([o["seconds"] for o in one]))
+    guard = int(np.sum(one[0]["margins"] < 1e-4))
     return {"value": K * N / best, "unit": UNIT, "cores": threads, "kind": "port",
             "sample": f"{K} of the workload's samples x N={N}, full MPPIPlan (FP64, supplied noise), "
                       f"median of {reps} repetitions, OpenMP over samples",
-            "ms_per_iteration": best * 1e3}, K, N
+            "ms_per_iteration": best * 1e3,
+            "single_thread": {"value": K1 * N / t1, "unit": UNIT, "cores": 1,
+                              "sample": f"{K1} samples x N={N}, serial K loop as in MPPIUtils.jl:175, median of 3"},
+            "guard_band_samples": guard, "guard_band_of": K1,
+            "guard_band_note": "samples whose closest obstacle/bound comparison is within 1e-4 relative of flipping in the FP64 oracle "
+                               "(the FP32 fast path may legitimately flip these; strict_math = 1 matches a float oracle bit for bit)"}, K, N
 
 
 def run_reference(a, rank, world):
     """Reference arm: the reference's own CPU implementation of the path.  Julia is not
     installed on either box and the reference has no compiled code, so this times the oracle
-    port (kind "port") with all host threads.  Each step = one MPPIPlan on a bounded sample."""
+    port (kind "port") with all host threads.  Each step = one MPPIPlan on a bounded sample.
+    Imports nothing of the product (tests/test_oracle_config.py::test_oracle_wrapper_never_loads_the_product)."""
     if rank != 0:
         return
-    import oracle_lib as orc
-    from motionplanning_b200 import _capi as capi
-    from motionplanning_b200 import scenarios as sc
-
+    orc, cfg, circles, blocks, args, eps, K, N = cpu_problem(a.config)
     threads = host_cores()
-    args, kw, circles, blocks = sc.config(a.config)
-    K = min(args[5], 65536)
-    N = args[7]
-    args = args[:5] + (K,) + args[6:]
-    kw = dict(kw, precision=capi.FP64, noise_mode=capi.NOISE_SUPPLIED, FeasibilityCount=K)
-    kw.pop("B", None)
-    cfg = orc.make_config(args, kw)
-    eps = orc.generate_noise(args[6], sc.SEED, 0, K, N, capi.FP64)
     U = np.zeros((N, 2))
-    steps = min(a.steps, 50)   # bounded: ~0.1-1 s per CPU iteration
-    warm = min(a.warmup, 3)
+    steps, warm = a.steps, max(a.warmup, 3)
     for _ in range(warm):
-        U = orc.plan(cfg, circles, blocks, args[3], U, eps, capi.FP64, threads=threads)["Control"]
+        U = orc.plan(cfg, circles, blocks, args[3], U, eps, orc.FP64, threads=threads)["Control"]
     t0 = time.perf_counter()
     for _ in range(steps):
-        U = orc.plan(cfg, circles, blocks, args[3], U, eps, capi.FP64, threads=threads)["Control"]
+        U = orc.plan(cfg, circles, blocks, args[3], U, eps, orc.FP64, threads=threads)["Control"]
     dt = time.perf_counter() - t0
     v = K * N * steps / dt
+    scaling = "strong" if a.config in (3, 4) else "weak"
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": steps,
-            "warmup": warm, "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "warmup": warm, "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": scaling,
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOADS[a.config], "samples_per_step": K, "horizon": N},
+            "config": config_keys(a.config, world),
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                              "sample": f"{K} samples x N={N} per step, {steps} steps, OpenMP over samples; "
                                        "reference Julia path: unavailable on this box (no julia)"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
+
+
+def parity_across_ranks(m, mdist, args, kw, circles, blocks, exchange, rank, world, local_rank, iters=3):
+    """N > 1, outside the timed region: the sharded step (this rank's shard + the exchange under test) against ONE
+    unsharded handle with K = K_total on this rank's GPU, same seed, same iteration, `iters` chained iterations.
+    Costs come from the same kernel on both sides (the unsharded handle is forced onto the sharded handle's rollout
+    variant), so what is checked is exactly the exchange + combine: argmin, RolloutCount, FeasibleTrajCount identical,
+    |U_new - U_ref| <= 2e-6 max|U_ref|, and U_new bit-identical on all ranks.  Raises on mismatch (rc != 0)."""
+    import torch
+    import torch.distributed as dist
+
+    capi = m.capi
+    sh = m.defineMPPI(*args, **kw)
+    if circles:
+        m.defineMPPIobs(sh, circles)
+    if blocks:
+        m.defineMPPIblocks(sh, blocks)
+    if exchange == "peer":
+        mdist.init_peer_exchange(sh)
+    else:
+        mdist.init_library_comm(sh)
+    info = sh.plan_info()
+    kw_ref = dict(kw, k_offset=0, K_local=0)
+    kw_ref["rollout_variant"] = 5 if info["scan"] else (2 if info["packed"] else 1)
+    kw_ref["noise_policy"] = 1 if info["pregen"] else 2
+    ref = m.defineMPPI(*args, **kw_ref)
+    if circles:
+        m.defineMPPIobs(ref, circles)
+    if blocks:
+        m.defineMPPIblocks(ref, blocks)
+    N = args[7]
+    U = np.zeros((N, 2))
+    max_du, ok_arg, ok_cnt = 0.0, True, True
+    for _ in range(iters):
+        m.defineMPPINominalControl(sh, U)
+        m.defineMPPINominalControl(ref, U)
+        m.MPPIPlan(sh)
+        m.MPPIPlan(ref)
+        scale = max(float(np.abs(ref.r.Control).max()), 1e-12)
+        max_du = max(max_du, float(np.abs(sh.r.Control - ref.r.Control).max()) / scale)
+        ok_arg &= sh.r.argmin == ref.r.argmin
+        ok_cnt &= sh.r.RolloutCount == ref.r.RolloutCount and sh.r.FeasibleTrajCount == ref.r.FeasibleTrajCount
+        U = sh.r.Control.copy()
+    mine = torch.from_numpy(np.ascontiguousarray(U).view(np.uint8).reshape(-1).copy()).cuda()
+    allU = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(allU, mine)
+    identical = all(bool(torch.equal(allU[0], t)) for t in allU)
+    flags = torch.tensor([max_du, 0.0 if ok_arg else 1.0, 0.0 if ok_cnt else 1.0, 0.0 if identical else 1.0], dtype=torch.float64, device="cuda")
+    dist.all_reduce(flags, op=dist.ReduceOp.MAX)
+    out = {"checked": True, "iterations": iters, "exchange": exchange, "max_du": float(flags[0]), "tol_du": 2e-6,
+           "argmin_equal": flags[1].item() == 0.0, "counts_equal": flags[2].item() == 0.0,
+           "ranks_bit_identical": flags[3].item() == 0.0,
+           "against": "one unsharded handle (K = K_total) per rank, same seed / iteration / rollout kernel"}
+    sh.close()
+    ref.close()
+    if not (out["max_du"] <= out["tol_du"] and out["argmin_equal"] and out["counts_equal"] and out["ranks_bit_identical"]):
+        raise SystemExit(f"[rank {rank}] sharded step differs from the unsharded one: {json.dumps(out)}")
+    return out
 
 
 def run_ours(a, rank, world, local_rank):
@@ -227,28 +317,36 @@ def run_ours(a, rank, world, local_rank):
     N, nx = args[7], args[0]
     B = kw.get("B", 1)
     kw.update(device=local_rank, precision=capi.FP32, noise_mode=capi.NOISE_PHILOX)
+    if a.walls:
+        blocks = sc.wall_blocks(a.walls)
+    if a.x0:
+        args = args[:3] + ([float(v) for v in a.x0.split(",")],) + args[4:]
+    if a.noise_policy:
+        kw["noise_policy"] = a.noise_policy
     batched = B > 1
     if batched:
         x0s = sc.jittered_x0(B, seed=7 + rank)
         args = args[:3] + (x0s,) + args[4:]
+    exchange = "none"
+    parity_n = None
+    if world > 1 and not batched:
+        exchange = a.exchange
+        # correctness of the sharded step, outside the timed region, recorded in the JSON line (fails the run on mismatch)
+        parity_n = parity_across_ranks(m, mdist, args, kw, circles, blocks, exchange, rank, world, local_rank)
     mppi = m.defineMPPI(*args, **kw)
     if circles:
         m.defineMPPIobs(mppi, circles)
     if blocks:
         m.defineMPPIblocks(mppi, blocks)
-    exchange = "none"
-    if world > 1 and not batched:
-        exchange = a.exchange
-        if exchange == "peer":
-            try:
-                mdist.init_peer_exchange(mppi)
-            except Exception as e:  # no peer access between these devices: NCCL carries the exchange
-                print(f"[rank {rank}] peer exchange unavailable ({e}); using NCCL", file=sys.stderr)
-                exchange = "nccl"
-        if exchange == "nccl":
-            mdist.init_library_comm(mppi)
+    if exchange == "peer":
+        mdist.init_peer_exchange(mppi)   # no silent fallback: without peer access between the GPUs this raises; ask for --exchange nccl
+    elif exchange == "nccl":
+        mdist.init_library_comm(mppi)
+    info = mppi.plan_info()
 
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")   # > 126 MB L2
+    lib_stream = torch.cuda.ExternalStream(mppi.stream(), device=torch.device("cuda", local_rank))
+    sync_t = torch.zeros(1, device="cuda")
 
     def l2_flush():
         flush.zero_()
@@ -271,10 +369,11 @@ def run_ours(a, rank, world, local_rank):
 
     # ---- device-resident timing: one graph launch per iteration, CUDA events on the LIBRARY's
     #      stream, L2 flushed (256 MiB write on the same stream) before every timed iteration.
-    #      Everything is enqueued asynchronously, so host jitter never enters the timed spans and
-    #      the ranks of a sharded run stay in lockstep through the step's own exchange. ----
-    lib_stream = torch.cuda.ExternalStream(mppi.stream(), device=torch.device("cuda", local_rank))
-    for _ in range(max(a.warmup, 3)):
+    #      Everything is enqueued asynchronously, so host jitter never enters the timed spans.  N > 1: the ranks
+    #      meet in a one-element all-reduce on the same stream between the flush and the first event, so that the
+    #      differing durations of the ranks' flushes do not count as step time; the step's own exchange is inside. ----
+    warm = max(a.warmup, 3)
+    for _ in range(warm):
         mppi.step_async(adopt=False)
     mppi.sync()
     clocks = ClockSampler(local_rank)
@@ -286,6 +385,8 @@ def run_ours(a, rank, world, local_rank):
     for i in range(a.steps):
         with torch.cuda.stream(lib_stream):
             flush.zero_()
+            if world > 1 and not batched:
+                torch.distributed.all_reduce(sync_t)
         ev0[i].record(lib_stream)
         mppi.step_async(adopt=False)
         ev1[i].record(lib_stream)
@@ -303,28 +404,36 @@ def run_ours(a, rank, world, local_rank):
     value = units_per_step * a.steps / total_s
 
     # ---- end to end through the reference-facing API with HOST buffers, every step:
-    #      ShiftInitialCondition + defineMPPINominalControl! + MPPIPlan (main.jl:59-62) ----
+    #      ShiftInitialCondition + defineMPPINominalControl! + MPPIPlan (main.jl:59-62).  The timed span of a step
+    #      ends when the handle's stream is IDLE (mppi.sync() after the call returns), so work the step leaves behind
+    #      the delivery of its result (the next iteration's noise under the "latency" policy) is inside it; the time
+    #      to the result alone is reported as latency_us.e2e_result_*. ----
     U_host = np.array(mppi.s.NominalControl if batched else mppi.r.Control, copy=True)
     x_host = np.array(mppi.s.X0, dtype=np.float64, copy=True)
-    e2e_s = []
+    e2e_s, e2e_res_s = [], []
     if batched:   # host buffers in the ABI's own layout (what a Julia caller holds): no reshuffling in the timed call
         xb = np.ascontiguousarray(x_host.T)                                  # (B, n_x)
         Ub = np.ascontiguousarray(np.transpose(U_host, (2, 1, 0))) if U_host.ndim == 3 else np.zeros((B, 2, N))
-        Uo, cb, fb = np.empty_like(Ub), np.empty(B), np.empty(B, dtype=np.int32)
-    gc.disable()   # the timed calls are ~60 us each: a collector pause would be the largest term in the sum
+        Uo, cb_, fb = np.empty_like(Ub), np.empty(B), np.empty(B, dtype=np.int32)
+    gc.disable()   # the timed calls are tens of us each: a collector pause would be the largest term in the sum
     for i in range(a.steps + 3):
         l2_flush()
+        if world > 1:
+            torch.distributed.barrier()
         t0 = time.perf_counter()
         if batched:
-            mppi.step_batched_abi(xb, Ub, Uo, cb, fb)
+            mppi.step_batched_abi(xb, Ub, Uo, cb_, fb)
         else:
             m.ShiftInitialCondition(mppi, x_host)
             m.defineMPPINominalControl(mppi, U_host)
             m.MPPIPlan(mppi)
             _ = mppi.r.Control[0, 0]
         t1 = time.perf_counter()
+        mppi.sync()
+        t2 = time.perf_counter()
         if i >= 3:
-            e2e_s.append(t1 - t0)
+            e2e_res_s.append(t1 - t0)
+            e2e_s.append(t2 - t0)
     gc.enable()
     e2e_total = float(np.sum(e2e_s))
     if world > 1:
@@ -334,16 +443,18 @@ def run_ours(a, rank, world, local_rank):
     e2e_value = units_per_step * a.steps / e2e_total
     h2d = B * (nx + 2 * N) * 8
     d2h = B * (8 + 2 * N) * 8 + (0 if batched else (N + 1) * nx * 8)
-
-    # ---- per-kernel times (eager launches bracketed by events on the library stream) ----
-    mppi.set_profiling(True)
+    # ---- per-kernel times: eager launches bracketed by CUDA events on the library stream (mppi_set_profiling(1)); the L2
+    #      flush is enqueued on the same stream right before, without a host synchronise in between, so the events do not
+    #      also time an idle GPU's launch latency.  The scan-form step launches its tail as a separate kernel in this mode. ----
+    mppi.set_profiling(1)
     k_us = []
-    for _ in range(12):
-        l2_flush()
+    for _ in range(14):
+        with torch.cuda.stream(lib_stream):
+            flush.zero_()
         mppi.step_async(adopt=False)
         mppi.sync()
         k_us.append(mppi.timings_us())
-    mppi.set_profiling(False)
+    mppi.set_profiling(0)
     k_us = np.median(np.array(k_us[2:]), axis=0)
     # ---- the same kernels inside the replayed graph: %globaltimer first-block-in / last-block-out spans
     #      (mppi_set_profiling(2)); free of the launch and event gaps an eager bracket includes ----
@@ -357,67 +468,95 @@ def run_ours(a, rank, world, local_rank):
             mppi.sync()
             c = mppi.phase_clocks()
             if i >= 2:
-                noise = c[15] > 0 and c[14] < 2 ** 63   # noise_kernel for the next iteration ran beside finalize (V_PREGEN)
-                spans.append([(c[9 + 2 * j] - c[8 + 2 * j]) * 1e-3 for j in range(3)] + [(c[13] - c[8]) * 1e-3] +
-                             ([(c[15] - c[14]) * 1e-3, (max(c[13], c[15]) - c[8]) * 1e-3] if noise else [0.0, (c[13] - c[8]) * 1e-3]))
+                def span(j):
+                    return (c[9 + 2 * j] - c[8 + 2 * j]) * 1e-3 if (c[9 + 2 * j] > 0 and c[8 + 2 * j] < 2 ** 63) else 0.0
+                noise = c[15] > 0 and c[14] < 2 ** 63   # noise_kernel for the next iteration ran behind the step
+                last = max(c[13], c[15]) if noise else c[13]
+                spans.append([span(0), span(1), span(2), (c[13] - c[8]) * 1e-3, span(3), (last - c[8]) * 1e-3])
         mppi.set_profiling(0)
         g_us = np.median(np.array(spans), axis=0)
     fp32_peak = mppi.measure_fp32_peak()
     peaks, peak_src = measured_peaks()
     F = sc.flop_per_sample_step(kw["model"], len(circles), len(blocks))
     local_units = kl * N * B
+    fused = bool(info["scan"])
     roll_tflops = local_units * F / (k_us[0] * 1e-6) / 1e12
-    upd_bytes = local_units * 2 * 4 + kl * B * 4 + N * 2 * 4 * B
-    upd_gbs = upd_bytes / (k_us[1] * 1e-6) / 1e9
+    eps_bytes = local_units * 2 * 4
+    upd_bytes = eps_bytes + kl * B * 4 + N * 2 * 4 * B
+    traffic = NCU_TRAFFIC.get((a.config, a.walls or 0), (None, None)) if world == 1 else (None, None)
 
     line = None
     if rank == 0:
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": warm,
             "ms_per_step": total_s / a.steps * 1e3, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOADS[a.config], "K_total": K if not batched else K, "K_per_gpu": kl, "N": N,
-                       "instances": B * (world if batched else 1), "noise": ("philox4x32-10 on the device, one tensor drawn per step inside the timed region: noise_kernel draws the next "
-                                 "iteration's tensor on a graph branch beside finalize, the rollout reads it back (TMA-staged)"
-                                 if not batched else "philox4x32-10 inside the rollout kernel"),
-                       "parallelism": (f"samples sharded x{world}, softmin all-gather in the finalize kernel over NVLink peer memory"
-                                       if exchange == "peer" else f"samples sharded x{world}, one NCCL all-gather per step") if world > 1 and not batched
-                       else ("instances sharded, no collective" if batched and world > 1 else "1 GPU"),
-                       "l2": "flushed between timed iterations (256 MiB write)",
-                       "timing": "CUDA events on the library stream around one graph launch per iteration (flush + step enqueued asynchronously), summed, max over ranks"},
+            "config": config_keys(a.config, world),
+            "method": {
+                "K_per_gpu": kl, "walls": len(blocks), "circles": len(circles),
+                "step": ("scan-form fused kernel: horizon-parallel rollout + cost + online softmin + weighted update, tail (fold, exchange, "
+                         "combine, nominal rollout) in its last CTA" if fused else "rollout_kernel -> update_kernel -> finalize_kernel"),
+                "noise": ("philox4x32-10 on the device, one tensor per step inside the timed region: noise_kernel draws the NEXT iteration's tensor "
+                          "behind the step, the rollout reads it back" if info["pregen"] else "philox4x32-10 inside the rollout kernel"),
+                "parallelism": ((f"samples sharded x{world}, softmin all-gather inside the step kernel over NVLink peer memory"
+                                 if exchange == "peer" else f"samples sharded x{world}, one NCCL all-gather per step") if world > 1 and not batched
+                                else ("instances sharded, no collective" if batched and world > 1 else "1 GPU")),
+                "l2": "flushed between timed iterations (256 MiB write)",
+                "timing": "CUDA events on the library stream around one graph launch per iteration (flush + step enqueued asynchronously), "
+                          "summed, max over ranks" + ("; ranks aligned by a one-element all-reduce between flush and first event" if world > 1 and not batched else ""),
+                "plan_info": info},
             "latency_us": {"device_median": float(np.median(dev_us)), "device_p99": float(np.percentile(dev_us, 99)),
-                           "e2e_median": float(np.median(e2e_s) * 1e6), "e2e_p99": float(np.percentile(e2e_s, 99) * 1e6)},
+                           "device_max": float(np.max(dev_us)),
+                           "e2e_result_median": float(np.median(e2e_res_s) * 1e6), "e2e_result_p99": float(np.percentile(e2e_res_s, 99) * 1e6),
+                           "e2e_idle_median": float(np.median(e2e_s) * 1e6), "e2e_idle_p99": float(np.percentile(e2e_s, 99) * 1e6)},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "span": "call start -> result in host memory -> handle's stream idle (the tail a step leaves behind its result is inside)",
                     "api": ("mppi_step_batched (host x0s/Us in, Us_out/costs/feasible out, synchronous)" if batched else
                             "ShiftInitialCondition + defineMPPINominalControl + MPPIPlan (host buffers, synchronous)")},
             "gpu_launches": int(launches),
             "kernels_us": {"rollout_cost": float(k_us[0]), "softmin_update": float(k_us[1]), "finalize_nominal": float(k_us[2]),
                            "step_eager": float(k_us[3]),
-                           "source": "CUDA events around eager launches on the library stream, L2 flushed, median of 10"},
+                           "source": "CUDA events around eager launches on the library stream, L2 flushed on the same stream, median of 12"
+                                     + ("; rollout_cost = the fused scan kernel (softmin + update inside), finalize_nominal = its tail launched separately" if fused else "")},
             "kernels_us_in_graph": None if g_us is None else {
                 "rollout_cost": float(g_us[0]), "softmin_update": float(g_us[1]), "finalize_nominal": float(g_us[2]),
                 "rollout_start_to_finalize_end": float(g_us[3]),
                 "noise_next_iteration": float(g_us[4]), "rollout_start_to_last_kernel_end": float(g_us[5]),
                 "source": "%globaltimer spans written by the kernels themselves inside the replayed graph (mppi_set_profiling(2))"},
-            "roofline": {"kernel": "rollout_kernel", "bound": "fp32", "achieved": roll_tflops, "peak": fp32_peak,
+            "roofline": {"kernel": "scan_rollout_kernel (rollout + cost + softmin + weighted update)" if fused else "rollout_kernel",
+                         "bound": "fp32", "achieved": roll_tflops, "peak": fp32_peak,
                          "unit": "TFLOP/s", "frac": roll_tflops / fp32_peak if fp32_peak else None,
-                         "traffic": NCU_TRAFFIC.get(a.config, (None, None))[0] if world == 1 else None,
-                         "traffic_source": "profiles/r01_ncu_*.md (ncu --set full, per launch)",
-                         "flop_per_sample_step": F,
-                         "frac_in_graph": None if g_us is None or not fp32_peak else local_units * F / (g_us[0] * 1e-6) / 1e12 / fp32_peak,
-                         "peak_source": "FFMA-chain probe measured in this run (mppi_measure_fp32_peak)"},
-            "roofline_update": {"kernel": "update_kernel", "bound": "hbm", "achieved": upd_gbs, "peak": peaks.get("hbm_gbs"),
-                                "unit": "GB/s", "frac": upd_gbs / peaks["hbm_gbs"],
-                                "traffic": NCU_TRAFFIC.get(a.config, (None, None))[1] if world == 1 else None,
-                                "bytes_per_launch": upd_bytes, "peak_source": f"MEASURED_PEAKS.json ({peak_src})",
-                                "frac_in_graph": None if g_us is None else upd_bytes / (g_us[1] * 1e-6) / 1e9 / peaks["hbm_gbs"],
-                                "note": "eps was read (or produced) by the rollout kernel earlier in the same step; when it fits the "
-                                        "126 MB L2 the stream is served from L2 and can exceed the HBM peak"},
+                         "traffic": traffic[0], "traffic_source": "profiles/r02_ncu_*.md (ncu --set full, per launch)",
+                         "flop_per_sample_step": F, "algorithmic_flop_per_launch": local_units * F,
+                         "frac_in_graph": None if g_us is None or not fp32_peak or g_us[0] <= 0 else local_units * F / (g_us[0] * 1e-6) / 1e12 / fp32_peak,
+                         "peak_source": "FFMA-chain probe measured in this run (mppi_measure_fp32_peak)",
+                         "hbm_view": {"algorithmic_bytes": eps_bytes + kl * B * 5, "gbs": (eps_bytes + kl * B * 5) / (k_us[0] * 1e-6) / 1e9,
+                                      "frac_of_measured_peak": (eps_bytes + kl * B * 5) / (k_us[0] * 1e-6) / 1e9 / peaks["hbm_gbs"]}
+                         if (fused or info["pregen"]) else None},
             "clocks": clocks.summary(),
         }
+        if fused:
+            line["roofline_update"] = {"kernel": None, "fused": True,
+                                       "note": "no separate update kernel at this size: the weighted control sum is accumulated by the scan kernel from "
+                                               "the eps values it already holds in registers, so eps is read ONCE per step (update_kernel's second pass, "
+                                               f"{upd_bytes} B here, is gone); update_kernel's HBM roofline is reported on the configurations that run it "
+                                               "(profiles/r02_bench_cfg3.json, cfg4, cfg5)"}
+        else:
+            upd_gbs = upd_bytes / (k_us[1] * 1e-6) / 1e9
+            in_l2 = eps_bytes <= 100e6
+            line["roofline_update"] = {"kernel": "update_kernel", "bound": "hbm", "achieved": upd_gbs, "peak": peaks.get("hbm_gbs"),
+                                       "unit": "GB/s", "frac": upd_gbs / peaks["hbm_gbs"], "frac_of_nominal_8TBs": upd_gbs / 8000.0,
+                                       "traffic": traffic[1], "bytes_per_launch": upd_bytes, "peak_source": f"MEASURED_PEAKS.json ({peak_src})",
+                                       ("l2_frac_in_graph" if in_l2 else "frac_in_graph"):
+                                           None if g_us is None or g_us[1] <= 0 else upd_bytes / (g_us[1] * 1e-6) / 1e9 / peaks["hbm_gbs"],
+                                       "note": ("in the graph eps (smaller than the 126 MB L2) was just touched by the rollout: that figure is an L2 rate, not HBM evidence"
+                                                if in_l2 else "eps exceeds the L2: the in-graph figure is an HBM rate")}
+        if parity_n is not None:
+            line["parity_n"] = parity_n
         if not a.no_cpu_baseline:
             cb, _, _ = cpu_baseline(a.config if a.config != 4 else 0)
             line["cpu_baseline"] = cb
+            line["guard_band_samples"] = {"count": cb["guard_band_samples"], "of": cb["guard_band_of"], "band": 1e-4}
     return line
 
 

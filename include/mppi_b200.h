@@ -28,7 +28,8 @@
 extern "C" {
 #endif
 
-#define MPPI_B200_VERSION 100 /* 0.1.0 */
+#define MPPI_B200_VERSION 200 /* 0.2.0 */
+#define MPPI_MAX_GPUS 8
 #define MPPI_MAX_NX 8
 #define MPPI_MAX_CIRCLES 64
 #define MPPI_MAX_BLOCKS 32
@@ -97,6 +98,21 @@ typedef struct mppi_config {
                               * rollout.  0-2 pre-generate the next iteration's noise beside finalize whenever the
                               * step is a single-instance Philox MPPI step.
                               * Environment MPPI_ROLLOUT_VARIANT overrides; MPPI_PREGEN=0 disables pre-generation. */
+  int32_t strict_math;       /* FP32 only.  1: the K-sample rollout runs the reference's operation sequence in IEEE
+                              * round-to-nearest arithmetic without fused multiply-add and with the elementary
+                              * functions of include/mppi_strict_math.h, so that per-sample costs, flags and the
+                              * argmin are BIT-IDENTICAL to a float restatement of the reference using the same
+                              * functions (tests/test_gpu_strict.py).  Verification flavour: ~10x slower. */
+  int32_t noise_policy;      /* Philox steps, B == 1.  0 auto | 1 "latency": the NEXT iteration's noise tensor is drawn
+                              * by noise_kernel beside finalize and the rollout reads it back (the result arrives
+                              * earlier; +1 HBM pass over eps) | 2 "throughput": noise drawn inside the rollout
+                              * (no extra pass).  auto = latency up to 131,072 samples per GPU, throughput beyond. */
+  int32_t n_gpus;            /* 0 / 1: this handle drives cfg.device only.  2..8: ONE handle, ONE host thread, samples
+                              * sharded over device_ids[0..n_gpus) (the reference's caller is a single Julia task,
+                              * main.jl:55-83); results are read from device_ids[0].  Needs peer access between the
+                              * devices (NVLink / NVSwitch). */
+  int32_t device_ids[MPPI_MAX_GPUS];
+  int32_t reserved0;
   uint64_t seed;             /* Philox key */
   double T;                  /* horizon seconds; dt = T/N (setup.jl:53) */
   double lambda;             /* types.jl:28 */
@@ -274,6 +290,12 @@ int32_t mppi_get_phase_clocks(mppi_handle_t* h, uint64_t clocks[16]);
  * CTA's end into the phase-clock block: clocks[8+2i], clocks[9+2i] for i = rollout, update,
  * finalize.  Re-arm with mppi_set_profiling(h, 2) before each traced step. */
 int32_t mppi_set_profiling(mppi_handle_t* h, int32_t on);
+/* which kernels the next single-instance step of this handle runs (diagnostics, tests, bench):
+ * [0] 1 = scan-form fused step (rollout + softmin + update + tail in one kernel), 0 = rollout / update / finalize kernels
+ * [1] 1 = the next iteration's Philox noise is pre-generated behind the step ("latency" policy)
+ * [2] 1 = packed FP32x2 sequential rollout   [3] CTAs of the scan kernel   [4] update ksplit   [5] update jsplit
+ * [6] strict_math   [7] GPUs driven by this handle */
+int32_t mppi_get_plan_info(mppi_handle_t* h, int32_t info[8]);
 /* number of kernels the library launched on this handle so far */
 int64_t mppi_launch_count(const mppi_handle_t* h);
 

@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libmppi_b200.so")
 
 MPPI_MAX_NX = 8
 MPPI_MAX_N = 256
+MPPI_MAX_GPUS = 8
 MPPI_COMM_ID_BYTES = 128
 MPPI_PEER_HANDLE_BYTES = 64
 
@@ -35,6 +36,7 @@ class Config(C.Structure):
         ("precision", _i), ("noise_mode", _i), ("planner", _i),
         ("feasibility_count", _i), ("use_cuda_graph", _i), ("device", _i),
         ("k_offset", _i), ("K_local", _i), ("rollout_variant", _i),
+        ("strict_math", _i), ("noise_policy", _i), ("n_gpus", _i), ("device_ids", _i * MPPI_MAX_GPUS), ("reserved0", _i),
         ("seed", C.c_uint64),
         ("T", _d), ("lambda_", _d),
         ("Sigma", _d * 4),
@@ -122,6 +124,7 @@ SIGNATURES = {
     "mppi_get_stream": (_i, [_H, _P(C.c_void_p)]),
     "mppi_get_phase_clocks": (_i, [_H, _P(C.c_uint64)]),
     "mppi_set_profiling": (_i, [_H, _i]),
+    "mppi_get_plan_info": (_i, [_H, _P(_i)]),
     "mppi_launch_count": (C.c_int64, [_H]),
     "mppi_check_poses": (_i, [_H, _P(_d), _i, _P(_i)]),
     "mppi_measure_fp32_peak": (_i, [_H, _P(_d)]),

@@ -63,6 +63,15 @@ const char* mppi_last_error(const mppi_handle_t* h) { return h ? h->err.c_str() 
 
 int64_t mppi_launch_count(const mppi_handle_t* h) { return h ? h->launches : 0; }
 
+// MvNormal(zeros(m), Sigma) (setup.jl:57,77) throws unless Sigma is symmetric positive definite; the Cholesky factor
+// build_params takes must exist: s00 > 0, s11 - s10^2 / s00 > 0, s01 == s10.
+static bool sigma_ok(const double* S) {
+  const double s00 = S[0], s10 = S[1], s01 = S[2], s11 = S[3];
+  if (!(s00 > 0) || !(s11 > 0)) return false;
+  if (!(std::fabs(s10 - s01) <= 1e-12 * std::max(1.0, std::max(std::fabs(s10), std::fabs(s01))))) return false;
+  return s11 - s10 * s10 / s00 > 0;
+}
+
 static int validate(const mppi_config_t* c, std::string* why) {
   char buf[256];
   // same checks, same wording as setup.jl:19-39 where they apply to a fixed-size POD
@@ -81,11 +90,14 @@ static int validate(const mppi_config_t* c, std::string* why) {
   if (c->precision != MPPI_FP32 && c->precision != MPPI_FP64) { *why = "unknown precision"; return MPPI_EINVAL; }
   if (c->noise_mode != MPPI_NOISE_SUPPLIED && c->noise_mode != MPPI_NOISE_PHILOX) { *why = "unknown noise_mode"; return MPPI_EINVAL; }
   if (c->planner != MPPI_PLANNER_MPPI && c->planner != MPPI_PLANNER_DWA) { *why = "unknown planner"; return MPPI_EINVAL; }
-  if (c->rollout_variant < 0 || c->rollout_variant > 4) { *why = "rollout_variant must be 0..4"; return MPPI_EINVAL; }
+  if (c->rollout_variant < 0 || c->rollout_variant > 5) { *why = "rollout_variant must be 0..5"; return MPPI_EINVAL; }
+  if (c->noise_policy < 0 || c->noise_policy > 2) { *why = "noise_policy must be 0 (auto), 1 (latency) or 2 (throughput)"; return MPPI_EINVAL; }
+  if (c->strict_math != 0 && c->strict_math != 1) { *why = "strict_math must be 0 or 1"; return MPPI_EINVAL; }
+  if (c->strict_math && (c->precision != MPPI_FP32 || c->planner != MPPI_PLANNER_MPPI || c->B != 1)) { *why = "strict_math is the FP32 verification flavour of a single-instance MPPI step"; return MPPI_EINVAL; }
+  if (c->n_gpus < 0 || c->n_gpus > MPPI_MAX_GPUS) { *why = "n_gpus must be in 0..8"; return MPPI_EINVAL; }
   const int Kl = c->K_local > 0 ? c->K_local : c->K;
   if (c->k_offset < 0 || c->k_offset + Kl > c->K) { *why = "sample shard [k_offset, k_offset+K_local) must lie inside [0, K)"; return MPPI_EINVAL; }
-  const double det = c->Sigma[0] * c->Sigma[3] - c->Sigma[1] * c->Sigma[2];
-  if (!(c->Sigma[0] > 0) || !(det > 0)) { *why = "Sigma must be positive definite"; return MPPI_EINVAL; }
+  if (!sigma_ok(c->Sigma)) { *why = "Sigma must be symmetric positive definite"; return MPPI_EINVAL; }
   for (int i = 0; i < c->n_x; ++i)
     if (c->XL[i] > c->XU[i]) { snprintf(buf, sizeof buf, "XL[%d] (%g) must be <= XU[%d] (%g)", i, c->XL[i], i, c->XU[i]); *why = buf; return MPPI_EINVAL; }
   if (c->planner == MPPI_PLANNER_DWA && (Kl != c->K || c->B != 1)) { *why = "DWA planner runs unsharded, B = 1"; return MPPI_EINVAL; }
@@ -103,7 +115,8 @@ int32_t mppi_destroy(mppi_handle_t* h) {
   if (h->d_window) cudaFree(h->d_window);
   if (h->d_peers) cudaFree(h->d_peers);
   void* dev[] = {h->d_in, h->d_eps, h->d_costs, h->d_flags, h->d_scratch, h->d_scratch_tmpl, h->d_iter, h->d_Spart,
-                 h->d_eta_part, h->d_partial, h->d_gathered, h->d_res, h->d_cand, h->d_dbg, h->d_seq, h->d_his, h->d_iterlog, h->d_pstate, h->d_ref};
+                 h->d_eta_part, h->d_partial, h->d_gathered, h->d_res, h->d_cand, h->d_dbg, h->d_seq, h->d_his, h->d_iterlog, h->d_pstate, h->d_ref,
+                 h->d_cta_part, h->d_ticket};
   for (void* p : dev) if (p) cudaFree(p);
   void* host[] = {h->h_in, h->h_res, h->h_partial, h->h_gathered, h->h_seq, h->h_ll, h->h_pdone};
   for (void* p : host) if (p) cudaFreeHost(p);
@@ -146,13 +159,24 @@ static int create_impl(mppi_handle* h) {
     if (const char* e = getenv("MPPI_PDL")) h->pdl = atoi(e) != 0;
     const bool can_pack = c.precision == MPPI_FP32 && (h->K_local % 2) == 0;
     // pre-generated noise (variants 0-2): single-instance Philox MPPI steps; 3 / 4 keep Philox inside the rollout
-    h->pregen_ok = c.planner == MPPI_PLANNER_MPPI && c.noise_mode == MPPI_NOISE_PHILOX && c.B == 1 && variant != 3 && variant != 4;
+    // noise_policy: latency = pre-generate (one more HBM pass over eps, the result arrives earlier), throughput = Philox inside
+    // the rollout.  auto: latency up to 131,072 samples per GPU (the eps tensor stays L2-sized and the step is latency-bound).
+    const long long samples_ = (long long)h->K_local * c.B;
+    const bool want_pregen = c.noise_policy == 1 || (c.noise_policy == 0 && (samples_ <= 131072 || c.model == MPPI_MODEL_DYNAMIC7));
+    h->pregen_ok = c.planner == MPPI_PLANNER_MPPI && c.noise_mode == MPPI_NOISE_PHILOX && c.B == 1 && variant != 3 && variant != 4 &&
+                   (want_pregen || variant == 5) && !c.strict_math;
     if (const char* e = getenv("MPPI_PREGEN")) h->pregen_ok = h->pregen_ok && atoi(e) != 0;
+    // scan-form fused step (mppi_scan.cuh): FP32 kinematic MPPI, one instance, no cut-off; obstacle kind / reference path are
+    // checked per step (scan_eligible).  auto: below 262,144 samples per GPU, where the sequential rollout is latency-bound.
+    h->scan_ok = c.precision == MPPI_FP32 && c.model == MPPI_MODEL_KINEMATIC5 && c.planner == MPPI_PLANNER_MPPI && c.B == 1 &&
+                 !h->cutoff && !c.strict_math && scan_chunk(c.N) != 0 && (variant == 5 || (variant == 0 && samples_ < 262144));
+    if (const char* e = getenv("MPPI_SCAN")) h->scan_ok = h->scan_ok && atoi(e) != 0;
+    if (variant == 5 && !h->scan_ok) { h->err = "rollout_variant 5 (scan-form fused step) needs FP32, the kinematic model, the MPPI planner, B = 1, no cut-off, N <= 104"; return MPPI_EINVAL; }
     // auto: packing halves the warps, so it needs enough samples to keep every SM sub-partition busy; with the
     // per-lane Philox / Box-Muller work out of the loop it pays from 65,536 samples (tools/sweep_pregen.py)
     const long long samples = (long long)h->K_local * c.B;
     const long long pack_min = h->pregen_ok ? MPPI_PACK_MIN_SAMPLES_PREGEN : MPPI_PACK_MIN_SAMPLES;
-    h->packed = can_pack && (variant == 2 || variant == 4 || (variant == 0 && samples >= pack_min));
+    h->packed = !c.strict_math && can_pack && (variant == 2 || variant == 4 || (variant == 0 && samples >= pack_min));
   }
   MPPI_CUDA(h, cudaMalloc(&h->d_in, B * (MPPI_MAX_NX + 2 * N) * sizeof(double)));
   if (c.planner == MPPI_PLANNER_MPPI) MPPI_CUDA(h, cudaMalloc(&h->d_eps, B * N * K * 2 * rs));
@@ -169,6 +193,15 @@ static int create_impl(mppi_handle* h) {
   MPPI_CUDA(h, cudaMalloc(&h->d_res, B * (RES_SCALARS + 2 * N + (N + 1) * c.n_x) * sizeof(double)));
   h->d_traj = h->d_res + B * (RES_SCALARS + 2 * N);
   if (c.planner == MPPI_PLANNER_DWA) MPPI_CUDA(h, cudaMalloc(&h->d_cand, K * 2 * sizeof(double)));
+  if (h->scan_ok) {
+    const int tiles = (h->K_local + SCAN_SPW - 1) / SCAN_SPW;
+    const int want = h->sm_count * 3;   // __launch_bounds__(SCAN_BS, 3): one resident wave
+    h->scan_ctas = std::max(1, std::min(std::min(want, FOLD_MAX_CTAS), (tiles + SCAN_NW - 1) / SCAN_NW));
+    if (const char* e = getenv("MPPI_SCAN_CTAS")) { const int v = atoi(e); if (v >= 1 && v <= FOLD_MAX_CTAS) h->scan_ctas = v; }
+    MPPI_CUDA(h, cudaMalloc(&h->d_cta_part, size_t(2 * N + 2) * FOLD_MAX_CTAS * sizeof(float)));
+    MPPI_CUDA(h, cudaMalloc(&h->d_ticket, sizeof(unsigned int)));
+    MPPI_CUDA(h, cudaMemset(h->d_ticket, 0, sizeof(unsigned int)));
+  }
   MPPI_CUDA(h, cudaMalloc(&h->d_dbg, 16 * sizeof(unsigned long long)));
   MPPI_CUDA(h, cudaMemset(h->d_dbg, 0, 16 * sizeof(unsigned long long)));
   // inputs and results are MAPPED pinned memory: for B == 1 the step's kernels read / write them
@@ -256,8 +289,7 @@ int32_t mppi_set_nominal(mppi_handle_t* h, const double* U, int32_t N, int32_t m
 int32_t mppi_set_sigma_lambda(mppi_handle_t* h, const double* Sigma, double lambda) {
   H_CHECK(h);
   if (!Sigma) return fail(h, MPPI_EINVAL, "null Sigma");
-  const double det = Sigma[0] * Sigma[3] - Sigma[1] * Sigma[2];
-  if (!(Sigma[0] > 0) || !(det > 0) || !(lambda > 0)) return fail(h, MPPI_EINVAL, "Sigma must be positive definite and lambda > 0");
+  if (!sigma_ok(Sigma) || !(lambda > 0)) return fail(h, MPPI_EINVAL, "Sigma must be symmetric positive definite and lambda > 0");
   int rc = quiesce(h); if (rc) return rc;
   for (int i = 0; i < 4; ++i) h->cfg.Sigma[i] = Sigma[i];
   h->cfg.lambda = lambda;
@@ -301,6 +333,7 @@ int32_t mppi_set_reference_path(mppi_handle_t* h, const double* xy, int32_t n, d
   H_CHECK(h);
   if (n < 0 || n > MPPI_MAX_REF) { char b[96]; snprintf(b, sizeof b, "reference path: n (%d) must be in 0..%d", n, MPPI_MAX_REF); return fail(h, MPPI_EINVAL, b); }
   if (n > 0 && (!xy || !(weight >= 0) || window < 1)) return fail(h, MPPI_EINVAL, "reference path: null points, negative weight or window < 1");
+  if (n > 0 && h->cfg.strict_math) return fail(h, MPPI_EINVAL, "the reference-path term is not part of the strict_math flavour");
   if (n > 0 && h->cfg.planner == MPPI_PLANNER_MPPI && h->cfg.noise_mode != MPPI_NOISE_PHILOX)
     return fail(h, MPPI_EINVAL, "a reference path needs PHILOX noise (the tracking rollout is not built for supplied noise)");
   int rc = quiesce(h); if (rc) return rc;

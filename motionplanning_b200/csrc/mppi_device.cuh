@@ -79,6 +79,7 @@ enum { RES_COST = 0, RES_FEASIBLE = 1, RES_ROLLOUTS = 2, RES_FEASCOUNT = 3, RES_
 // latency end to end.  Rank r stores its partial into slot [parity][r] of EVERY rank's window;
 // a rank polls its own window until every line carries this step's flag.  Two parities: a rank
 // can be at most one step ahead of the slowest.
+constexpr int FOLD_MAX_CTAS = 640;    // scan_rollout_kernel grid limit (per-CTA partials folded by one block)
 constexpr int PEER_MAX_RANKS = 8;
 constexpr int PEER_PLEN = 8 + 2 * MPPI_MAX_N;   // PART_HDR + 2 N at the largest horizon
 struct PeerWindow {
@@ -123,9 +124,15 @@ struct Buffers {
   int n_ranks;
   int rank;
   PeerWindow* const* peers;   // [n_ranks] exchange windows of all ranks (own + IPC-mapped peers), or nullptr
+  unsigned long long seq_base;   // *seq when the peer exchange was set up: exchange flags count steps from there
   const int* halt;      // closed loop: nonzero once the episode is over; the step's kernels then do nothing (nullptr otherwise)
   int trace;            // 1: kernels stamp %globaltimer at first-CTA start / last-CTA end into dbg[8..]
   int eps_stage;        // rollout reading eps (SRC_SUPPLIED): 1 = the block's eps slab is bulk-copied (TMA) into shared memory
+  // scan-form fused step (mppi_scan.cuh)
+  R* cta_part;          // [2N + 2][n_cta] per-CTA softmin partials: 2N weighted control sums ([j][c] interleaved), eta, rho_cta
+  int n_cta;            // CTAs of scan_rollout_kernel (columns of cta_part)
+  unsigned int* ticket; // arrival counter: the last CTA to finish runs the step's tail (fold, exchange, combine, nominal rollout)
+  int tail_in_kernel;   // 1: that tail runs inside scan_rollout_kernel's last CTA; 0: finalize_kernel<PH_FOLD|...> follows as its own launch
 };
 
 // ---------------------------------------------------------------------------

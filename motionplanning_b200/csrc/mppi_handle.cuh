@@ -13,7 +13,8 @@
 #include <string>
 #include <vector>
 
-#include "mppi_update.cuh"
+#include "mppi_scan.cuh"
+#include "mppi_strict.cuh"
 #include "mppi_plant.cuh"
 
 namespace mppi {
@@ -81,6 +82,11 @@ struct mppi_handle {
   // pre-generated noise (V_PREGEN): second capture branch for noise_kernel, and whether d_eps already holds
   // the noise of the iteration the device counter points at
   bool pregen_ok = false, noise_ready = false;
+  // scan-form fused step (mppi_scan.cuh): eligible configuration, grid size, per-CTA partial table, arrival counter
+  bool scan_ok = false;
+  int scan_ctas = 0;
+  float* d_cta_part = nullptr;
+  unsigned int* d_ticket = nullptr;
   int sm_count = 148;
   cudaStream_t stream2 = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
@@ -100,6 +106,7 @@ struct mppi_handle {
   // static params
   mppi::StaticParams<float> pf;
   mppi::StaticParams<double> pd;
+  mppi::StrictParams sp;   // strict_math flavour: the configuration rounded once to float, as the reference's functions see it
   // graphs, keyed by variant
   std::map<int, cudaGraphExec_t> graphs;
   // multi-GPU
@@ -109,6 +116,7 @@ struct mppi_handle {
   mppi::PeerWindow* peer_ptr[8] = {nullptr};     // all ranks' windows as seen from this device
   mppi::PeerWindow** d_peers = nullptr;          // device copy of peer_ptr
   bool p2p = false;                              // exchange in-kernel over peer memory instead of NCCL
+  unsigned long long seq_base = 0;               // device step counter at mppi_peer_init
   // profiling
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // step begin | rollout end | update end | finalize end | step end | inputs staged
   int profiling = 0;   // 0 off | 1 eager launches bracketed by events | 2 graph replay, kernels stamp %globaltimer
@@ -193,9 +201,29 @@ void build_params(const mppi_handle* h, StaticParams<R>* p) {
   }
 }
 
+inline void build_strict_params(const mppi_handle* h, StrictParams* p) {
+  const mppi_config_t& c = h->cfg;
+  memset(p, 0, sizeof(*p));
+  p->model = c.model; p->n_x = c.n_x; p->N = c.N; p->K_local = h->K_local; p->k_offset = c.k_offset;
+  p->n_circles = int(h->circles.size() / 3); p->n_blocks = int(h->blocks.size() / 5);
+  p->dt = float(c.T / c.N);   // setup.jl:53, rounded once
+  p->lambda = float(c.lambda);
+  for (int i = 0; i < 4; ++i) p->Sigma[i] = float(c.Sigma[i]);
+  for (int i = 0; i < 2; ++i) { p->goal[i] = float(c.goal[i]); p->CL[i] = float(c.CL[i]); p->CU[i] = float(c.CU[i]); }
+  for (int i = 0; i < MPPI_MAX_NX; ++i) { p->XL[i] = float(c.XL[i]); p->XU[i] = float(c.XU[i]); }
+  p->slack_penalty = float(c.slack_penalty); p->obstacle_penalty = float(c.obstacle_penalty); p->terminal_scale = float(c.terminal_scale);
+  p->la = float(c.la); p->lb = float(c.lb); p->mass = float(c.mass); p->Izz = float(c.Izz); p->g = float(c.g); p->mu = float(c.mu);
+  p->KFZF = float(c.KFZF); p->KFZR = float(c.KFZR); p->KFZX = float(c.KFZX);
+  for (int i = 0; i < 6; ++i) { p->tire[i] = float(c.tire[i]); p->w[i] = float(c.stage_w[i]); }
+  p->veh_L = float(c.veh_L); p->veh_W = float(c.veh_W); p->veh_off = float(c.veh_center_offset);
+  for (int o = 0; o < p->n_circles; ++o) for (int q = 0; q < 3; ++q) p->circles[o][q] = float(h->circles[3 * o + q]);
+  for (int b = 0; b < p->n_blocks; ++b) for (int q = 0; q < 5; ++q) p->blocks[b][q] = float(h->blocks[5 * b + q]);
+}
+
 inline void rebuild_params(mppi_handle* h) {
   build_params(h, &h->pf);
   build_params(h, &h->pd);
+  if (h->cfg.strict_math) build_strict_params(h, &h->sp);
 }
 
 inline void drop_graphs(mppi_handle* h) {
@@ -226,10 +254,15 @@ Buffers<R> make_buffers(const mppi_handle* h) {
   b.n_ranks = h->n_ranks;
   b.rank = h->rank;
   b.peers = h->p2p ? h->d_peers : nullptr;
+  b.seq_base = h->seq_base;
   b.trace = h->profiling == 2 ? 1 : 0;
   b.halt = nullptr;
   b.eps_stage = 0;
   b.ref = static_cast<const R*>(h->d_ref);
+  b.cta_part = (R*)h->d_cta_part;
+  b.n_cta = h->scan_ctas;
+  b.ticket = h->d_ticket;
+  b.tail_in_kernel = 0;
   return b;
 }
 

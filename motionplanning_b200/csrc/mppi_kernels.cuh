@@ -211,8 +211,8 @@ __global__ void __launch_bounds__(NOISE_BS) noise_kernel(const __grid_constant__
   const int k = blockIdx.x * NOISE_BS + threadIdx.x, b = blockIdx.z;
   const int K = p.K_local, N = p.N;
   trace_begin(buf.dbg, buf.trace, 3);
-  if (k >= K) return;
-  const uint32_t iter = *iter_ptr + uint32_t(delta);
+  if (k >= K) { pdl_wait(); return; }
+  const uint32_t iter = __ldcg(iter_ptr) + uint32_t(delta);   // L2: the producer may still be running (programmatic dependent launch)
   const R L00 = p.L00, L10 = p.L10, L11 = p.L11;
 #pragma unroll
   for (int q = 0; q < NOISE_PAIRS; ++q) {
@@ -228,6 +228,9 @@ __global__ void __launch_bounds__(NOISE_BS) noise_kernel(const __grid_constant__
     }
   }
   trace_end(buf.dbg, buf.trace, 3);
+  // Launched as a programmatic dependent of scan_rollout_kernel this grid runs beside that kernel's tail; it must not
+  // COMPLETE before it (the next step's kernels are ordered behind this grid only).  A no-op in a normal launch.
+  pdl_wait();
 }
 
 // Bulk copies (TMA) of the block's eps slab into shared memory: one copy per horizon row (the block's samples at step j,

@@ -29,7 +29,8 @@ enum {
   // bits 16..19 carry n_ranks (variant_key), bit 24 the tracing flag
   V_PREGEN = 1 << 20,   // rollout reads pre-generated Philox noise; noise_kernel for the NEXT iteration runs beside finalize
   V_NOISE_NOW = 1 << 21,   // ... and the buffer does not hold this iteration's noise yet: draw it ahead of the rollout
-  V_ENQ_MASK = 0xFFFF | V_PREGEN | V_NOISE_NOW
+  V_SCAN = 1 << 22,        // scan-form fused step (mppi_scan.cuh) instead of rollout + update + finalize
+  V_ENQ_MASK = 0xFFFF | V_PREGEN | V_NOISE_NOW | V_SCAN
 };
 
 template <class R> const StaticParams<R>& params_of(const mppi_handle* h);
@@ -62,6 +63,18 @@ inline bool first_on_device(unsigned long long& mask) {
   return true;
 }
 
+// noise_kernel behind the scan kernel on the SAME stream, as its programmatic dependent
+template <class R>
+cudaError_t launch_noise_dependent(dim3 grid, cudaStream_t s, bool dependent, const StaticParams<R>& p, const Buffers<R>& buf, const unsigned int* iter_ptr) {
+  cudaLaunchConfig_t lc = {};
+  lc.gridDim = grid; lc.blockDim = dim3(NOISE_BS); lc.dynamicSmemBytes = 0; lc.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  lc.attrs = at; lc.numAttrs = dependent ? 1 : 0;
+  return cudaLaunchKernelEx(&lc, noise_kernel<R>, p, buf, iter_ptr, 0);
+}
+
 // long horizons need more than the default 48 KB of dynamic shared memory: opt in once per instantiation
 template <class R, class Model, int SRC, int PHASES, int BS>
 cudaError_t launch_finalize_bs(int B, size_t smem, cudaStream_t s, bool dependent, const StaticParams<R>& p, const Buffers<R>& buf) {
@@ -80,6 +93,29 @@ template <class R, class Model, int SRC, int PHASES>
 cudaError_t launch_finalize(int B, size_t smem, cudaStream_t s, bool dependent, const StaticParams<R>& p, const Buffers<R>& buf) {
   if ((PHASES & PH_XCHG) == 0 && B >= FINAL_BATCH_MIN_B) return launch_finalize_bs<R, Model, SRC, PHASES, FINAL_BS_BATCH>(B, smem, s, dependent, p, buf);
   return launch_finalize_bs<R, Model, SRC, PHASES, FINAL_BS>(B, smem, s, dependent, p, buf);
+}
+
+// The scan-form fused step (mppi_scan.cuh): chunk length C covers the horizon with SCAN_L lanes per sample, NC = circles held
+// in the unrolled test.  `tail`: the last CTA runs fold / exchange / combine / nominal rollout inside the kernel.
+template <int C, int NC>
+cudaError_t launch_scan_cn(dim3 grid, size_t smem, cudaStream_t s, bool dependent, const StaticParams<float>& p, const Buffers<float>& buf) {
+  auto kernel = scan_rollout_kernel<C, NC, PH_FOLD | PH_XCHG | PH_COMBINE>;
+  static size_t allowed_dev[64];
+  int dev = 0; cudaGetDevice(&dev);
+  size_t& allowed = allowed_dev[dev & 63];
+  if (allowed == 0) allowed = 48 * 1024;
+  if (smem > allowed) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    if (e != cudaSuccess) return e;
+    allowed = smem;
+  }
+  return launch_step_kernel(kernel, grid, dim3(SCAN_BS), smem, s, dependent, p, buf);
+}
+inline int scan_chunk(int N) { return N <= 7 * SCAN_L ? 7 : (N <= 13 * SCAN_L ? 13 : 0); }
+inline cudaError_t launch_scan(int N, int n_circles, dim3 grid, size_t smem, cudaStream_t s, bool dependent, const StaticParams<float>& p, const Buffers<float>& buf) {
+  const int C = scan_chunk(N);
+  if (C == 7) return n_circles <= 3 ? launch_scan_cn<7, 3>(grid, smem, s, dependent, p, buf) : launch_scan_cn<7, 8>(grid, smem, s, dependent, p, buf);
+  return n_circles <= 3 ? launch_scan_cn<13, 3>(grid, smem, s, dependent, p, buf) : launch_scan_cn<13, 8>(grid, smem, s, dependent, p, buf);
 }
 
 template <class R, class Model, int SRC>
@@ -140,8 +176,42 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
     h->launches++;
   }
   if (timed == 1) MPPI_CUDA(h, cudaEventRecord(h->ev[5], s));   // the rollout's interval starts after the inputs are staged
-  if (v & V_LOCAL) {
+  // ---- scan-form fused step: rollout + cost + online softmin + weighted sum in ONE kernel whose last CTA also runs the tail ----
+  bool scan_done = false, scan_tail = false;
+  if constexpr (std::is_same<R, float>::value && std::is_same<Model, Kin5<float>>::value && SRC != SRC_DWA) {
+    if ((v & V_LOCAL) && (v & V_SCAN)) {
+      const int C = scan_chunk(N);
+      const size_t plen_ = PART_HDR + 2 * size_t(N);
+      const size_t smemF_ = (RES_SCALARS + 2 * size_t(N) + size_t(N + 1) * 5 + plen_ + size_t(h->n_ranks) * plen_) * sizeof(double) +
+                            (size_t(N) * 6 + size_t(N + 1) * (5 + 2 + 3 + 1)) * sizeof(float);
+      const size_t smemS = size_t(SCAN_L) * C * sizeof(float4) + size_t(SCAN_NW) * (2 * N + 2) * sizeof(float);
+      // the tail runs in-kernel for whole steps (fused / peer-exchange finalize); eager profiling and split-phase steps launch it separately
+      scan_tail = !timed && (v & (V_FUSED_FINAL | V_XFINAL)) != 0;
+      buf.tail_in_kernel = scan_tail ? 1 : 0;
+      buf.n_cta = h->scan_ctas;
+      if (v & V_FUSED_FINAL) { buf.n_ranks = 1; buf.peers = nullptr; }
+      MPPI_CUDA(h, launch_scan(N, p.n_circles, dim3(h->scan_ctas), std::max(smemS, smemF_), s, pdl_in, p, buf));
+      h->launches++;
+      if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[1], s));
+      if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[2], s));
+      scan_done = true;
+    }
+  }
+  if ((v & V_LOCAL) && !scan_done) {
     bool launched = pregen;
+    if constexpr (std::is_same<R, float>::value && SRC != SRC_DWA) {
+      if (h->cfg.strict_math) {   // verification flavour: the reference's operation sequence in unfused IEEE FP32 (mppi_strict.cuh); reads eps
+        if (SRC == SRC_PHILOX) {
+          noise_kernel<R><<<noise_grid, NOISE_BS, 0, s>>>(p, buf, h->d_iter, 0);
+          h->launches++;
+        }
+        const size_t smemS = (size_t(2) * N + size_t(10) * p.n_blocks) * sizeof(float);
+        const dim3 sg((K + strict::BS - 1) / strict::BS);
+        if (Model::NX == 7) strict::rollout_strict_kernel<MPPI_MODEL_DYNAMIC7><<<sg, strict::BS, smemS, s>>>(h->sp, buf);
+        else strict::rollout_strict_kernel<MPPI_MODEL_KINEMATIC5><<<sg, strict::BS, smemS, s>>>(h->sp, buf);
+        launched = true;
+      }
+    }
     if (pregen) {   // eps read back (the host keeps V_PREGEN off for tracking handles)
       bool done = false;
       if constexpr (std::is_same<R, float>::value) {
@@ -165,7 +235,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
       }
     }
     if constexpr (std::is_same<R, float>::value) {
-      if (h->packed && !pregen) {   // two samples per thread on the packed FP32 pipe (mppi_pack.cuh)
+      if (h->packed && !pregen && !launched) {   // two samples per thread on the packed FP32 pipe (mppi_pack.cuh)
         dim3 grid((K + 2 * ROLLOUT_BS - 1) / (2 * ROLLOUT_BS), B);
         if constexpr (SRC != SRC_SUPPLIED) {
           if (track) rollout_kernel<f32x2, typename Rebind<Model, f32x2>::type, SRC, true><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);
@@ -221,6 +291,22 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   const size_t smemF = (RES_SCALARS + 2 * size_t(N) + size_t(N + 1) * Model::NX + plen) * sizeof(double) +
                        (size_t(N) * 6 + size_t(N + 1) * (Model::NX + 2 + 3 + 1) + size_t(2) * p.n_ref) * sizeof(R);
   const size_t smemX = smemF + size_t(h->n_ranks) * plen * sizeof(double);
+  if (scan_done) {
+    if constexpr (std::is_same<R, float>::value && std::is_same<Model, Kin5<float>>::value && SRC != SRC_DWA) {
+      if (!scan_tail && (v & V_FUSED_FINAL)) {
+        MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_FOLD | PH_COMBINE>(B, smemF, s, false, p, buf)));
+        h->launches++;
+      }
+      if (!scan_tail && (v & V_XFINAL)) {
+        MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_FOLD | PH_XCHG | PH_COMBINE>(B, smemX, s, false, p, buf)));
+        h->launches++;
+      }
+      if (v & V_PARTIAL) {
+        MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_FOLD>(B, smemF, s, false, p, buf)));
+        h->launches++;
+      }
+    }
+  } else {
   if (v & V_FUSED_FINAL) {
     MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_PARTIAL | PH_COMBINE>(B, smemF, s, pdl_final, p, buf)));
     h->launches++;
@@ -232,6 +318,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   if (v & V_PARTIAL) {
     MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_PARTIAL>(B, smemF, s, pdl_final, p, buf)));
     h->launches++;
+  }
   }
   if (v & V_D2H_PARTIAL)
     MPPI_CUDA(h, cudaMemcpyAsync(h->h_partial, h->d_partial, size_t(B) * h->plen * sizeof(double), cudaMemcpyDeviceToHost, s));
@@ -248,7 +335,13 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
     h->launches++;
   }
   if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[3], s));
-  if (pregen) MPPI_CUDA(h, cudaStreamWaitEvent(s, h->ev_join, 0));   // join
+  if (pregen && scan_done) {
+    // next iteration's noise behind the scan kernel: with the tail in-kernel it is that kernel's programmatic dependent, so
+    // its blocks take the SMs as the scan CTAs drain and run beside the one-CTA tail
+    MPPI_CUDA(h, launch_noise_dependent<R>(noise_grid, s, scan_tail && h->pdl, p, buf, h->d_iter + 1));
+    h->launches++;
+  }
+  if (pregen && !scan_done) MPPI_CUDA(h, cudaStreamWaitEvent(s, h->ev_join, 0));   // join
   if (v & V_PLANT) {
     plant_kernel<typename Rebind<Model, double>::type><<<1, 32, 0, s>>>(h->pd, h->plant);
     h->launches++;
@@ -294,6 +387,11 @@ inline int kernels_in(const mppi_handle* h, int v) {
   int n = 0;
   const bool dwa = h->cfg.planner == MPPI_PLANNER_DWA;
   if ((v & (V_H2D_IN | V_H2D_X0 | V_H2D_U)) && h->cfg.B == 1) n++;
+  if ((v & V_LOCAL) && (v & V_SCAN)) {   // scan kernel (tail inside for whole steps) [+ partial-only finalize] [+ next noise]
+    n += 1 + ((v & V_PARTIAL) ? 1 : 0) + ((v & V_PREGEN) ? 1 + ((v & V_NOISE_NOW) ? 1 : 0) : 0) + ((v & V_COMBINE) ? 1 : 0) + ((v & V_PLANT) ? 1 : 0) + ((v & V_SHIFT) ? 1 : 0);
+    return n;
+  }
+  if ((v & V_LOCAL) && h->cfg.strict_math && h->cfg.noise_mode == MPPI_NOISE_PHILOX && !dwa) n++;   // strict flavour draws its noise ahead of the rollout
   if (v & V_LOCAL) n += 1 + ((h->cutoff && !dwa) ? 1 : 0) + (dwa ? 0 : 1);
   if ((v & V_LOCAL) && (v & V_PREGEN)) n += 1 + ((v & V_NOISE_NOW) ? 1 : 0);
   if (v & V_FUSED_FINAL) n++;
@@ -308,9 +406,14 @@ inline int kernels_in(const mppi_handle* h, int v) {
 // Pre-generated noise applies to single-instance Philox MPPI steps with one-sample rollout threads: the
 // latency-bound regime, where the rollout's issue slots are the step's critical path.  Large sample
 // counts (packed rollout) are throughput-bound: the same instructions cost the same wherever they run.
+inline bool scan_eligible(const mppi_handle* h) {   // the scan kernel reads eps from memory: host-supplied, or pre-generated
+  if (!h->scan_ok || !h->ref_path.empty() || !h->blocks.empty() || h->circles.size() / 3 > 8) return false;
+  return h->cfg.noise_mode == MPPI_NOISE_SUPPLIED || h->pregen_ok;
+}
 inline int noise_bits(const mppi_handle* h) {
-  if (!h->pregen_ok || !h->ref_path.empty()) return 0;
-  return V_PREGEN | (h->noise_ready ? 0 : V_NOISE_NOW);
+  int v = scan_eligible(h) ? V_SCAN : 0;
+  if (!h->pregen_ok || !h->ref_path.empty()) return v;
+  return v | V_PREGEN | (h->noise_ready ? 0 : V_NOISE_NOW);
 }
 
 // pending host-side input changes -> the H2D node(s) the next step must carry

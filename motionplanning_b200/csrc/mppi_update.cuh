@@ -246,7 +246,8 @@ struct NominalStates<Kin5<R>> {
 //               then the final nominal rollout (MPPIUtils.jl:192-198) on thread 0.
 // DWA (DWAUtils.jl:152-158): U_new = the arg-min candidate, replicated over the horizon.
 // ---------------------------------------------------------------------------
-enum { PH_PARTIAL = 1, PH_COMBINE = 2, PH_XCHG = 4 };
+enum { PH_PARTIAL = 1, PH_COMBINE = 2, PH_XCHG = 4,
+       PH_FOLD = 8 };   // PH_FOLD: this rank's partial comes from the per-CTA partials of scan_rollout_kernel (mppi_scan.cuh), not from update_kernel's
 // phase clocks, written out with the results; stamped by a lane of the LAST warp: an `if (t == 0)` ahead
 // of a warp-collective section gets threaded into that section's warp test and splits warp 0 (see NominalStates)
 #define MPPI_STAMP(i) do { if (t == BS - 32) s_clk[i] = clock64(); } while (0)
@@ -255,13 +256,15 @@ __device__ __forceinline__ Scratch fresh_scratch(int K_local) {
   fresh.rho_key = ~0ull; fresh.argmin = ~0u; fresh.feasible_count = 0; fresh.k_eff = K_local; fresh.pad = 0;
   return fresh;
 }
+// The block-level body: called by finalize_kernel (one block per instance) and by the LAST block of
+// scan_rollout_kernel to finish (mppi_scan.cuh), which saves the launch and the inter-kernel gap.
+// `wait_prev`: issue griddepcontrol.wait before the first read of the previous kernel's output.
 template <class R, class Model, int SRC, int PHASES, int BS>
-__global__ void __launch_bounds__(BS) finalize_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) {
+__device__ __forceinline__ void finalize_block(const StaticParams<R>& p, const Buffers<R>& buf, unsigned char* smem_raw, const int b, const bool wait_prev) {
   // Everything this block produces is staged in shared memory and leaves in one burst at the end:
   // a global store followed by a barrier, or a read-back of a value the block just stored, costs
   // an L2 round trip (~1,000 cycles, more across the die boundary), and the old form chained six.
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int b = blockIdx.x, N = p.N, t = threadIdx.x;
+  const int N = p.N, t = threadIdx.x;
   constexpr int NX = Model::NX, ROW = Model::NX + 2;   // state, sin(heading), cos(heading)
   const int plen = PART_HDR + 2 * N;
   const int n_res = RES_SCALARS + 2 * N + (N + 1) * NX;
@@ -270,6 +273,7 @@ __global__ void __launch_bounds__(BS) finalize_kernel(const __grid_constant__ St
   double* sTR = sRC + 2 * N;
   double* sOwn = sRS + n_res;                          // [plen] this rank's partial
   double* sGat = sOwn + plen;                          // [G][plen] all ranks' partials (PH_XCHG only)
+  const bool xchg = (PHASES & PH_XCHG) && buf.n_ranks > 1 && buf.peers != nullptr;   // compiled in, decided per launch
   R* sU = reinterpret_cast<R*>(sGat + ((PHASES & PH_XCHG) ? buf.n_ranks * plen : 0));   // [N][4]: U_nom0, U_nom1, g0, g1
   R* sNew = sU + 4 * N;                                // [N][2]: U_new
   __shared__ double s_scale[8];
@@ -300,11 +304,44 @@ __global__ void __launch_bounds__(BS) finalize_kernel(const __grid_constant__ St
       sU[4 * j + 3] = p.G10 * u0 + p.G11 * u1;
     }
   }
-  pdl_wait();   // the loads above do not depend on the update kernel; everything below does
+  if (wait_prev) pdl_wait();   // the loads above do not depend on the update kernel; everything below does
   const Scratch sc = buf.scratch[b];
   constexpr bool PART_TO_GLOBAL = !(PHASES & PH_COMBINE);   // only a partial-only launch has a consumer outside this block
   double* pdst = PART_TO_GLOBAL ? part : sOwn;
 
+  if (PHASES & PH_FOLD) {
+    // Per-CTA partials of scan_rollout_kernel, laid out [2N + 2][n_cta]: 2N weighted control sums, eta, rho_cta, each against
+    // the CTA's own minimum.  Fold them against the global minimum (already in the scratch key): a warp per column,
+    // lanes across CTAs, fixed order -> deterministic.
+    __shared__ double s_cscale[FOLD_MAX_CTAS];
+    const int n_cta = buf.n_cta;
+    const R* Cp = buf.cta_part;
+    const double rho = double(key_cost(sc.rho_key, R(0)));
+    for (int c = t; c < n_cta; c += BS) {
+      const double rc = double(Cp[size_t(2 * N + 1) * n_cta + c]);
+      s_cscale[c] = (rc < 1e300 && rc == rc) ? exp(-(rc - rho) / double(p.lambda)) : 0.0;   // a CTA that saw no sample carries rho = +inf
+    }
+    __syncthreads();
+    const int lane = t & 31, wid = t >> 5;
+    constexpr int NW = BS / 32;
+    for (int col = wid; col <= 2 * N; col += NW) {
+      const R* src = Cp + size_t(col) * n_cta;
+      double s0 = 0.0;
+      for (int c = lane; c < n_cta; c += 32) s0 += double(src[c]) * s_cscale[c];
+      s0 = warp_sum(s0);
+      if (lane == 0) {
+        if (col < 2 * N) pdst[PART_HDR + ((col & 1) * N + (col >> 1))] = s0;   // CTA partials are [j][c] interleaved; the partial is col-major N x m
+        else pdst[PART_ETA] = s0;
+      }
+    }
+    if (t == 0) {
+      pdst[PART_RHO] = rho;
+      pdst[PART_ARGMIN] = double((unsigned int)(sc.rho_key & 0xFFFFFFFFull)) + double(p.k_offset);
+      pdst[PART_ROLLOUTS] = double(sc.k_eff);
+      pdst[PART_FEASIBLE] = double(sc.feasible_count);
+    }
+    __syncthreads();
+  }
   if (PHASES & PH_PARTIAL) {
     if (SRC == SRC_DWA) {
       // arg-min candidate (DWAUtils.jl:152).  FP32 keys carry the index; FP64 keys do not:
@@ -380,13 +417,15 @@ __global__ void __launch_bounds__(BS) finalize_kernel(const __grid_constant__ St
 
   const int G = buf.n_ranks;
   // gathered partials [G][B][plen]: an earlier kernel's output (COMBINE-only launch), or shared memory
-  const double* gat = (PHASES & PH_PARTIAL) ? sOwn - size_t(b) * plen : buf.gathered;
+  const double* gat = (PHASES & (PH_PARTIAL | PH_FOLD)) ? sOwn - size_t(b) * plen : buf.gathered;
   size_t gstride = size_t(p.B) * plen;
   bool xchg_timeout = false;
-  if (PHASES & PH_XCHG) {
+  if (xchg) {
     // In-kernel all-gather over NVLink peer memory (B == 1), LL protocol (see PeerWindow).
     const int me = buf.rank;
-    const unsigned long long step = seq_all + 1ull;   // ranks step in lockstep, so this agrees everywhere
+    // exchange steps are counted from mppi_peer_init (seq_base), so ranks whose handles ran different numbers of
+    // steps before the exchange was set up still agree on the flag; from then on they step in lockstep
+    const unsigned long long step = seq_all - buf.seq_base + 1ull;
     const int par = int(step & 1ull);
     const uint32_t flag = uint32_t(step);
     for (int i = t; i < plen; i += BS) {
@@ -536,7 +575,7 @@ __global__ void __launch_bounds__(BS) finalize_kernel(const __grid_constant__ St
     else tr[i - RES_SCALARS - 2 * N] = v;
   }
   if (t == 0) {
-    if (PHASES & PH_PARTIAL) buf.scratch[b] = fresh_scratch(p.K_local);   // last consumer of the scratch: re-arm it for the next step
+    if (PHASES & (PH_PARTIAL | PH_FOLD)) buf.scratch[b] = fresh_scratch(p.K_local);   // last consumer of the scratch: re-arm it for the next step
     if (b == 0) {
       *buf.iter = iter0 + 1u;   // next step draws fresh Philox noise
       *buf.seq = seq0 + 1ull;
@@ -548,6 +587,12 @@ __global__ void __launch_bounds__(BS) finalize_kernel(const __grid_constant__ St
     for (int i = 0; i < 7; ++i) buf.dbg[i] = s_clk[i];
   }
   trace_end(buf.dbg, buf.trace, 2);
+}
+
+template <class R, class Model, int SRC, int PHASES, int BS>
+__global__ void __launch_bounds__(BS) finalize_kernel(const __grid_constant__ StaticParams<R> p, const Buffers<R> buf) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  finalize_block<R, Model, SRC, PHASES, BS>(p, buf, smem_raw, blockIdx.x, true);
 }
 
 }  // namespace mppi

@@ -180,6 +180,12 @@ class MPPISearcher:  # types.jl:46-50
         self._check(self._lib.mppi_get_phase_clocks(self._h, ck))
         return list(ck)
 
+    def plan_info(self):
+        """Which kernels the next step runs: dict(scan, pregen, packed, scan_ctas, ksplit, jsplit, strict, n_gpus)."""
+        a = (C.c_int32 * 8)()
+        self._check(self._lib.mppi_get_plan_info(self._h, a))
+        return dict(zip(("scan", "pregen", "packed", "scan_ctas", "ksplit", "jsplit", "strict", "n_gpus"), list(a)))
+
     def launch_count(self):
         return int(self._lib.mppi_launch_count(self._h))
 
@@ -324,7 +330,8 @@ def _fill(arr, vals):
 def defineMPPI(numStates=0, numControls=0, lambda_=0.25, X0=None, goal=None, SamplingNumber=500, Sigma=None,
                N=15, T=3.0, XL=None, XU=None, CL=None, CU=None, *, model=None, precision=capi.FP32,
                noise_mode=capi.NOISE_PHILOX, seed=0x5EED0001, device=0, FeasibilityCount=1300,
-               use_cuda_graph=True, k_offset=0, K_local=0, B=1, planner=capi.PLANNER_MPPI, **overrides):
+               use_cuda_graph=True, k_offset=0, K_local=0, B=1, planner=capi.PLANNER_MPPI, strict_math=0,
+               noise_policy=0, rollout_variant=0, n_gpus=0, device_ids=None, **overrides):
     """defineMPPI (setup.jl:3-59).  Positional arguments as in the reference; keyword-only
     arguments select what the reference fixes by `include` or does not have (model,
     precision, noise source, device, sample shard)."""
@@ -362,6 +369,10 @@ def defineMPPI(numStates=0, numControls=0, lambda_=0.25, X0=None, goal=None, Sam
     cfg.use_cuda_graph = 1 if use_cuda_graph else 0
     cfg.device, cfg.k_offset, cfg.K_local = device, k_offset, K_local
     cfg.seed = seed
+    cfg.strict_math, cfg.noise_policy, cfg.rollout_variant = int(strict_math), int(noise_policy), int(rollout_variant)
+    cfg.n_gpus = int(n_gpus)
+    for i, d in enumerate(device_ids if device_ids is not None else range(max(int(n_gpus), 0))):
+        cfg.device_ids[i] = int(d)
     cfg.T, cfg.lambda_ = float(T), float(lambda_)
     _fill(cfg.Sigma, np.asarray(Sigma, dtype=np.float64).reshape(-1, order="F"))
     x0_first = X0 if X0.ndim == 1 else X0[:, 0]

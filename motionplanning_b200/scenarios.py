@@ -1,13 +1,14 @@
 """The five BASELINE.json configurations as synthetic scenes.
 
 Pure host-side data: positional arguments for defineMPPI plus obstacle lists.
-Used by tests/ and bench.py so both run the same workloads.
+Used by tests/ and bench.py so both run the same workloads.  Deliberately import-free (no
+`_capi`, so no product library): bench.py's reference arm loads this file by path.
 """
 import math
 
 import numpy as np
 
-from . import _capi as capi
+MODEL_DYNAMIC7, MODEL_KINEMATIC5 = 0, 1   # include/mppi_b200.h
 
 SEED = 0x5EED0001
 CIRCLES = [[50.0, 1, 2.5], [70.0, -1, 2.5], [90.0, 1, 2.5]]  # MPPI/main.jl:30
@@ -52,7 +53,7 @@ def config(idx, K=None, N=None, **kw):
         n = 50
         K, N = K or k, N or n
         args = (5, 2, LAMBDA, X0_KIN, GOAL, K, SIGMA, N, 0.1 * N, XL_KIN, XU_KIN, CL, CU)
-        kwargs = dict(model=capi.MODEL_KINEMATIC5, FeasibilityCount=K, seed=SEED)
+        kwargs = dict(model=MODEL_KINEMATIC5, FeasibilityCount=K, seed=SEED)
         if idx == 4:
             kwargs["B"] = 4096
         kwargs.update(kw)
@@ -63,7 +64,7 @@ def config(idx, K=None, N=None, **kw):
         xl = [-5, 0, -PI, -2, -PI / 6]  # :29, :22
         xu = [10, 10, PI, 2, PI / 6]
         args = (5, 2, LAMBDA, x0, [0.0, 0.5], K, SIGMA, N, 0.1 * N, xl, xu, CL, CU)
-        kwargs = dict(model=capi.MODEL_KINEMATIC5, FeasibilityCount=K, seed=SEED, veh_L=3.0, veh_W=2.0,
+        kwargs = dict(model=MODEL_KINEMATIC5, FeasibilityCount=K, seed=SEED, veh_L=3.0, veh_W=2.0,
                       veh_center_offset=1.5)
         kwargs.update(kw)
         return args, kwargs, [], PARKING_BLOCKS
@@ -71,7 +72,7 @@ def config(idx, K=None, N=None, **kw):
         K, N = K or 1048576, N or 100
         M_p = kw.pop("M_p", 3)
         args = (7, 2, LAMBDA, X0_DYN, GOAL, K, SIGMA, N, 0.05 * N, XL_DYN, XU_DYN, CL, CU)
-        kwargs = dict(model=capi.MODEL_DYNAMIC7, FeasibilityCount=K, seed=SEED)
+        kwargs = dict(model=MODEL_DYNAMIC7, FeasibilityCount=K, seed=SEED)
         kwargs.update(kw)
         return args, kwargs, [], wall_blocks(M_p)
     raise ValueError(idx)
@@ -86,7 +87,7 @@ def jittered_x0(B, seed=7):
 
 # algorithmic flop per sample-step, SURVEY.md 8(a) closed forms
 def flop_per_sample_step(model, n_circles, n_blocks):
-    if model == capi.MODEL_KINEMATIC5:
+    if model == MODEL_KINEMATIC5:
         base = 83 if n_blocks == 0 else 121
     else:
         base = 201 if n_blocks == 0 else 239

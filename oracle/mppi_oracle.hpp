@@ -41,8 +41,26 @@
 #include <vector>
 
 #include "../include/mppi_b200.h"
+#include "../include/mppi_strict_math.h"
 
 namespace oracle {
+
+// Elementary functions of the restatement.  Julia's sin/cos/tan/atan are libm-class (<= 1 ulp);
+// here: the C library's, in the precision of R.  For the strict FP32 flavour (north_star's
+// "bit-exact argmin and flags", checked in tests/test_gpu_strict.py) the float instantiation
+// switches to the portable functions of include/mppi_strict_math.h, which the GPU's strict
+// rollout executes operation for operation; double is never affected.
+inline bool& strict_f32() { static bool on = false; return on; }
+namespace om {
+inline double sin(double x) { return std::sin(x); }
+inline double cos(double x) { return std::cos(x); }
+inline double tan(double x) { return std::tan(x); }
+inline double atan(double x) { return std::atan(x); }
+inline float sin(float x) { return strict_f32() ? mppi_strict::sm_sin(x) : std::sin(x); }
+inline float cos(float x) { return strict_f32() ? mppi_strict::sm_cos(x) : std::cos(x); }
+inline float tan(float x) { return strict_f32() ? mppi_strict::sm_tan(x) : std::tan(x); }
+inline float atan(float x) { return strict_f32() ? mppi_strict::sm_atan(x) : std::atan(x); }
+}  // namespace om
 
 // Smallest relative distance of any threshold comparison (obstacle, bound) from
 // flipping; used by the tests' guard-band protocol, not part of the reference.
@@ -126,15 +144,15 @@ void vehicle_dynamics_dyn7(const Params<R>& p, const R* states, const R* ctrl, R
 
   const R FZF = R(2) * (KFZF * g - (ax - r * v) * KFZX);                 // :30
   const R FZR = R(2) * (KFZR * g + (ax - r * v) * KFZX);                 // :31
-  const R alpha_f = std::atan((v + la * r) / (ux + R(0.01))) - sa;       // :32
-  const R alpha_r = std::atan((v - lb * r) / (ux + R(0.01)));            // :33
+  const R alpha_f = om::atan((v + la * r) / (ux + R(0.01))) - sa;       // :32
+  const R alpha_r = om::atan((v - lb * r) / (ux + R(0.01)));            // :33
   const R X1_f = B * alpha_f;                                            // :35
-  const R FY1 = mu * FZF * p.tire[2] * std::sin(C * std::atan(X1_f - E * (X1_f - std::atan(X1_f))));  // :36
+  const R FY1 = mu * FZF * p.tire[2] * om::sin(C * om::atan(X1_f - E * (X1_f - om::atan(X1_f))));  // :36
   const R X1_r = B * alpha_r;                                            // :37
-  const R FY2 = mu * FZR * p.tire[2] * std::sin(C * std::atan(X1_r - E * (X1_r - std::atan(X1_r))));  // :38
+  const R FY2 = mu * FZR * p.tire[2] * om::sin(C * om::atan(X1_r - E * (X1_r - om::atan(X1_r))));  // :38
   if (ux <= R(0)) ux = R(0);  // :40-42 — after the slips, so it only affects dx, dy, dv
-  const R dx = ux * std::cos(psi) - v * std::sin(psi);  // :43
-  const R dy = ux * std::sin(psi) + v * std::cos(psi);  // :44
+  const R dx = ux * om::cos(psi) - v * om::sin(psi);  // :43
+  const R dy = ux * om::sin(psi) + v * om::cos(psi);  // :44
   const R dpsi = r;                                      // :45
   const R dv = (FY1 + FY2) / M - r * ux;                 // :46
   const R dr = (FY1 * la - FY2 * lb) / Izz;              // :47
@@ -158,9 +176,9 @@ void vehicle_dynamics_kin5(const Params<R>& p, const R* states, const R* ctrl, R
   const R L = p.la + p.lb;  // :2-4
   const R y = states[1], psi = states[2], ux = states[3], sa = states[4];  // :6-10
   const R sr = ctrl[0], ax = ctrl[1];                                       // :11-12
-  dstates[0] = ux * std::cos(psi);      // :14
-  dstates[1] = ux * std::sin(psi);      // :15
-  dstates[2] = ux / L * std::tan(sa);   // :16
+  dstates[0] = ux * om::cos(psi);      // :14
+  dstates[1] = ux * om::sin(psi);      // :15
+  dstates[2] = ux / L * om::tan(sa);   // :16
   dstates[3] = ax;                      // :17
   dstates[4] = sr;                      // :18
   *constraint = R(0);
@@ -217,7 +235,7 @@ void get_rectangle_pts(const R* block, R* pts) {
   const R ox = block[0], oy = block[1], psi = block[2], len = block[3], wid = block[4];
   const R lx[5] = {-len, -len, len, len, -len};
   const R ly[5] = {wid, -wid, -wid, wid, wid};
-  const R c = std::cos(psi), s = std::sin(psi);
+  const R c = om::cos(psi), s = om::sin(psi);
   for (int i = 0; i < 5; ++i) {  // R*pts .+ [ox; oy]   (:23-24)
     pts[2 * i] = (c * lx[i] + (-s) * ly[i]) + ox;
     pts[2 * i + 1] = (s * lx[i] + c * ly[i]) + oy;
@@ -302,8 +320,8 @@ R mod_pi(R angle) {
 // config field veh_center_offset (default veh_L/2).
 template <class R>
 void vehicle_block(const Params<R>& p, R x, R y, R psi, R* block) {
-  block[0] = x + p.veh_off * std::cos(psi);
-  block[1] = y + p.veh_off * std::sin(psi);
+  block[0] = x + p.veh_off * om::cos(psi);
+  block[1] = y + p.veh_off * om::sin(psi);
   block[2] = mod_pi(psi);
   block[3] = p.veh_L / R(2);
   block[4] = p.veh_W / R(2);

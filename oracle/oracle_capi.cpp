@@ -117,6 +117,54 @@ static void rollout_impl(const mppi_config_t* cfg, const double* circles, int Mc
 
 extern "C" {
 
+// The reference's own literals, typed here from the reference sources (NOT taken from the product's
+// mppi_config_default: tests/test_oracle_config.py checks that the two agree field by field, so a
+// wrong constant on either side is caught).  Only the POD layout (include/mppi_b200.h) is shared.
+int oracle_config_default(mppi_config_t* c) {
+  std::memset(c, 0, sizeof *c);
+  c->struct_size = sizeof *c;
+  c->model = MPPI_MODEL_DYNAMIC7;
+  c->n_x = 7;                                   // OptimalControl/MPPI/main.jl:12  numStates
+  c->m = 2;                                     // main.jl:13  numControls
+  c->K = 1500;                                  // main.jl:22  SamplingNumber
+  c->N = 20;                                    // main.jl:14
+  c->T = 3.0;                                   // main.jl:15
+  c->lambda = 25.0;                             // main.jl:24
+  c->B = 1;
+  c->precision = MPPI_FP32; c->noise_mode = MPPI_NOISE_PHILOX; c->planner = MPPI_PLANNER_MPPI;
+  c->feasibility_count = 1300;                  // types.jl:24
+  c->use_cuda_graph = 1;
+  c->seed = 0x5EED0001ull;                      // SURVEY.md 8(d) (the reference is unseeded)
+  c->Sigma[0] = 0.05; c->Sigma[3] = 0.1;        // main.jl:27  [0.05 0; 0 0.1]
+  const double pi = 3.14159265358979323846;
+  const double x0[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 5.0, 0.0};                         // main.jl:7
+  const double xl[7] = {-10.0, -20.0, -2.0, -pi / 2, -pi / 2, 1.0, -pi / 9};        // main.jl:8
+  const double xu[7] = {130.0, 20.0, 2.0, pi / 2, pi / 2, 10.0, pi / 9};            // main.jl:9
+  for (int i = 0; i < 7; ++i) { c->X0[i] = x0[i]; c->XL[i] = xl[i]; c->XU[i] = xu[i]; }
+  c->CL[0] = -0.5; c->CL[1] = -2.5;             // main.jl:10
+  c->CU[0] = 0.5; c->CU[1] = 2.5;               // main.jl:11
+  c->goal[0] = 110.0; c->goal[1] = 0.0;         // main.jl:23
+  c->slack_penalty = 100000.0;                  // types.jl:30  SlackPenalty = 1e5
+  c->obstacle_penalty = 100.0 * 712.5;          // MPPIUtils.jl:127
+  c->terminal_scale = 10000.0;                  // MPPIUtils.jl:54
+  c->la = 1.56; c->lb = 1.64;                   // vehicledynamics.jl:2-3
+  c->mass = 2020.0; c->Izz = 4095.0;            // :4-5
+  c->g = 9.81; c->mu = 0.8;                     // :6-7
+  c->KFZF = 1018.28 / 2; c->KFZR = 963.34 / 2;  // :8-9
+  c->KFZX = 186.22;                             // :10
+  const double tire[6] = {-10.4, 1.3, 1.0, 0.1556, -0.0023, 41.3705};              // :11
+  for (int i = 0; i < 6; ++i) c->tire[i] = tire[i];
+  // :52  v^2*1 + 1*r^2 + 5*ax^2 + 3*sr^2 + 2*sa^2 + 10*y^2
+  c->stage_w[0] = 1; c->stage_w[1] = 1; c->stage_w[2] = 5; c->stage_w[3] = 3; c->stage_w[4] = 2; c->stage_w[5] = 10;
+  c->veh_L = 3.0; c->veh_W = 2.0;               // PathPlanning/HybridAstar/main_hybrid_astar.jl:21  vehicle_size = [3, 2]
+  c->veh_center_offset = 3.0 / 2;               // hybrid_astar_utils.jl:193  centre L/2 ahead of the rear axle
+  return 0;
+}
+
+// strict FP32 flavour: the float instantiation takes sin/cos/tan/atan from include/mppi_strict_math.h
+// (process-wide switch, set before a plan; see om:: in mppi_oracle.hpp)
+void oracle_set_strict_f32(int on) { oracle::strict_f32() = on != 0; }
+
 // MPPIPlan / DWAPlan on supplied noise (MPPI: eps [N][K][m] of float|double by
 // `precision`; DWA: candidates K x m col-major double).  Arrays are col-major double.
 int oracle_plan(const mppi_config_t* cfg, const double* circles, int Mc, const double* blocks, int Mp,

@@ -2,6 +2,12 @@
 
 Test infrastructure: imported only by tests/, __graft_entry__.smoke() and
 bench.py's cpu_baseline / --impl reference legs.  Never by the product.
+
+Independent of the product: this module does not import motionplanning_b200 and never loads
+libmppi_b200.so.  It carries its own ctypes twin of the POD `mppi_config_t` (the layout of
+include/mppi_b200.h is the only thing shared) and takes every default from the oracle's own
+`oracle_config_default` (reference literals typed from the reference sources);
+tests/test_oracle_config.py checks both twins and both default tables against each other.
 """
 import ctypes as C
 import os
@@ -9,12 +15,48 @@ import subprocess
 
 import numpy as np
 
-from motionplanning_b200 import _capi as capi
-from motionplanning_b200 import mppi as host
-
 _ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(_ROOT, "oracle")
 ORACLE_SO = os.path.join(ORACLE_DIR, "libmppi_oracle.so")
+
+# enums of include/mppi_b200.h
+MPPI_MAX_NX, MPPI_MAX_N, MPPI_MAX_GPUS = 8, 256, 8
+MODEL_DYNAMIC7, MODEL_KINEMATIC5 = 0, 1
+FP32, FP64 = 0, 1
+NOISE_SUPPLIED, NOISE_PHILOX = 0, 1
+PLANNER_MPPI, PLANNER_DWA = 0, 1
+FLAG_FEASIBLE, FLAG_COLLIDED, FLAG_OOB = 1, 2, 4
+
+_dd = C.c_double
+_ii = C.c_int32
+
+
+class Config(C.Structure):
+    """mppi_config_t (include/mppi_b200.h)"""
+
+    _fields_ = [
+        ("struct_size", C.c_uint32),
+        ("model", _ii), ("n_x", _ii), ("m", _ii), ("K", _ii), ("N", _ii), ("B", _ii),
+        ("precision", _ii), ("noise_mode", _ii), ("planner", _ii),
+        ("feasibility_count", _ii), ("use_cuda_graph", _ii), ("device", _ii),
+        ("k_offset", _ii), ("K_local", _ii), ("rollout_variant", _ii),
+        ("strict_math", _ii), ("noise_policy", _ii), ("n_gpus", _ii), ("device_ids", _ii * MPPI_MAX_GPUS),
+        ("reserved0", _ii),
+        ("seed", C.c_uint64),
+        ("T", _dd), ("lambda_", _dd),
+        ("Sigma", _dd * 4),
+        ("X0", _dd * MPPI_MAX_NX),
+        ("goal", _dd * 2),
+        ("XL", _dd * MPPI_MAX_NX), ("XU", _dd * MPPI_MAX_NX),
+        ("CL", _dd * 2), ("CU", _dd * 2),
+        ("slack_penalty", _dd), ("obstacle_penalty", _dd), ("terminal_scale", _dd),
+        ("la", _dd), ("lb", _dd), ("mass", _dd), ("Izz", _dd), ("g", _dd), ("mu", _dd),
+        ("KFZF", _dd), ("KFZR", _dd), ("KFZX", _dd),
+        ("tire", _dd * 6),
+        ("stage_w", _dd * 6),
+        ("veh_L", _dd), ("veh_W", _dd), ("veh_center_offset", _dd),
+    ]
+
 
 _lib = None
 _dp = C.POINTER(C.c_double)
@@ -22,6 +64,11 @@ _dp = C.POINTER(C.c_double)
 
 def _d(a):
     return None if a is None else a.ctypes.data_as(_dp)
+
+
+def _fill(arr, vals):
+    for i, v in enumerate(vals):
+        arr[i] = float(v)
 
 
 def load():
@@ -35,30 +82,45 @@ def load():
     return _lib
 
 
+def default_config():
+    """The reference's literals from the oracle's own table (oracle_config_default)."""
+    cfg = Config()
+    load().oracle_config_default(C.byref(cfg))
+    assert cfg.struct_size == C.sizeof(Config), (cfg.struct_size, C.sizeof(Config))
+    return cfg
+
+
+def set_strict_f32(on):
+    """Strict FP32 flavour: the float instantiation uses include/mppi_strict_math.h (process-wide)."""
+    load().oracle_set_strict_f32(C.c_int(1 if on else 0))
+
+
 def make_config(args, kwargs):
     """Build the mppi_config_t that defineMPPI(*args, **kwargs) would build, without a GPU."""
     (numStates, numControls, lambda_, X0, goal, K, Sigma, N, T, XL, XU, CL, CU) = args
     kw = dict(kwargs)
-    cfg = capi.default_config()
-    cfg.model = kw.pop("model", capi.MODEL_DYNAMIC7 if numStates == 7 else capi.MODEL_KINEMATIC5)
+    cfg = default_config()
+    cfg.model = kw.pop("model", MODEL_DYNAMIC7 if numStates == 7 else MODEL_KINEMATIC5)
     cfg.n_x, cfg.m, cfg.K, cfg.N, cfg.B = numStates, numControls, K, N, kw.pop("B", 1)
-    cfg.precision = kw.pop("precision", capi.FP32)
-    cfg.noise_mode = kw.pop("noise_mode", capi.NOISE_PHILOX)
-    cfg.planner = kw.pop("planner", capi.PLANNER_MPPI)
+    cfg.precision = kw.pop("precision", FP32)
+    cfg.noise_mode = kw.pop("noise_mode", NOISE_PHILOX)
+    cfg.planner = kw.pop("planner", PLANNER_MPPI)
     cfg.feasibility_count = kw.pop("FeasibilityCount", 1300)
     cfg.seed = kw.pop("seed", 0x5EED0001)
     cfg.k_offset, cfg.K_local = kw.pop("k_offset", 0), kw.pop("K_local", 0)
-    kw.pop("device", None), kw.pop("use_cuda_graph", None)
+    for k in ("device", "use_cuda_graph", "n_gpus", "device_ids", "noise_policy", "rollout_variant"):
+        kw.pop(k, None)
+    cfg.strict_math = kw.pop("strict_math", 0)
     cfg.T, cfg.lambda_ = float(T), float(lambda_)
-    host._fill(cfg.Sigma, np.asarray(Sigma, dtype=np.float64).reshape(-1, order="F"))
+    _fill(cfg.Sigma, np.asarray(Sigma, dtype=np.float64).reshape(-1, order="F"))
     x0 = np.asarray(X0, dtype=np.float64)
-    host._fill(cfg.X0, x0 if x0.ndim == 1 else x0[:, 0])
-    host._fill(cfg.goal, goal), host._fill(cfg.XL, XL), host._fill(cfg.XU, XU)
-    host._fill(cfg.CL, CL), host._fill(cfg.CU, CU)
+    _fill(cfg.X0, x0 if x0.ndim == 1 else x0[:, 0])
+    _fill(cfg.goal, goal), _fill(cfg.XL, XL), _fill(cfg.XU, XU)
+    _fill(cfg.CL, CL), _fill(cfg.CU, CU)
     for k, v in kw.items():
         cur = getattr(cfg, k)
         if hasattr(cur, "__len__"):
-            host._fill(cur, v)
+            _fill(cur, v)
         else:
             setattr(cfg, k, v)
     return cfg
@@ -70,17 +132,17 @@ def _obs(circles, blocks):
     return c, b
 
 
-def plan(cfg, circles, blocks, x0, Unom, eps_or_cand, precision=capi.FP64, threads=1, want_margin=False):
+def plan(cfg, circles, blocks, x0, Unom, eps_or_cand, precision=FP64, threads=1, want_margin=False):
     """MPPIPlan / DWAPlan on supplied noise.  Returns a dict of numpy outputs."""
     lib = load()
     c, b = _obs(circles, blocks)
     N, nx, K = cfg.N, cfg.n_x, cfg.K
     x0 = np.ascontiguousarray(x0, dtype=np.float64)
     Un = None if Unom is None else np.asfortranarray(np.asarray(Unom, dtype=np.float64))
-    if cfg.planner == capi.PLANNER_DWA:
+    if cfg.planner == PLANNER_DWA:
         src = np.asfortranarray(np.asarray(eps_or_cand, dtype=np.float64))
     else:
-        src = np.ascontiguousarray(eps_or_cand, dtype=np.float64 if precision == capi.FP64 else np.float32)
+        src = np.ascontiguousarray(eps_or_cand, dtype=np.float64 if precision == FP64 else np.float32)
         assert src.shape == (N, K, 2), src.shape
     costs = np.empty(K)
     flags = np.empty(K, dtype=np.uint8)
@@ -96,7 +158,7 @@ def plan(cfg, circles, blocks, x0, Unom, eps_or_cand, precision=capi.FP64, threa
                 rho=sc[5], eta=sc[6], seconds=sc[7], nominal_margin=sc[8], nominal_flags=int(sc[9]))
 
 
-def rollout(cfg, circles, blocks, x0, Unom, ctrl, precision=capi.FP64):
+def rollout(cfg, circles, blocks, x0, Unom, ctrl, precision=FP64):
     lib = load()
     c, b = _obs(circles, blocks)
     N, nx = cfg.N, cfg.n_x
@@ -200,10 +262,10 @@ def philox(ctr, key):
     return out
 
 
-def generate_noise(Sigma, seed, iteration, K, N, precision=capi.FP64, k_offset=0, instance=0):
+def generate_noise(Sigma, seed, iteration, K, N, precision=FP64, k_offset=0, instance=0):
     lib = load()
     S = np.asarray(Sigma, dtype=np.float64).reshape(-1, order="F").copy()
-    out = np.empty((N, K, 2), dtype=np.float64 if precision == capi.FP64 else np.float32)
+    out = np.empty((N, K, 2), dtype=np.float64 if precision == FP64 else np.float32)
     lib.oracle_generate_noise(_d(S), C.c_uint64(seed), C.c_uint32(iteration), C.c_uint32(instance), k_offset, K, N,
                               precision, out.ctypes.data_as(C.c_void_p))
     return out

@@ -43,14 +43,19 @@ def run_pair(args, kw, circles, blocks, precision, Unom=None, eps=None, iteratio
     return mppi, ref
 
 
-def check(mppi, ref, precision):
+GUARD_MAX_FRACTION = 0.005   # at most 0.5 % of the samples may sit inside the guard band
+
+
+def check(mppi, ref, precision, guard_max=GUARD_MAX_FRACTION):
     tol = FP64_TOL if precision == capi.FP64 else FP32_TOL
     costs, flags = mppi.p.costs, mppi.p.flags
     R = ref["rollout_count"] - 1
     ok = np.ones(len(costs), dtype=bool)
     if precision == capi.FP32:
         ok = ref["margins"] > GUARD
-        assert (~ok[:R]).sum() <= 0.05 * R, f"{(~ok[:R]).sum()} guard-band samples of {R}"
+        n_guard = int((~ok[:R]).sum())
+        print(f"[guard band] {n_guard} of {R} samples excluded from the FP32 flag comparison ({100.0 * n_guard / max(R, 1):.3f} %)")
+        assert n_guard <= max(guard_max * R, 2), f"{n_guard} guard-band samples of {R}"
     ok[R:] = False  # samples past the feasibility cut-off are never drawn by the reference
     rel = np.abs(costs - ref["costs"]) / np.maximum(np.abs(ref["costs"]), 1e-300)
     assert rel[ok].max() <= tol, f"per-sample cost rel err {rel[ok].max():.3e}"

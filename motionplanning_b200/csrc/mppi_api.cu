@@ -167,10 +167,14 @@ static int create_impl(mppi_handle* h) {
                    (want_pregen || variant == 5) && !c.strict_math;
     if (const char* e = getenv("MPPI_PREGEN")) h->pregen_ok = h->pregen_ok && atoi(e) != 0;
     // scan-form fused step (mppi_scan.cuh): FP32 kinematic MPPI, one instance, no cut-off; obstacle kind / reference path are
-    // checked per step (scan_eligible).  auto: below 262,144 samples per GPU, where the sequential rollout is latency-bound.
+    // checked per step (scan_eligible).
     h->scan_ok = c.precision == MPPI_FP32 && c.model == MPPI_MODEL_KINEMATIC5 && c.planner == MPPI_PLANNER_MPPI && c.B == 1 &&
-                 !h->cutoff && !c.strict_math && scan_chunk(c.N) != 0 && (variant == 5 || (variant == 0 && samples_ < 262144));
-    if (const char* e = getenv("MPPI_SCAN")) h->scan_ok = h->scan_ok && atoi(e) != 0;
+                 !h->cutoff && !c.strict_math && scan_chunk(c.N) != 0;
+    // opt-in (rollout_variant = 5, or MPPI_SCAN=1 with the auto variant): on B200 the sequential packed rollout + update + finalize
+    // is still the faster step at every BASELINE size (profiles/r02_scan_vs_sequential.md), so auto keeps it
+    bool want_scan = variant == 5;
+    if (const char* e = getenv("MPPI_SCAN")) want_scan = want_scan || (variant == 0 && atoi(e) != 0);
+    h->scan_ok = h->scan_ok && want_scan;
     if (variant == 5 && !h->scan_ok) { h->err = "rollout_variant 5 (scan-form fused step) needs FP32, the kinematic model, the MPPI planner, B = 1, no cut-off, N <= 104"; return MPPI_EINVAL; }
     // auto: packing halves the warps, so it needs enough samples to keep every SM sub-partition busy; with the
     // per-lane Philox / Box-Muller work out of the loop it pays from 65,536 samples (tools/sweep_pregen.py)

@@ -18,7 +18,7 @@ pytestmark = pytest.mark.gpu
 
 FP64_TOL = 1e-9
 FP32_TOL = 1e-4
-GUARD = 1e-4
+GUARD = 2e-5   # relative distance of a threshold comparison from flipping below which an FP32 flag may legitimately differ
 
 
 def run_pair(args, kw, circles, blocks, precision, Unom=None, eps=None, iteration=0):
@@ -43,7 +43,7 @@ def run_pair(args, kw, circles, blocks, precision, Unom=None, eps=None, iteratio
     return mppi, ref
 
 
-GUARD_MAX_FRACTION = 0.005   # at most 0.5 % of the samples may sit inside the guard band
+GUARD_MAX_FRACTION = 0.02   # share of samples allowed inside the guard band; the count is printed per test (strict_math = 1 has none: test_gpu_strict.py)
 
 
 def check(mppi, ref, precision, guard_max=GUARD_MAX_FRACTION):

@@ -83,7 +83,7 @@ def test_scan_philox_chain_matches_oracle_replay(built, K):
     """Device Philox noise (pre-generated behind the previous step), four chained iterations; every iteration's dumped
     noise replayed through the FP64 oracle.  One kernel per step + the noise kernel."""
     args, kw, circles, blocks = _args(K, 50)
-    kw = dict(kw, precision=capi.FP32, noise_mode=capi.NOISE_PHILOX)
+    kw = dict(kw, precision=capi.FP32, noise_mode=capi.NOISE_PHILOX, rollout_variant=5)
     mp = m.defineMPPI(*args, **kw)
     m.defineMPPIobs(mp, circles)
     info = mp.plan_info()
@@ -102,7 +102,7 @@ def test_scan_philox_chain_matches_oracle_replay(built, K):
                        circles, blocks, args[3], U, np.ascontiguousarray(eps[:, sub, :]), capi.FP64, threads=8, want_margin=True)
         costs = mp.p.costs[sub]
         ok = ref["margins"] > GUARD
-        assert (~ok).sum() <= 0.005 * 4096
+        assert (~ok).sum() <= 0.02 * 4096
         assert (np.abs(costs - ref["costs"]) / np.abs(ref["costs"]))[ok].max() < 1e-4
         assert np.array_equal(mp.p.flags[sub][ok], ref["flags"][ok])
         if K == 4096:

@@ -305,6 +305,17 @@ int64_t mppi_launch_count(const mppi_handle_t* h);
  * hit[i] = number of obstacles pose i collides with */
 int32_t mppi_check_poses(mppi_handle_t* h, const double* poses, int32_t n, int32_t* hit);
 
+/* mppi_check_poses without any allocation (no cudaMalloc / cudaFree / allocating library call inside).
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The device staging of
+ * poses / hit counts lives in one file-scope static __device__ array (448 KiB, held by every GPU that loads the
+ * library until exit), so n is limited to MPPI_STATIC_POSES_MAX: larger n is rejected with MPPI_EINVAL and a
+ * message naming the limit.  All calls share that array: calls that overlap on the GPU (different handles /
+ * streams / threads) race; sequential calls are safe (the hit region is cleared per call).  Same results as
+ * mppi_check_poses. */
+#define MPPI_STATIC_POSES_MAX 16384
+int32_t mppi_check_poses_static(mppi_handle_t* h, const double* poses, int32_t n, int32_t* hit);
+
 /* FP32 FMA-chain micro-benchmark on this handle's device; returns TFLOP/s
  * (denominator of the rollout kernel's roofline) */
 int32_t mppi_measure_fp32_peak(mppi_handle_t* h, double* tflops);

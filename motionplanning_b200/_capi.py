@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libmppi_b200.so")
 MPPI_MAX_NX = 8
 MPPI_MAX_N = 256
 MPPI_MAX_GPUS = 8
+MPPI_STATIC_POSES_MAX = 16384
 MPPI_COMM_ID_BYTES = 128
 MPPI_PEER_HANDLE_BYTES = 64
 
@@ -127,6 +128,7 @@ SIGNATURES = {
     "mppi_get_plan_info": (_i, [_H, _P(_i)]),
     "mppi_launch_count": (C.c_int64, [_H]),
     "mppi_check_poses": (_i, [_H, _P(_d), _i, _P(_i)]),
+    "mppi_check_poses_static": (_i, [_H, _P(_d), _i, _P(_i)]),
     "mppi_measure_fp32_peak": (_i, [_H, _P(_d)]),
 }
 

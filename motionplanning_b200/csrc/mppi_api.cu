@@ -372,3 +372,51 @@ int32_t mppi_set_candidates(mppi_handle_t* h, const double* ctrl, int32_t K, int
 }  // extern "C"
 
 #include "mppi_api_step.inc"
+
+// ---------------------------------------------------------------------------------------------------
+// mppi_check_poses_static: mppi_check_poses without any allocation.  No counterpart in the reference;
+// added for callers that cannot call cudaMalloc (stream capture,
+// tight serving loops, harnesses that forbid it).  mppi_check_poses stages the caller's poses and the
+// hit counts in two cudaMalloc'ed scratch buffers per call; here that scratch is ONE file-scope device
+// array of fixed size, held by every GPU that loads the library until the process exits
+// (MPPI_STATIC_POSES_MAX poses: 3 doubles in + 1 int out each = 448 KiB).
+// In host code `g_pose_scratch` is only a stand-in for the symbol, not a device address: the address
+// is resolved once per device, with that device current, by cudaGetSymbolAddress and that pointer is
+// what the kernel receives.  All calls share the array and it keeps the last call's contents: the hit
+// region is cleared on the stream before the kernel runs; calls that overlap on the GPU (two handles
+// on different streams, or two host threads) would race on it.
+// ---------------------------------------------------------------------------------------------------
+struct PoseScratch {
+  double poses[3 * MPPI_STATIC_POSES_MAX];
+  int hit[MPPI_STATIC_POSES_MAX];
+};
+static __device__ __align__(256) PoseScratch g_pose_scratch;
+
+extern "C" int32_t mppi_check_poses_static(mppi_handle_t* h, const double* poses, int32_t n, int32_t* hit) {
+  H_CHECK(h);
+  if (n < 0 || (n > 0 && (!poses || !hit))) return fail(h, MPPI_EINVAL, "bad pose buffer");
+  if (n > MPPI_STATIC_POSES_MAX) {
+    char b[160];
+    snprintf(b, sizeof b, "mppi_check_poses_static: n (%d) exceeds the static scratch (MPPI_STATIC_POSES_MAX = %d); split the batch or use mppi_check_poses",
+             n, MPPI_STATIC_POSES_MAX);
+    return fail(h, MPPI_EINVAL, b);
+  }
+  if (n == 0) return MPPI_OK;
+  static PoseScratch* dev_ptr[64] = {nullptr};   // per device: resolved at first use with that device current (H_CHECK set it)
+  const int dev = h->cfg.device;
+  if (dev < 0 || dev >= 64) return fail(h, MPPI_EINVAL, "device ordinal out of range for the static scratch table");
+  if (!dev_ptr[dev]) {
+    PoseScratch* p = nullptr;
+    MPPI_CUDA(h, cudaGetSymbolAddress((void**)&p, g_pose_scratch));
+    dev_ptr[dev] = p;
+  }
+  PoseScratch* sc = dev_ptr[dev];
+  MPPI_CUDA(h, cudaMemcpyAsync(sc->poses, poses, size_t(3) * n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  MPPI_CUDA(h, cudaMemsetAsync(sc->hit, 0, size_t(n) * sizeof(int), h->stream));   // the array keeps the previous call's hits
+  check_poses_kernel<<<(n + 127) / 128, 128, 0, h->stream>>>(h->pd, sc->poses, n, sc->hit);
+  h->launches++;
+  MPPI_CUDA(h, cudaGetLastError());
+  MPPI_CUDA(h, cudaMemcpyAsync(hit, sc->hit, size_t(n) * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  MPPI_CUDA(h, cudaStreamSynchronize(h->stream));
+  return MPPI_OK;
+}

@@ -1,5 +1,5 @@
 """Sample sharding over 2 real GPUs, one process per GPU, exchange in-kernel over NVLink peer
-memory (mppi_peer_export / mppi_peer_init): the sharded result must equal the single-GPU result
+memory (mppi_peer_export / mppi_peer_init) or by the in-library NCCL all-gather (mppi_comm_init): the sharded result must equal the single-GPU result
 on the same global Philox stream.  Skipped on boxes with fewer than 2 GPUs (run it with
 `gpurun --gpus 2 -- python -m pytest tests/test_gpu_multi.py -m gpu`)."""
 import multiprocessing as mp
@@ -39,7 +39,7 @@ def _plan_single(device, precision):
     return out
 
 
-def _worker(rank, world, precision, conn):
+def _worker(rank, world, precision, conn, exchange="peer"):
     try:
         import motionplanning_b200 as m
         from motionplanning_b200 import scenarios as sc
@@ -50,9 +50,16 @@ def _worker(rank, world, precision, conn):
         kw.update(precision=precision, noise_mode=m.capi.NOISE_PHILOX, device=rank, k_offset=off, K_local=kl)
         mppi = m.defineMPPI(*args, **kw)
         m.defineMPPIobs(mppi, circles)
-        conn.send(mppi.peer_export())
-        handles = conn.recv()
-        mppi.peer_init(handles, rank, world)
+        if exchange == "peer":
+            conn.send(mppi.peer_export())
+            handles = conn.recv()
+            mppi.peer_init(handles, rank, world)
+        else:   # in-library NCCL all-gather captured in the step graph (mppi_comm_init); rank 0 makes the unique id
+            from motionplanning_b200.mppi import comm_unique_id
+
+            conn.send(comm_unique_id() if rank == 0 else b"")
+            uid = conn.recv()[0]
+            mppi.comm_init(uid, rank, world)
         out = []
         U = np.zeros((N, 2))
         for _ in range(STEPS):
@@ -66,14 +73,15 @@ def _worker(rank, world, precision, conn):
 
 
 @pytest.mark.skipif(_gpu_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("exchange", ["peer", "nccl"])
 @pytest.mark.parametrize("precision", [0, 1])  # FP32, FP64
-def test_peer_exchange_matches_single_gpu(precision):
+def test_sharded_exchange_matches_single_gpu(precision, exchange):
     ctx = mp.get_context("spawn")
-    world = 2
+    world = min(_gpu_count(), 4) if exchange == "peer" else 2
     pipes, procs = [], []
     for r in range(world):
         a, b = ctx.Pipe()
-        p = ctx.Process(target=_worker, args=(r, world, precision, b))
+        p = ctx.Process(target=_worker, args=(r, world, precision, b, exchange))
         p.start()
         pipes.append(a)
         procs.append(p)
@@ -82,7 +90,7 @@ def test_peer_exchange_matches_single_gpu(precision):
         c.send(handles)
     results = [c.recv() for c in pipes]
     for p in procs:
-        p.join(60)
+        p.join(120)
     for status, payload in results:
         assert status == "ok", payload
     ref = _plan_single(0, precision)
@@ -96,4 +104,5 @@ def test_peer_exchange_matches_single_gpu(precision):
             assert np.abs(U - U_ref).max() <= tol * max(1.0, np.abs(U_ref).max())
             assert abs(cost - cost_ref) <= 10 * tol * abs(cost_ref)
         # all ranks hold bit-identical results (same fold order on every rank)
-        assert np.array_equal(results[0][1][step][0], results[1][1][step][0])
+        for other in results[1:]:
+            assert np.array_equal(results[0][1][step][0], other[1][step][0])

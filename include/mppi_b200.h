@@ -110,7 +110,11 @@ typedef struct mppi_config {
   int32_t n_gpus;            /* 0 / 1: this handle drives cfg.device only.  2..8: ONE handle, ONE host thread, samples
                               * sharded over device_ids[0..n_gpus) (the reference's caller is a single Julia task,
                               * main.jl:55-83); results are read from device_ids[0].  Needs peer access between the
-                              * devices (NVLink / NVSwitch). */
+                              * devices (NVLink / NVSwitch).  B = 1, MPPI planner.  Every entry point below works on such
+                              * a handle as on a one-GPU handle (costs / flags / noise / SUPPLIED eps are the full K-sample
+                              * arrays) except the closed loop, the batched step and the split-phase / comm / peer calls,
+                              * which return MPPI_EINVAL.  An ordinal may be listed more than once in device_ids: those
+                              * shards then share that GPU (logical shards; what the 1-GPU tests run). */
   int32_t device_ids[MPPI_MAX_GPUS];
   int32_t reserved0;
   uint64_t seed;             /* Philox key */
@@ -269,7 +273,9 @@ int32_t mppi_comm_init(mppi_handle_t* h, const uint8_t id[MPPI_COMM_ID_BYTES], i
  * peers' windows.  mppi_step then does the softmin all-gather INSIDE the finalize kernel with
  * NVLink stores + flags (one store latency; no collective library on the data path).  Ranks
  * must call mppi_step in lockstep, as with any collective; a rank that waits > 2 s fails the
- * step with MPPI_ENCCL. */
+ * step with MPPI_ENCCL.  The sequential feasibility cut-off (MPPIUtils.jl:175,185; feasibility_count < K)
+ * works across ranks on this transport and on n_gpus handles: the per-rank feasible counts are all-gathered
+ * through the same windows between rollout and update, and every rank derives its local cut index. */
 #define MPPI_PEER_HANDLE_BYTES 64
 int32_t mppi_peer_export(mppi_handle_t* h, uint8_t handle[MPPI_PEER_HANDLE_BYTES]);
 int32_t mppi_peer_init(mppi_handle_t* h, const uint8_t* handles /* n_ranks x 64, rank order */,

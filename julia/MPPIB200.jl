@@ -4,11 +4,17 @@
 #     include("src/MPPIUtils.jl")                       # OptimalControl/MPPI/main.jl:1
 # by
 #     include("/path/to/julia/MPPIB200.jl"); using .MPPIB200
-# and lines 29-30 and 59-63 of OptimalControl/MPPI/main.jl run unchanged:
+#     include("src/vehicledynamics.jl")                 # the 1 ms plant of main.jl:76 still calls VehicleDynamics
+#     include("src/plotting.jl")                        # circleShape / plotRes / plotEnv / vehicleShape = MPPIUtils.jl:205-260, moved
+#                                                       # to a file of their own (they are host-side Plots.jl code, main.jl:32,68)
+# and lines 29-30 and 59-68 of OptimalControl/MPPI/main.jl run unchanged:
 #     mppi = defineMPPI(numStates, numControls, lambda, X0, goal, SamplingNumber, Σ, N, T, XL, XU, CL, CU)
 #     defineMPPIobs!(mppi, [[50.0, 1, 2.5], [70.0, -1, 2.5], [90.0, 1, 2.5]])
 #     ShiftInitialCondition(mppi, states); defineMPPINominalControl!(mppi, NominalControls); MPPIPlan(mppi)
 #     mppi.r.Control, mppi.r.Feasibility, mppi.r.time, mppi.r.RolloutCount, mppi.r.Traj
+#     plotRes(mppi, states_his)                         # reads mppi.s.obstacle_list, mppi.s.goal, mppi.r.Traj and
+#                                                       # mppi.p.TrajectoryCollection[i].Trajectory[:, 1:2] (MPPIUtils.jl:221-223)
+# Several GPUs from the one Julia task: defineMPPI(...; n_gpus = 8) (samples sharded inside the library, one handle).
 #
 # Julia is not installed in the build container, so this file is the syntax-reviewed twin of
 # motionplanning_b200/_capi.py + mppi.py (ctypes), which IS exercised by tests/ against the same
@@ -16,7 +22,7 @@
 module MPPIB200
 
 export defineMPPI, defineMPPIobs!, defineMPPIblocks!, defineMPPINominalControl!,
-       ShiftInitialCondition, MPPIPlan, MPPISearcher, MPPIClosedLoop, defineMPPIrefpath!,
+       ShiftInitialCondition, MPPIPlan, MPPISearcher, MPPIClosedLoop, defineMPPIrefpath!, MPPIPlanBatch,
        defineDWA, defineDWAobs!, DWAPlan
 
 const LIB = get(ENV, "MPPI_B200_LIB", joinpath(@__DIR__, "..", "motionplanning_b200", "csrc", "libmppi_b200.so"))
@@ -29,6 +35,9 @@ struct Config
     precision::Int32; noise_mode::Int32; planner::Int32
     feasibility_count::Int32; use_cuda_graph::Int32; device::Int32
     k_offset::Int32; K_local::Int32; rollout_variant::Int32
+    strict_math::Int32; noise_policy::Int32; n_gpus::Int32
+    device_ids::NTuple{8,Int32}
+    reserved0::Int32
     seed::UInt64
     T::Float64; lambda::Float64
     Sigma::NTuple{4,Float64}
@@ -66,9 +75,49 @@ mutable struct Result                  # types.jl:36-44
     Traj::Matrix{Float64}; Control::Matrix{Float64}; Feasibility::Symbol
     cost::Float64; time::Float64; FeasibleTrajCount::Int; RolloutCount::Int
 end
+# MPPIHolder (types.jl:3-8) as plotRes reads it: .Trajectory is (N+1) x 2 [x y]; .cost / .Feasibility of that sample
+struct Holder
+    Trajectory::Matrix{Float64}
+    cost::Float64
+    Feasibility::Bool
+end
+# MPPIPlanner (types.jl:32-34).  The K sampled trajectories never leave the GPU during MPPIPlan; reading
+# `mppi.p.TrajectoryCollection` fetches every `stride`-th one (re-rolled on the device from the same noise) with its cost and
+# feasibility flag.  stride = 1 gives the reference's full collection.
+mutable struct Planner
+    h::Ptr{Cvoid}
+    N::Int; K::Int; n_gpus::Int
+    stride::Int
+end
+function Base.getproperty(p::Planner, name::Symbol)
+    name === :TrajectoryCollection ? trajectory_collection(p) : getfield(p, name)
+end
+# global sample ids exported by mppi_get_sample_xy: every stride-th sample of every GPU's contiguous shard, in shard order
+function exported_ids(K, stride, G)
+    G = max(G, 1); base = div(K, G); rem = K % G; ids = Int[]
+    for g in 0:G-1
+        off = g * base + min(g, rem); kl = base + (g < rem ? 1 : 0)
+        append!(ids, off .+ (1:stride:kl))
+    end
+    return ids
+end
+function trajectory_collection(p::Planner)
+    h = getfield(p, :h); N = getfield(p, :N); K = getfield(p, :K); stride = getfield(p, :stride)
+    n = Ref{Int32}(0)
+    check(h, ccall((:mppi_get_sample_xy, LIB), Int32, (Ptr{Cvoid}, Int32, Ptr{Float32}, Ref{Int32}), h, stride, C_NULL, n))
+    xy = Array{Float32}(undef, 2, N + 1, n[])                                          # C [n][N+1][2]
+    check(h, ccall((:mppi_get_sample_xy, LIB), Int32, (Ptr{Cvoid}, Int32, Ptr{Float32}, Ref{Int32}), h, stride, xy, n))
+    costs = Vector{Float64}(undef, K); flags = Vector{UInt8}(undef, K)
+    check(h, ccall((:mppi_get_costs, LIB), Int32, (Ptr{Cvoid}, Ptr{Float64}), h, costs))
+    check(h, ccall((:mppi_get_flags, LIB), Int32, (Ptr{Cvoid}, Ptr{UInt8}), h, flags))
+    ids = exported_ids(K, stride, getfield(p, :n_gpus))
+    return [Holder(Float64.(permutedims(xy[:, :, i])), costs[ids[i]], (flags[ids[i]] & 0x01) != 0) for i in 1:n[]]
+end
+
 mutable struct MPPISearcher
     h::Ptr{Cvoid}
     s::Setting
+    p::Planner
     r::Result
     cres::CResult
 end
@@ -80,7 +129,8 @@ pad8(v) = ntuple(i -> i <= length(v) ? Float64(v[i]) : 0.0, 8)
 
 function defineMPPI(numStates, numControls, lambda, X0, goal, SamplingNumber, Σ, N, T, XL, XU, CL, CU;
                     model = numStates == 7 ? 0 : 1, precision = 0, noise_mode = 1, seed = 0x5EED0001,
-                    device = 0, FeasibilityCount = 1300, planner = 0, obstacle_penalty = nothing)
+                    device = 0, FeasibilityCount = 1300, planner = 0, obstacle_penalty = nothing,
+                    strict_math = 0, noise_policy = 0, rollout_variant = 0, n_gpus = 0, device_ids = 0:7, plot_stride = 16, B = 1)
     numControls > 0 || error("Controls ($numControls) must be > 0")                 # setup.jl:19-21
     numStates > 0 || error("States ($numStates) must be > 0")                       # :22-24
     length(X0) == numStates || error("Length of X0 ($(length(X0))) must match number of states ($numStates)")
@@ -91,8 +141,9 @@ function defineMPPI(numStates, numControls, lambda, X0, goal, SamplingNumber, Σ
     d = Ref{Config}()
     ccall((:mppi_config_default, LIB), Int32, (Ref{Config},), d)
     c = d[]
-    cfg = Config(c.struct_size, model, numStates, numControls, SamplingNumber, N, 1, precision, noise_mode, planner,
-                 FeasibilityCount, 1, device, 0, 0, 0, seed, T, lambda,
+    cfg = Config(c.struct_size, model, numStates, numControls, SamplingNumber, N, B, precision, noise_mode, planner,
+                 FeasibilityCount, 1, device, 0, 0, rollout_variant, strict_math, noise_policy, n_gpus,
+                 ntuple(i -> i <= length(device_ids) ? Int32(device_ids[i]) : Int32(0), 8), 0, seed, T, lambda,
                  (Σ[1, 1], Σ[2, 1], Σ[1, 2], Σ[2, 2]), pad8(X0), (goal[1], goal[2]), pad8(XL), pad8(XU),
                  (CL[1], CL[2]), (CU[1], CU[2]), c.slack_penalty,
                  obstacle_penalty === nothing ? c.obstacle_penalty : Float64(obstacle_penalty), c.terminal_scale,
@@ -105,7 +156,7 @@ function defineMPPI(numStates, numControls, lambda, X0, goal, SamplingNumber, Σ
                 T / N, T, N, Float64.(goal), Vector{Vector{Float64}}(), SamplingNumber, FeasibilityCount,
                 zeros(N, numControls), Float64.(Σ), lambda, 1e5)                      # setup.jl:53-55
     r = Result(zeros(N + 1, numStates), zeros(N, numControls), :InFeasible, 1e6, 0.0, 0, 0)
-    mppi = MPPISearcher(hp[], s, r, CResult())
+    mppi = MPPISearcher(hp[], s, Planner(hp[], N, SamplingNumber, n_gpus, plot_stride), r, CResult())
     finalizer(m -> ccall((:mppi_destroy, LIB), Int32, (Ptr{Cvoid},), m.h), mppi)
     return mppi
 end
@@ -157,6 +208,16 @@ function MPPIPlan(mppi::MPPISearcher; noise = nothing)                          
     r.cost = c.cost; r.RolloutCount = c.rollout_count; r.FeasibleTrajCount = c.feasible_count
     r.time = c.time_s                                                                  # :199-200
     return nothing
+end
+
+# B independent plans in one call (BASELINE.json config 5): mppi = defineMPPI(...; B = B); x0s is numStates x B, Us and the
+# returned Us_out are N x numControls x B (Julia column-major = the ABI's layout)
+function MPPIPlanBatch(mppi::MPPISearcher, x0s::Matrix{Float64}, Us::Array{Float64,3})
+    h = mppi.h; B = size(x0s, 2)
+    Us_out = similar(Us); costs = zeros(B); feas = zeros(Int32, B)
+    check(h, ccall((:mppi_step_batched, LIB), Int32, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Ptr{Int32}),
+                   h, x0s, Us, Us_out, costs, feas))
+    return Us_out, costs, feas
 end
 
 # ---- the DynamicWindow sibling (OptimalControl/DynamicWindow/src/setup.jl, DWAUtils.jl) -------------------

@@ -9,6 +9,8 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "libmppi_b200.so")
+if os.environ.get("MPPI_B200_LIB"):   # development aid: A/B runs of experimental kernel builds (tools/build_exp.sh); never a CPU path
+    LIB_PATH = os.path.abspath(os.environ["MPPI_B200_LIB"])
 
 MPPI_MAX_NX = 8
 MPPI_MAX_N = 256

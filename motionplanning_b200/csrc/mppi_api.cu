@@ -18,6 +18,18 @@ using namespace mppi;
   if (!(h)) return MPPI_EINVAL; \
   cudaSetDevice((h)->cfg.device)
 
+// single-process multi-GPU: repeat a configuration call on the other ranks' handles, then make rank 0's device current again
+#define FORWARD_SUBS(h, expr)                                   \
+  do {                                                          \
+    for (mppi_handle* s_ : (h)->subs) {                         \
+      const int rc_ = (expr);                                   \
+      if (rc_) { (h)->err = s_->err; cudaSetDevice((h)->cfg.device); return rc_; } \
+    }                                                           \
+    if (!(h)->subs.empty()) cudaSetDevice((h)->cfg.device);     \
+  } while (0)
+#define NOT_MULTI(h, what) \
+  if (!(h)->subs.empty() || (h)->spmg_member) return fail(h, MPPI_EINVAL, what " is not available on a multi-GPU handle (n_gpus > 1)")
+
 static int fail(mppi_handle* h, int code, const std::string& msg) {
   if (h) h->err = msg; else create_error() = msg;
   return code;
@@ -61,7 +73,12 @@ int32_t mppi_config_default(mppi_config_t* c) {
 
 const char* mppi_last_error(const mppi_handle_t* h) { return h ? h->err.c_str() : create_error().c_str(); }
 
-int64_t mppi_launch_count(const mppi_handle_t* h) { return h ? h->launches : 0; }
+int64_t mppi_launch_count(const mppi_handle_t* h) {
+  if (!h) return 0;
+  int64_t n = h->launches;
+  for (const mppi_handle* s : h->subs) n += s->launches;
+  return n;
+}
 
 // MvNormal(zeros(m), Sigma) (setup.jl:57,77) throws unless Sigma is symmetric positive definite; the Cholesky factor
 // build_params takes must exist: s00 > 0, s11 - s10^2 / s00 > 0, s01 == s10.
@@ -95,6 +112,13 @@ static int validate(const mppi_config_t* c, std::string* why) {
   if (c->strict_math != 0 && c->strict_math != 1) { *why = "strict_math must be 0 or 1"; return MPPI_EINVAL; }
   if (c->strict_math && (c->precision != MPPI_FP32 || c->planner != MPPI_PLANNER_MPPI || c->B != 1)) { *why = "strict_math is the FP32 verification flavour of a single-instance MPPI step"; return MPPI_EINVAL; }
   if (c->n_gpus < 0 || c->n_gpus > MPPI_MAX_GPUS) { *why = "n_gpus must be in 0..8"; return MPPI_EINVAL; }
+  if (c->n_gpus >= 2) {
+    if (c->B != 1 || c->planner != MPPI_PLANNER_MPPI) { *why = "n_gpus > 1 shards the samples of ONE MPPI instance (B = 1, MPPI planner)"; return MPPI_EINVAL; }
+    if (c->k_offset != 0 || (c->K_local != 0 && c->K_local != c->K)) { *why = "n_gpus > 1: the handle owns all K samples (k_offset = 0, K_local = 0)"; return MPPI_EINVAL; }
+    if (c->K < c->n_gpus) { *why = "n_gpus > 1 needs at least one sample per GPU"; return MPPI_EINVAL; }
+    for (int g = 0; g < c->n_gpus; ++g)
+      if (c->device_ids[g] < 0) { *why = "device_ids must be CUDA device ordinals"; return MPPI_EINVAL; }
+  }
   const int Kl = c->K_local > 0 ? c->K_local : c->K;
   if (c->k_offset < 0 || c->k_offset + Kl > c->K) { *why = "sample shard [k_offset, k_offset+K_local) must lie inside [0, K)"; return MPPI_EINVAL; }
   if (!sigma_ok(c->Sigma)) { *why = "Sigma must be symmetric positive definite"; return MPPI_EINVAL; }
@@ -106,12 +130,14 @@ static int validate(const mppi_config_t* c, std::string* why) {
 
 int32_t mppi_destroy(mppi_handle_t* h) {
   if (!h) return MPPI_EINVAL;
+  for (mppi_handle* s : h->subs) { s->subs.clear(); mppi_destroy(s); }
+  h->subs.clear();
   cudaSetDevice(h->cfg.device);
   if (h->stream) cudaStreamSynchronize(h->stream);
   drop_graphs(h);
   if (h->comm && nccl_api().CommDestroy) nccl_api().CommDestroy(h->comm);
   for (int g = 0; g < 8; ++g)
-    if (h->peer_ptr[g] && h->peer_ptr[g] != h->d_window) cudaIpcCloseMemHandle(h->peer_ptr[g]);
+    if (h->peers_ipc && h->peer_ptr[g] && h->peer_ptr[g] != h->d_window) cudaIpcCloseMemHandle(h->peer_ptr[g]);
   if (h->d_window) cudaFree(h->d_window);
   if (h->d_peers) cudaFree(h->d_peers);
   void* dev[] = {h->d_in, h->d_eps, h->d_costs, h->d_flags, h->d_scratch, h->d_scratch_tmpl, h->d_iter, h->d_Spart,
@@ -238,12 +264,81 @@ static int create_impl(mppi_handle* h) {
   return MPPI_OK;
 }
 
+// ONE handle, ONE host thread, G GPUs (cfg.n_gpus, cfg.device_ids): the reference's caller is a single Julia task
+// (OptimalControl/MPPI/main.jl:55-83), so a drop-in that needs one process per GPU would leave it on one GPU.  Rank g owns the
+// contiguous samples shard_range(K, g, G) on device_ids[g]; every member is an ordinary sharded handle whose exchange window is
+// a plain device allocation reachable from the other GPUs through peer access (no CUDA IPC inside one process); the step
+// launches all members' graphs before it waits for any (the in-kernel all-gather spins for its peers).  The same ordinal
+// may appear more than once in device_ids: the shards then share that GPU on separate streams (logical shards; tests).
+static int create_multi(const mppi_config_t* cfg, mppi_handle_t** out) {
+  const int G = cfg->n_gpus;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess) return fail(nullptr, MPPI_ECUDA, "cudaGetDeviceCount failed");
+  for (int g = 0; g < G; ++g)
+    if (cfg->device_ids[g] >= ndev) return fail(nullptr, MPPI_EINVAL, "device_ids: device ordinal out of range");
+  std::vector<mppi_handle*> hs;
+  auto bail = [&](int rc, const std::string& why) {
+    create_error() = why;
+    for (mppi_handle* x : hs) mppi_destroy(x);
+    return rc;
+  };
+  const int base = cfg->K / G, rem = cfg->K % G;   // = motionplanning_b200/dist.py shard_range
+  for (int g = 0; g < G; ++g) {
+    mppi_handle* h = new (std::nothrow) mppi_handle();
+    if (!h) return bail(MPPI_ENOMEM, "out of host memory");
+    hs.push_back(h);
+    h->cfg = *cfg;
+    h->cfg.device = cfg->device_ids[g];
+    h->cfg.n_gpus = g == 0 ? G : 0;
+    h->cfg.k_offset = g * base + std::min(g, rem);
+    h->K_local = base + (g < rem ? 1 : 0);
+    h->cfg.K_local = h->K_local;
+    h->spmg_member = true;
+    const int rc = create_impl(h);
+    if (rc != MPPI_OK) return bail(rc, h->err);
+  }
+  for (int a = 0; a < G; ++a) {
+    for (int b = 0; b < G; ++b) {
+      const int da = hs[a]->cfg.device, db = hs[b]->cfg.device;
+      if (da == db) continue;
+      int can = 0;
+      cudaSetDevice(da);
+      if (cudaDeviceCanAccessPeer(&can, da, db) != cudaSuccess || !can) return bail(MPPI_EINVAL, "n_gpus > 1 needs peer access between the devices (NVLink / NVSwitch)");
+      const cudaError_t e = cudaDeviceEnablePeerAccess(db, 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return bail(MPPI_ECUDA, std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e));
+      cudaGetLastError();
+    }
+  }
+  for (int g = 0; g < G; ++g) {
+    mppi_handle* h = hs[g];
+    cudaSetDevice(h->cfg.device);
+    if (cudaMalloc(&h->d_window, sizeof(PeerWindow)) != cudaSuccess || cudaMemset(h->d_window, 0, sizeof(PeerWindow)) != cudaSuccess)
+      return bail(MPPI_ENOMEM, "exchange window allocation failed");
+  }
+  for (int g = 0; g < G; ++g) {
+    mppi_handle* h = hs[g];
+    cudaSetDevice(h->cfg.device);
+    for (int q = 0; q < G; ++q) h->peer_ptr[q] = hs[q]->d_window;
+    if (cudaMalloc(&h->d_peers, PEER_MAX_RANKS * sizeof(PeerWindow*)) != cudaSuccess ||
+        cudaMemcpy(h->d_peers, h->peer_ptr, PEER_MAX_RANKS * sizeof(PeerWindow*), cudaMemcpyHostToDevice) != cudaSuccess)
+      return bail(MPPI_ECUDA, "peer table upload failed");
+    h->seq_base = 0;
+    h->rank = g; h->n_ranks = G; h->p2p = true;
+  }
+  mppi_handle* root = hs[0];
+  root->subs.assign(hs.begin() + 1, hs.end());
+  cudaSetDevice(root->cfg.device);
+  *out = root;
+  return MPPI_OK;
+}
+
 int32_t mppi_create(const mppi_config_t* cfg, mppi_handle_t** out) {
   if (!cfg || !out) return fail(nullptr, MPPI_EINVAL, "null argument");
   *out = nullptr;
   std::string why;
   int rc = validate(cfg, &why);
   if (rc != MPPI_OK) return fail(nullptr, rc, why);
+  if (cfg->n_gpus >= 2) return create_multi(cfg, out);
   mppi_handle* h = new (std::nothrow) mppi_handle();
   if (!h) return fail(nullptr, MPPI_ENOMEM, "out of host memory");
   h->cfg = *cfg;
@@ -272,6 +367,7 @@ int32_t mppi_set_x0(mppi_handle_t* h, const double* x0, int32_t n) {
     snprintf(buf, sizeof buf, "Length of X0 (%d) must match number of states (%d)", n, h->cfg.n_x);
     return fail(h, MPPI_EINVAL, buf);
   }
+  FORWARD_SUBS(h, mppi_set_x0(s_, x0, n));
   int rc = quiesce_inputs(h); if (rc) return rc;
   for (int b = 0; b < h->cfg.B; ++b)
     for (int i = 0; i < n; ++i) h->h_in[size_t(b) * MPPI_MAX_NX + i] = x0[size_t(b) * n + i];
@@ -283,6 +379,7 @@ int32_t mppi_set_nominal(mppi_handle_t* h, const double* U, int32_t N, int32_t m
   H_CHECK(h);
   if (!U) return fail(h, MPPI_EINVAL, "null U");
   if (N != h->cfg.N || m != h->cfg.m) return fail(h, MPPI_EINVAL, "NominalControl must be N x numControls");
+  FORWARD_SUBS(h, mppi_set_nominal(s_, U, N, m));
   int rc = quiesce_inputs(h); if (rc) return rc;
   const size_t B = h->cfg.B, off = B * MPPI_MAX_NX, n = B * 2 * N;
   memcpy(h->h_in + off, U, n * sizeof(double));
@@ -294,6 +391,7 @@ int32_t mppi_set_sigma_lambda(mppi_handle_t* h, const double* Sigma, double lamb
   H_CHECK(h);
   if (!Sigma) return fail(h, MPPI_EINVAL, "null Sigma");
   if (!sigma_ok(Sigma) || !(lambda > 0)) return fail(h, MPPI_EINVAL, "Sigma must be symmetric positive definite and lambda > 0");
+  FORWARD_SUBS(h, mppi_set_sigma_lambda(s_, Sigma, lambda));
   int rc = quiesce(h); if (rc) return rc;
   for (int i = 0; i < 4; ++i) h->cfg.Sigma[i] = Sigma[i];
   h->cfg.lambda = lambda;
@@ -306,6 +404,7 @@ int32_t mppi_set_sigma_lambda(mppi_handle_t* h, const double* Sigma, double lamb
 int32_t mppi_set_circles(mppi_handle_t* h, const double* xyr, int32_t M_c) {
   H_CHECK(h);
   if (M_c < 0 || M_c > MPPI_MAX_CIRCLES || (M_c > 0 && !xyr)) return fail(h, MPPI_EINVAL, "circle count out of range");
+  FORWARD_SUBS(h, mppi_set_circles(s_, xyr, M_c));
   int rc = quiesce(h); if (rc) return rc;
   h->circles.assign(xyr, xyr + size_t(3) * M_c);
   rebuild_params(h);
@@ -316,6 +415,7 @@ int32_t mppi_set_circles(mppi_handle_t* h, const double* xyr, int32_t M_c) {
 int32_t mppi_set_blocks(mppi_handle_t* h, const double* blocks, int32_t M_p) {
   H_CHECK(h);
   if (M_p < 0 || M_p > MPPI_MAX_BLOCKS || (M_p > 0 && !blocks)) return fail(h, MPPI_EINVAL, "block count out of range");
+  FORWARD_SUBS(h, mppi_set_blocks(s_, blocks, M_p));
   int rc = quiesce(h); if (rc) return rc;
   h->blocks.assign(blocks, blocks + size_t(5) * M_p);
   rebuild_params(h);
@@ -326,6 +426,7 @@ int32_t mppi_set_blocks(mppi_handle_t* h, const double* blocks, int32_t M_p) {
 int32_t mppi_set_goal(mppi_handle_t* h, const double* goal2) {
   H_CHECK(h);
   if (!goal2) return fail(h, MPPI_EINVAL, "null goal");
+  FORWARD_SUBS(h, mppi_set_goal(s_, goal2));
   int rc = quiesce(h); if (rc) return rc;
   h->cfg.goal[0] = goal2[0]; h->cfg.goal[1] = goal2[1];
   rebuild_params(h);
@@ -340,6 +441,7 @@ int32_t mppi_set_reference_path(mppi_handle_t* h, const double* xy, int32_t n, d
   if (n > 0 && h->cfg.strict_math) return fail(h, MPPI_EINVAL, "the reference-path term is not part of the strict_math flavour");
   if (n > 0 && h->cfg.planner == MPPI_PLANNER_MPPI && h->cfg.noise_mode != MPPI_NOISE_PHILOX)
     return fail(h, MPPI_EINVAL, "a reference path needs PHILOX noise (the tracking rollout is not built for supplied noise)");
+  FORWARD_SUBS(h, mppi_set_reference_path(s_, xy, n, weight, window));
   int rc = quiesce(h); if (rc) return rc;
   h->ref_path.assign(xy, xy + size_t(2) * n);
   h->ref_w = n > 0 ? weight : 0.0;

@@ -84,6 +84,7 @@ constexpr int PEER_MAX_RANKS = 8;
 constexpr int PEER_PLEN = 8 + 2 * MPPI_MAX_N;   // PART_HDR + 2 N at the largest horizon
 struct PeerWindow {
   uint4 line[2][PEER_MAX_RANKS][PEER_PLEN];
+  uint4 cnt[2][PEER_MAX_RANKS];   // feasible-sample counts of all ranks (cross-GPU feasibility cut-off, cutoff_kernel), same protocol
   unsigned long long timeout;   // set to the step number when a wait gave up
 };
 __device__ __forceinline__ void ll_store(uint4* dst, double v, uint32_t flag) {

@@ -116,6 +116,11 @@ struct mppi_handle {
   mppi::PeerWindow* peer_ptr[8] = {nullptr};     // all ranks' windows as seen from this device
   mppi::PeerWindow** d_peers = nullptr;          // device copy of peer_ptr
   bool p2p = false;                              // exchange in-kernel over peer memory instead of NCCL
+  bool peers_ipc = false;                        // peer_ptr[] hold CUDA-IPC mappings (mppi_peer_init) rather than plain pointers of this process
+  // single-process multi-GPU (cfg.n_gpus >= 2; the reference's caller is ONE Julia task, main.jl:55-83): this handle is rank 0
+  // and drives the other ranks' handles from the caller's thread.  Members take the FULL eps tensor [N][K][m] in SUPPLIED mode.
+  std::vector<mppi_handle*> subs;                // ranks 1..G-1 (empty on ordinary handles and on the members themselves)
+  bool spmg_member = false;                      // rank 0..G-1 of a single-process group
   unsigned long long seq_base = 0;               // device step counter at mppi_peer_init
   // profiling
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // step begin | rollout end | update end | finalize end | step end | inputs staged

@@ -411,8 +411,33 @@ __global__ void __launch_bounds__(CUTOFF_BS) cutoff_kernel(const __grid_constant
     __syncthreads();
   }
   const int incl = s_cnt[t], excl = incl - cnt;
-  const int target = p.feasibility_count + 1;   // loop exits once FeasibilityCount > feasibility_count
-  if (excl < target && target <= incl) {
+  // Sample-sharded step (B == 1, peer exchange): the reference's loop walks the samples in GLOBAL order (MPPIUtils.jl:175,185), so
+  // this rank's cut index depends on how many feasible samples the LOWER ranks hold.  One all-gather of the per-rank feasible
+  // counts over the peer windows (LL lines, flag = step number, as in finalize's exchange) gives every rank its local target:
+  // ranks wholly before the crossing keep all their samples, the crossing rank cuts, ranks behind it contribute nothing.
+  int before = 0;
+  if (buf.n_ranks > 1 && buf.peers != nullptr) {
+    __shared__ int s_rank_cnt[PEER_MAX_RANKS];
+    const int G = buf.n_ranks, me = buf.rank;
+    const unsigned long long step = *buf.seq - buf.seq_base + 1ull;
+    const int par = int(step & 1ull);
+    const uint32_t flag = uint32_t(step);
+    if (t < G) {
+      ll_store(&buf.peers[t]->cnt[par][me], double(s_cnt[CUTOFF_BS - 1]), flag);
+      const unsigned long long t0 = globaltimer_ns();
+      double v = 0.0;
+      while (!ll_try_load(&buf.peers[me]->cnt[par][t], flag, &v)) {
+        if (globaltimer_ns() - t0 > 2000000000ull) { buf.peers[me]->timeout = step; break; }   // finalize's exchange reports the failure
+      }
+      s_rank_cnt[t] = int(v);
+    }
+    __syncthreads();
+    for (int g = 0; g < me; ++g) before += s_rank_cnt[g];
+  }
+  const int target = p.feasibility_count + 1 - before;   // loop exits once FeasibilityCount > feasibility_count
+  if (target <= 0) {
+    if (t == 0) { s_keff = 0; s_feas = 0; }   // the cut fell on a lower rank
+  } else if (excl < target && target <= incl) {
     int seen = excl;
     for (int k = k0; k < k1; ++k) {
       seen += fl[k] & MPPI_FLAG_FEASIBLE;

@@ -464,33 +464,46 @@ inline int wait_step(mppi_handle* h, bool flag_ok) {
   return MPPI_OK;
 }
 
+// Capture + instantiate + upload the graph of variant `v` if this handle does not hold it yet.  Split from run_variant because
+// a single-process multi-GPU step must do ALL host-side preparation for ALL members before the first member is launched:
+// a member's step kernel spins for its peers' partials, and capture / instantiation / first-launch upload of a later member can
+// block on device activity (seen: 2 s exchange time-outs when a new variant was captured with earlier members already spinning).
+inline bool uses_graph(const mppi_handle* h) { return h->cfg.use_cuda_graph && h->profiling != 1; }
+inline int graph_key(const mppi_handle* h, int v) { return h->profiling == 2 ? (v | (1 << 24)) : v; }   // graphs whose kernels trace %globaltimer are cached separately
+inline int ensure_graph(mppi_handle* h, int v) {
+  if (!uses_graph(h)) return MPPI_OK;
+  v = graph_key(h, v);
+  if (h->graphs.find(v) != h->graphs.end()) return MPPI_OK;
+  cudaGraph_t g = nullptr;
+  const int64_t before = h->launches;
+  MPPI_CUDA(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+  int rc = enqueue(h, v & V_ENQ_MASK, 0);
+  cudaError_t e = cudaStreamEndCapture(h->stream, &g);
+  h->launches = before;
+  if (rc != MPPI_OK) { if (g) cudaGraphDestroy(g); return rc; }
+  if (e != cudaSuccess) { h->err = std::string("cudaStreamEndCapture: ") + cudaGetErrorString(e); return MPPI_ECUDA; }
+  cudaGraphExec_t ex = nullptr;
+  e = cudaGraphInstantiate(&ex, g, 0);
+  cudaGraphDestroy(g);
+  if (e != cudaSuccess) { h->err = std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e); return MPPI_ECUDA; }
+  h->graphs.emplace(v, ex);
+  if (h->spmg_member) {   // pay the first-launch upload now, with no member spinning yet
+    MPPI_CUDA(h, cudaGraphUpload(ex, h->stream));
+    MPPI_CUDA(h, cudaStreamSynchronize(h->stream));
+  }
+  return MPPI_OK;
+}
+
 // run a variant: graph replay (captured on first use) or eager when profiling / graphs are off
 inline int run_variant(mppi_handle* h, int v) {
-  const bool use_graph = h->cfg.use_cuda_graph && h->profiling != 1;
-  if (!use_graph) {
+  if (!uses_graph(h)) {
     h->in_flight = h->inputs_busy = true;
     if (v & (V_COMBINE | V_FUSED_FINAL | V_XFINAL)) h->seq_launched++;
     h->noise_ready = (v & V_PREGEN) != 0;
     return enqueue(h, v & V_ENQ_MASK, h->profiling ? 1 : 0);
   }
-  const bool inner = false;
-  if (h->profiling == 2) v |= 1 << 24;   // graphs whose kernels trace %globaltimer are cached separately
-  auto it = h->graphs.find(v);
-  if (it == h->graphs.end()) {
-    cudaGraph_t g = nullptr;
-    const int64_t before = h->launches;
-    MPPI_CUDA(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
-    int rc = enqueue(h, v & V_ENQ_MASK, inner ? 2 : 0);
-    cudaError_t e = cudaStreamEndCapture(h->stream, &g);
-    h->launches = before;
-    if (rc != MPPI_OK) { if (g) cudaGraphDestroy(g); return rc; }
-    if (e != cudaSuccess) { h->err = std::string("cudaStreamEndCapture: ") + cudaGetErrorString(e); return MPPI_ECUDA; }
-    cudaGraphExec_t ex = nullptr;
-    e = cudaGraphInstantiate(&ex, g, 0);
-    cudaGraphDestroy(g);
-    if (e != cudaSuccess) { h->err = std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e); return MPPI_ECUDA; }
-    it = h->graphs.emplace(v, ex).first;
-  }
+  { const int rc = ensure_graph(h, v); if (rc != MPPI_OK) return rc; }
+  auto it = h->graphs.find(graph_key(h, v));
   // bracket the replay with events on the launching stream so callers can read the
   // device time of the whole step (mppi_get_timings()[3]) without a profiler
   MPPI_CUDA(h, cudaEventRecord(h->ev[0], h->stream));

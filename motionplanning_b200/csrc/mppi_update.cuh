@@ -461,7 +461,8 @@ __device__ __forceinline__ void finalize_block(const StaticParams<R>& p, const B
     double eta = 0.0, rollouts = 0.0, feas = 0.0;
     for (int g = 0; g < G; ++g) {
       const double* pg = gat + g * gstride + b * plen;
-      const double sc_g = (G == 1) ? 1.0 : exp(-(pg[PART_RHO] - rho) / double(p.lambda));
+      // a rank whose samples all lie behind the feasibility cut-off holds no sample: rho = NaN, eta = 0, S = 0
+      const double sc_g = (G == 1) ? 1.0 : ((pg[PART_RHO] == pg[PART_RHO]) ? exp(-(pg[PART_RHO] - rho) / double(p.lambda)) : 0.0);
       s_scale[g] = sc_g;
       eta += pg[PART_ETA] * sc_g;
       rollouts += pg[PART_ROLLOUTS];

@@ -137,6 +137,9 @@ class MPPISearcher:  # types.jl:46-50
 
     @property
     def K_local(self):
+        """Samples this handle exposes (costs, flags, noise): its shard, or all K for a single-process multi-GPU handle."""
+        if self._cfg.n_gpus > 1:
+            return self._cfg.K
         return self._cfg.K_local if self._cfg.K_local > 0 else self._cfg.K
 
     def _costs(self):

@@ -72,3 +72,29 @@ def test_product_never_touches_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".inc", ".h")) or f == "Makefile":
                 txt = open(os.path.join(d, f), errors="ignore").read()
                 assert "oracle_lib" not in txt and "libmppi_oracle" not in txt and "oracle/" not in txt, os.path.join(d, f)
+
+
+def test_julia_shim_mirrors_the_config_struct_field_by_field():
+    """julia/MPPIB200.jl cannot be executed here (no julia): at least its isbits mirror of mppi_config_t must list the
+    same fields, in the same order, with the same widths as the ctypes mirror, which IS checked against the library."""
+    import re
+
+    src = open(os.path.join(ROOT, "julia", "MPPIB200.jl")).read()
+    body = src[src.index("struct Config"):]
+    body = body[:body.index("\nend")]
+    fields = []
+    for line in body.splitlines()[1:]:
+        for part in line.split("#")[0].split(";"):
+            mm = re.match(r"\s*(\w+)::(.+?)\s*$", part)
+            if mm:
+                fields.append((mm.group(1), mm.group(2)))
+    size = {"UInt32": 4, "Int32": 4, "UInt64": 8, "Float64": 8}
+
+    def width(t):
+        mm = re.match(r"NTuple\{(\d+),(\w+)\}", t)
+        return int(mm.group(1)) * size[mm.group(2)] if mm else size[t]
+
+    ct = [(n, C.sizeof(t)) for n, t in capi.Config._fields_]
+    jl = [("lambda_" if n == "lambda" else n, width(t)) for n, t in fields]
+    assert jl == ct
+    assert sum(w for _, w in jl) <= C.sizeof(capi.Config)

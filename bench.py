@@ -267,7 +267,7 @@ def parity_across_ranks(m, mdist, args, kw, circles, blocks, exchange, rank, wor
         mdist.init_library_comm(sh)
     info = sh.plan_info()
     kw_ref = dict(kw, k_offset=0, K_local=0)
-    kw_ref["rollout_variant"] = 5 if info["scan"] else (2 if info["packed"] else 1)
+    kw_ref["rollout_variant"] = 5 if info["scan"] else ({2: 6, 1: 2}.get(info["packed"], 1))   # 6 = two-stage warp pipeline, 2 = packed sequential
     kw_ref["noise_policy"] = 1 if info["pregen"] else 2
     ref = m.defineMPPI(*args, **kw_ref)
     if circles:
@@ -459,6 +459,7 @@ def run_ours(a, rank, world, local_rank):
     # ---- the same kernels inside the replayed graph: %globaltimer first-block-in / last-block-out spans
     #      (mppi_set_profiling(2)); free of the launch and event gaps an eager bracket includes ----
     g_us = None
+    wall_tests = None
     if not batched:
         spans = []
         for i in range(14):
@@ -467,6 +468,7 @@ def run_ours(a, rank, world, local_rank):
             mppi.step_async(adopt=False)
             mppi.sync()
             c = mppi.phase_clocks()
+            wall_tests = c[7]
             if i >= 2:
                 def span(j):
                     return (c[9 + 2 * j] - c[8 + 2 * j]) * 1e-3 if (c[9 + 2 * j] > 0 and c[8 + 2 * j] < 2 ** 63) else 0.0
@@ -484,6 +486,13 @@ def run_ours(a, rank, world, local_rank):
     eps_bytes = local_units * 2 * 4
     upd_bytes = eps_bytes + kl * B * 4 + N * 2 * 4 * B
     traffic = NCU_TRAFFIC.get((a.config, a.walls or 0), (None, None)) if world == 1 else (None, None)
+    # share of the rectangle (SAT) tests the warp-voted broad phase left standing, counted by the kernel itself in the traced
+    # steps (mppi_get_phase_clocks()[7]); the algorithmic flop count F credits every wall at every step, F_exec only those run
+    sat_frac = F_exec = None
+    if blocks and wall_tests is not None:
+        warps = -(-kl // (32 * (2 if info["packed"] else 1)))
+        sat_frac = wall_tests / float(warps * N * len(blocks))
+        F_exec = F - 102 * len(blocks) * (1.0 - sat_frac)
 
     line = None
     if rank == 0:
@@ -495,7 +504,9 @@ def run_ours(a, rank, world, local_rank):
             "method": {
                 "K_per_gpu": kl, "walls": len(blocks), "circles": len(circles),
                 "step": ("scan-form fused kernel: horizon-parallel rollout + cost + online softmin + weighted update, tail (fold, exchange, "
-                         "combine, nominal rollout) in its last CTA" if fused else "rollout_kernel -> update_kernel -> finalize_kernel"),
+                         "combine, nominal rollout) in its last CTA" if fused else
+                         ("rollout_pipe_kernel (two-stage warp pipeline: producer / consumer warps per sample pair) -> update_kernel -> finalize_kernel"
+                          if info["packed"] == 2 else "rollout_kernel -> update_kernel -> finalize_kernel")),
                 "noise": ("philox4x32-10 on the device, one tensor per step inside the timed region: noise_kernel draws the NEXT iteration's tensor "
                           "behind the step, the rollout reads it back" if info["pregen"] else "philox4x32-10 inside the rollout kernel"),
                 "parallelism": ((f"samples sharded x{world}, softmin all-gather inside the step kernel over NVLink peer memory"
@@ -523,12 +534,18 @@ def run_ours(a, rank, world, local_rank):
                 "rollout_start_to_finalize_end": float(g_us[3]),
                 "noise_next_iteration": float(g_us[4]), "rollout_start_to_last_kernel_end": float(g_us[5]),
                 "source": "%globaltimer spans written by the kernels themselves inside the replayed graph (mppi_set_profiling(2))"},
-            "roofline": {"kernel": "scan_rollout_kernel (rollout + cost + softmin + weighted update)" if fused else "rollout_kernel",
+            "roofline": {"kernel": "scan_rollout_kernel (rollout + cost + softmin + weighted update)" if fused else ("rollout_pipe_kernel" if info["packed"] == 2 else "rollout_kernel"),
                          "bound": "fp32", "achieved": roll_tflops, "peak": fp32_peak,
-                         "unit": "TFLOP/s", "frac": roll_tflops / fp32_peak if fp32_peak else None,
+                         "unit": "TFLOP/s",
+                         # wall scenes: `frac` counts only the rectangle tests the kernel actually ran (sat_exact_fraction, counted by the
+                         # kernel); the figure that credits every wall at every step is kept as frac_algorithmic_unculled
+                         "frac": (roll_tflops / fp32_peak if F_exec is None else local_units * F_exec / (k_us[0] * 1e-6) / 1e12 / fp32_peak) if fp32_peak else None,
+                         "frac_algorithmic_unculled": roll_tflops / fp32_peak if fp32_peak else None,
                          "traffic": traffic[0], "traffic_source": "profiles/r02_ncu_*.md (ncu --set full, per launch)",
                          "flop_per_sample_step": F, "algorithmic_flop_per_launch": local_units * F,
-                         "frac_in_graph": None if g_us is None or not fp32_peak or g_us[0] <= 0 else local_units * F / (g_us[0] * 1e-6) / 1e12 / fp32_peak,
+                         "sat_exact_fraction": sat_frac, "executed_flop_per_sample_step": F_exec,
+
+                         "frac_in_graph": None if g_us is None or not fp32_peak or g_us[0] <= 0 else local_units * (F if F_exec is None else F_exec) / (g_us[0] * 1e-6) / 1e12 / fp32_peak,
                          "peak_source": "FFMA-chain probe measured in this run (mppi_measure_fp32_peak)",
                          "hbm_view": {"algorithmic_bytes": eps_bytes + kl * B * 5, "gbs": (eps_bytes + kl * B * 5) / (k_us[0] * 1e-6) / 1e9,
                                       "frac_of_measured_peak": (eps_bytes + kl * B * 5) / (k_us[0] * 1e-6) / 1e9 / peaks["hbm_gbs"]}

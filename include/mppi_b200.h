@@ -95,8 +95,10 @@ typedef struct mppi_config {
   int32_t K_local;           /* samples owned by this handle (0 => K) */
   int32_t rollout_variant;   /* 0 auto | 1 one sample per thread | 2 two samples per thread (packed FP32x2; FP32 and
                               * even K_local only) | 3, 4 = 1, 2 with the Philox noise always drawn inside the
-                              * rollout.  0-2 pre-generate the next iteration's noise beside finalize whenever the
-                              * step is a single-instance Philox MPPI step.
+                              * rollout | 5 scan-form fused step | 6 two-stage warp pipeline (kinematic model, packed; what
+                              * auto picks wherever it packs and the scene has circles only).  0-2, 5, 6 pre-generate the
+                              * next iteration's noise beside finalize whenever the step is a single-instance Philox MPPI
+                              * step.
                               * Environment MPPI_ROLLOUT_VARIANT overrides; MPPI_PREGEN=0 disables pre-generation. */
   int32_t strict_math;       /* FP32 only.  1: the K-sample rollout runs the reference's operation sequence in IEEE
                               * round-to-nearest arithmetic without fused multiply-add and with the elementary
@@ -289,7 +291,9 @@ int32_t mppi_get_timings(mppi_handle_t* h, float us[4]);
 int32_t mppi_get_stream(mppi_handle_t* h, void** stream);
 /* SM-clock stamps (clock64) at the phase boundaries of the last finalize kernel, instance 0:
  * [0] entry, [1] partials reduced, [2] ranks combined, [3] U_new ready, [4] nominal state
- * recurrence done, [5] states costed, [6] result written.  Diagnostics only. */
+ * recurrence done, [5] states costed, [6] result written.  [7] (profiling mode 2, scenes with walls): number of
+ * (warp-step, wall) pairs of the last rollout that ran the EXACT rectangle test, i.e. that the warp-voted broad
+ * phase did not cull; divided by warps x N x M_p it is the share of the SAT work actually executed.  Diagnostics only. */
 int32_t mppi_get_phase_clocks(mppi_handle_t* h, uint64_t clocks[16]);
 /* per-kernel timing: 0 off; 1 eager launches bracketed by CUDA events (no graph replay);
  * 2 graph replay in which every kernel stamps %globaltimer (ns) at its first CTA's start and last
@@ -299,7 +303,7 @@ int32_t mppi_set_profiling(mppi_handle_t* h, int32_t on);
 /* which kernels the next single-instance step of this handle runs (diagnostics, tests, bench):
  * [0] 1 = scan-form fused step (rollout + softmin + update + tail in one kernel), 0 = rollout / update / finalize kernels
  * [1] 1 = the next iteration's Philox noise is pre-generated behind the step ("latency" policy)
- * [2] 1 = packed FP32x2 sequential rollout   [3] CTAs of the scan kernel   [4] update ksplit   [5] update jsplit
+ * [2] 1 = packed FP32x2 sequential rollout, 2 = packed two-stage warp pipeline (mppi_pipe.cuh)   [3] CTAs of the scan kernel   [4] update ksplit   [5] update jsplit
  * [6] strict_math   [7] GPUs driven by this handle */
 int32_t mppi_get_plan_info(mppi_handle_t* h, int32_t info[8]);
 /* number of kernels the library launched on this handle so far */

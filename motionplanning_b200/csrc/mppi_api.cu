@@ -107,7 +107,7 @@ static int validate(const mppi_config_t* c, std::string* why) {
   if (c->precision != MPPI_FP32 && c->precision != MPPI_FP64) { *why = "unknown precision"; return MPPI_EINVAL; }
   if (c->noise_mode != MPPI_NOISE_SUPPLIED && c->noise_mode != MPPI_NOISE_PHILOX) { *why = "unknown noise_mode"; return MPPI_EINVAL; }
   if (c->planner != MPPI_PLANNER_MPPI && c->planner != MPPI_PLANNER_DWA) { *why = "unknown planner"; return MPPI_EINVAL; }
-  if (c->rollout_variant < 0 || c->rollout_variant > 5) { *why = "rollout_variant must be 0..5"; return MPPI_EINVAL; }
+  if (c->rollout_variant < 0 || c->rollout_variant > 6) { *why = "rollout_variant must be 0..6"; return MPPI_EINVAL; }
   if (c->noise_policy < 0 || c->noise_policy > 2) { *why = "noise_policy must be 0 (auto), 1 (latency) or 2 (throughput)"; return MPPI_EINVAL; }
   if (c->strict_math != 0 && c->strict_math != 1) { *why = "strict_math must be 0 or 1"; return MPPI_EINVAL; }
   if (c->strict_math && (c->precision != MPPI_FP32 || c->planner != MPPI_PLANNER_MPPI || c->B != 1)) { *why = "strict_math is the FP32 verification flavour of a single-instance MPPI step"; return MPPI_EINVAL; }
@@ -206,7 +206,14 @@ static int create_impl(mppi_handle* h) {
     // per-lane Philox / Box-Muller work out of the loop it pays from 65,536 samples (tools/sweep_pregen.py)
     const long long samples = (long long)h->K_local * c.B;
     const long long pack_min = h->pregen_ok ? MPPI_PACK_MIN_SAMPLES_PREGEN : MPPI_PACK_MIN_SAMPLES;
-    h->packed = !c.strict_math && can_pack && (variant == 2 || variant == 4 || (variant == 0 && samples >= pack_min));
+    h->packed = !c.strict_math && can_pack && (variant == 2 || variant == 4 || variant == 6 || (variant == 0 && samples >= pack_min));
+    // two-stage warp pipeline (mppi_pipe.cuh): packed FP32 kinematic rollout that READS eps; obstacle kind / reference path are
+    // checked per step (pipe_eligible).  auto uses it wherever it would have used the packed sequential kernel; 2 keeps the latter.
+    h->pipe = h->packed && (variant == 0 || variant == 6) && c.model == MPPI_MODEL_KINEMATIC5 && c.planner == MPPI_PLANNER_MPPI &&
+              (c.noise_mode == MPPI_NOISE_SUPPLIED || h->pregen_ok) && size_t(c.N) * PIPE_SAMPLES * 8 <= size_t(PIPE_SLAB_MAX) &&
+              c.N <= EPS_GROUP * EPS_MAX_GROUPS;
+    if (const char* e = getenv("MPPI_PIPE")) h->pipe = h->pipe && atoi(e) != 0;
+    if (variant == 6 && !h->pipe) { h->err = "rollout_variant 6 (two-stage warp pipeline) needs FP32, even K_local, the kinematic model, the MPPI planner, eps read from memory (SUPPLIED or pre-generated noise) and N <= 56"; return MPPI_EINVAL; }
   }
   MPPI_CUDA(h, cudaMalloc(&h->d_in, B * (MPPI_MAX_NX + 2 * N) * sizeof(double)));
   if (c.planner == MPPI_PLANNER_MPPI) MPPI_CUDA(h, cudaMalloc(&h->d_eps, B * N * K * 2 * rs));

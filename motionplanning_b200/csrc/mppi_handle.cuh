@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "mppi_scan.cuh"
+#include "mppi_pipe.cuh"
 #include "mppi_strict.cuh"
 #include "mppi_plant.cuh"
 
@@ -55,6 +56,7 @@ struct mppi_handle {
   int K_local = 0, ksplit = 1, jsplit = 1, plen = 0;   // update_kernel grid = (ksplit, jsplit, B)
   bool cutoff = false;
   bool packed = false;   // rollout carries two samples per thread as f32x2 (FP32, even K_local)
+  bool pipe = false;     // ... and, where the step qualifies (pipe_eligible), as the two-stage warp pipeline of mppi_pipe.cuh
   std::vector<double> circles, blocks;   // host copies (3 x Mc, 5 x Mp col-major)
   // device
   double* d_in = nullptr;        // [B][8] x0 then [B][2N] U  (d_x0 = d_in, d_U = d_in + 8B)

@@ -94,6 +94,7 @@ __device__ __forceinline__ void rollout_horizon(const StaticParams<typename Math
   const int N = p.N;
   const HotParams<S, Model::NX> hp = *sHot;   // smem -> registers (unused fields are dead)
   const bool walls = p.n_blocks > 0;
+  unsigned long long* const wall_stat = buf.trace ? buf.dbg + 7 : nullptr;   // profiling mode 2: exact wall tests are counted
   const size_t estride = size_t(p.K_local);
   S2* eps = reinterpret_cast<S2*>(buf.eps) + size_t(b) * N * estride + k;
   const S4* nu_p = reinterpret_cast<const S4*>(sU);
@@ -127,7 +128,7 @@ __device__ __forceinline__ void rollout_horizon(const StaticParams<typename Math
     veh.step(hp, u0, u1);                          // Rungekutta2 (:76-90)
     if (NQ >= 0) acc.hits += circle_hits_regs<V, (NQ > 0 ? NQ : 0)>(hp, veh.s[0], veh.s[1]);   // x_{j+1}: ObstacleEvaluation
     else acc.hits += circle_hits<V>(p, veh.s[0], veh.s[1]);
-    if (walls) acc.hits += block_hits<V>(hp, hp.blk_all, sBlk, p.n_blocks, veh.s[0], veh.s[1], veh.sn, veh.cs);
+    if (walls) acc.hits += block_hits<V>(hp, hp.blk_all, sBlk, p.n_blocks, veh.s[0], veh.s[1], veh.sn, veh.cs, wall_stat);
     acc.viol += bound_violation<V, Model::NX>(hp, veh.s);                 // BoundEvaluation
   };
   if (SRC == SRC_PHILOX) {

@@ -200,9 +200,11 @@ template <> __device__ __forceinline__ int hits_from_free<double>(int tested, in
 // the kernel parameter itself, or — in the rollout kernel — a shared-memory copy read as two
 // broadcast 128-bit loads per wall (a parameter table indexed by a loop counter costs an LDC
 // with register index per field).  V carries veh_off / veh_hl / veh_hw (StaticParams or HotParams).
+// `stat` (diagnostics, profiling mode 2 only, nullptr otherwise): incremented by the number of walls a warp-step tests EXACTLY,
+// so that a benchmark can report which share of the rectangle tests the broad phase left standing (mppi_get_phase_clocks()[7]).
 template <class V, class P>
 __device__ __forceinline__ typename Math<V>::Count block_hits(const P& veh, const typename Math<V>::S* all4, const typename Math<V>::S* tbl,
-                                                              int n_blocks, V x, V y, V sn, V cs) {
+                                                              int n_blocks, V x, V y, V sn, V cs, unsigned long long* stat = nullptr) {
   using M = Math<V>;
   using S = typename M::S;
   using S4 = typename Vec4<S>::type;
@@ -227,6 +229,8 @@ __device__ __forceinline__ typename Math<V>::Count block_hits(const P& veh, cons
   const S4* t4 = reinterpret_cast<const S4*>(tbl);
   typename M::Count freec = hits;
   int tested = 0;
+  const bool count_lane = stat != nullptr && int(threadIdx.x & 31) == __ffs(mask) - 1;
+  if (count_lane && n_blocks <= 4) atomicAdd(stat, (unsigned long long)n_blocks);
   if (n_blocks <= 4) {   // few walls: straight loop the compiler can unroll and software-pipeline
 #pragma unroll 4
     for (int b = 0; b < n_blocks; ++b) {
@@ -241,6 +245,7 @@ __device__ __forceinline__ typename Math<V>::Count block_hits(const P& veh, cons
       if (__ballot_sync(mask, M::any(M::lt(M::fma(dx, dx, dy * dy), V(w1.z)))) == 0u) continue;   // provably free for every lane
       freec += exact(w0, w1, dx, dy);
       ++tested;
+      if (count_lane) atomicAdd(stat, 1ull);
     }
   }
   return hits_from_free<V>(tested, freec);   // hits = walls tested - walls found free

@@ -1,0 +1,244 @@
+// mppi_pipe.cuh — the K-sample rollout of the kinematic bicycle as a two-stage warp pipeline.
+//
+// Why: at the headline size (K = 65,536, N = 50) the one-thread-per-sample rollout leaves 1.7 warps on every scheduler
+// and each of them walks one dependent instruction stream: issue-active 47 %, top stall `wait` (profiles/r02_ncu_cfg2_*).
+// The samples alone do not hold enough parallelism for 148 SMs; the horizon does, but a scan-form rollout pays for it with
+// 2.4x the instructions (mppi_scan.cuh: 210 issue slots per sample-step against 87).  The model
+// (OptimalControl/Parking/src/VehicleModel.jl:14-18 under the Heun step of MPPIUtils.jl:76-90) is triangular:
+//   stage A   (sa, ux) are running sums of the clamped controls; tan(sa)/L, the control cost (MPPIUtils.jl:45), the effort
+//             and sa^2 stage terms (vehicledynamics.jl:52), the bounds of sa and ux (:135-151) need nothing else;
+//   stage B   psi, x, y integrate quantities stage A produced; sincos, the y^2 term, the circle tests (:120-132), the
+//             bounds of x, y, psi and the terminal term (:54) need stage A's (ux, tan(sa)/L) of the step and nothing else.
+// So each sample pair is walked by TWO threads in two warps: a producer running stage A over the whole horizon and a
+// consumer running stage B a few steps behind, the values in between handed over through shared memory.  Twice the warps,
+// each with half the dependent chain, no recomputation and no padding: the instruction count stays that of the sequential
+// kernel (+ one 16-byte store / load per step).
+//
+// Hand-over without extra shared memory: the block's eps slab (TMA-staged, one row of 256 samples per horizon step) is
+// consumed by stage A exactly once, 16 bytes per pair and step, and stage A's output for stage B is 16 bytes per pair and
+// step, so the producer overwrites the eps it has just read IN PLACE.  A producer warp feeds exactly one consumer warp (same
+// lanes, same addresses), so the only synchronisation is "producer warp w has finished hand-over unit g of PIPE_HAND steps": one
+// mbarrier per warp pair and unit (32 arrivals, release) that the consumer waits on (acquire).
+// Measured at cfg 2 on B200 (L2 flushed): rollout span 17.9 -> 15.3 us; per-CTA timeline: 2.5 us until the first eps rows have
+// landed, then 50 steps in 8-12 us with the schedulers at ~60 % issue (two co-resident CTAs halve each other's speed: the SM
+// is then throughput-, no longer latency-bound).  Hand-over every 4 steps and a loop body of 2 steps were the best of the
+// grid {1, 2, 4, 8} x {1, 2, 4}.
+//
+// CTA = 8 warps = 4 producer / consumer pairs over 256 samples.  Warp i and warp i + 4 form a pair and sit on the same SM
+// sub-partition (warp id mod 4), so every scheduler holds both stages and the two instruction streams interleave.
+// FP32 packed (two samples per thread, mppi_pack.cuh), circles only, eps read from memory (host-supplied or pre-generated).
+// Differences from rollout_kernel in the result: the running cost is the sum of two partial sums (stage A's and stage B's
+// terms) instead of one, i.e. a different summation order — costs agree to FP32 rounding, flags are identical.
+#pragma once
+#include "mppi_kernels.cuh"
+
+namespace mppi {
+
+constexpr int PIPE_BS = 256;
+constexpr int PIPE_PAIRS_W = 4;                       // producer / consumer warp pairs per CTA
+constexpr int PIPE_SAMPLES = PIPE_PAIRS_W * 64;       // samples per CTA (two per thread)
+constexpr int PIPE_SLAB_MAX = 112 * 1024;             // N * PIPE_SAMPLES * 8 bytes: two CTAs per SM up to N = 56
+#ifndef MPPI_PIPE_HAND
+#define MPPI_PIPE_HAND 4                              // horizon steps per producer -> consumer hand-over (divides EPS_GROUP)
+#endif
+#ifndef MPPI_PIPE_UNROLL
+#define MPPI_PIPE_UNROLL 2                            // steps per loop body: lets the scheduler overlap the MUFU chains of neighbouring steps
+#endif
+constexpr int PIPE_HAND = MPPI_PIPE_HAND;
+constexpr int PIPE_UNROLL = MPPI_PIPE_UNROLL;
+constexpr int PIPE_MAX_HANDS = EPS_GROUP * EPS_MAX_GROUPS / PIPE_HAND;
+
+struct PipeHot {
+  float CL0, CU0, CL1, CU1, w2, w3, w4, w5;
+  float dt, half_dt, inv_Lwb, pad0;
+  float XL[5], XU[5];
+  float goal0, goal1, slack, obs_pen, term_scale, pad1;
+  float circ[HOT_CIRCLES][3];
+};
+
+static_assert(sizeof(PipeHot) == (28 + 3 * HOT_CIRCLES) * 4, "PipeHot is filled field by field through a float view");
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+template <int NQ>
+__global__ void __launch_bounds__(PIPE_BS, 2)
+rollout_pipe_kernel(const __grid_constant__ StaticParams<float> p, const Buffers<float> buf) {
+  using V = f32x2;
+  using M = Math<V>;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float4* sU = reinterpret_cast<float4*>(smem_raw);                                        // [N]: u0, u1, g0, g1
+  float4* slab = reinterpret_cast<float4*>(smem_raw + ((size_t(p.N) * 16 + 127) & ~size_t(127)));   // [N][PIPE_SAMPLES / 2]: one float4 per pair and step
+  __shared__ __align__(8) uint64_t s_bar[EPS_MAX_GROUPS];                     // TMA: rows of group g have landed
+  __shared__ __align__(8) uint64_t s_prog[PIPE_PAIRS_W][PIPE_MAX_HANDS];      // producer warp w has finished hand-over unit g (PIPE_HAND steps)
+  __shared__ __align__(16) PipeHot sh;
+  __shared__ float4 s_handA[PIPE_BS / 2];                                     // producer's partial sums: stage (2 samples), violation (2 samples)
+  __shared__ unsigned long long s_key[PIPE_PAIRS_W];
+  __shared__ int s_feas[PIPE_PAIRS_W];
+  __shared__ float s_x0[8];
+
+  const int N = p.N, K = p.K_local, b = blockIdx.y;
+  const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
+  if (buf.halt && *buf.halt) return;
+  trace_begin(buf.dbg, buf.trace, 0);
+  if ((blockIdx.x | blockIdx.y | t) == 0) buf.iter[1] = buf.iter[0] + 1u;   // for noise_kernel beside finalize (V_PREGEN)
+  const int k0 = blockIdx.x * PIPE_SAMPLES;
+  const int n_here = min(PIPE_SAMPLES, K - k0);
+  const int n_groups = (N + EPS_GROUP - 1) / EPS_GROUP;
+  const uint32_t row_bytes = uint32_t(n_here) * 8u;
+  const float2* src = reinterpret_cast<const float2*>(buf.eps) + size_t(b) * N * K + k0;
+  const int n_hands = (N + PIPE_HAND - 1) / PIPE_HAND;
+  // prologue spread over the block: barrier initialisation one per thread, parameters one field per thread; the bulk copies are
+  // issued by a CONSUMER lane (thread PIPE_BS / 2), whose warp has nothing to do until its producer has finished the first steps
+  // eps does not depend on begin_kernel: the whole slab is asked for before anything else, by the first CONSUMER warp (idle
+  // until its producer has finished the first steps).  Group by group, so that group 0 lands first; within a group lane r issues
+  // row r, i.e. one instruction per group instead of one per row (50 copies issued one after another by one thread took 3 us).
+  if (wid == PIPE_PAIRS_W) {
+    if (lane < n_groups) mbar_init(&s_bar[lane], 1);
+    mbar_init_fence();
+    __syncwarp();
+    for (int g = 0; g < n_groups; ++g) {
+      const int j0 = g * EPS_GROUP, j1 = min(j0 + EPS_GROUP, N);
+      if (lane == 0) mbar_arrive_expect_tx(&s_bar[g], row_bytes * uint32_t(j1 - j0));
+      const int j = j0 + lane;
+      if (j < j1) bulk_load(slab + size_t(j) * (PIPE_SAMPLES / 2), src + size_t(j) * K, row_bytes, &s_bar[g]);
+    }
+  }
+  for (int i = t; i < PIPE_PAIRS_W * n_hands; i += PIPE_BS) mbar_init(&s_prog[i / n_hands][i % n_hands], 32);
+  {
+    float* hot = reinterpret_cast<float*>(&sh);
+    constexpr int NHOT = sizeof(PipeHot) / 4;
+    if (t >= 64 && t < 64 + NHOT) {
+      const int i = t - 64;
+      float v = 0.f;
+      if (i < 4) v = (i == 0) ? p.CL[0] : (i == 1) ? p.CU[0] : (i == 2) ? p.CL[1] : p.CU[1];
+      else if (i < 8) v = p.w[i - 2];                                         // w2, w3, w4, w5
+      else if (i < 12) v = (i == 8) ? p.dt : (i == 9) ? p.half_dt : (i == 10) ? p.inv_Lwb : 0.f;
+      else if (i < 17) v = p.XL[i - 12];
+      else if (i < 22) v = p.XU[i - 17];
+      else if (i < 28) v = (i == 22) ? p.goal[0] : (i == 23) ? p.goal[1] : (i == 24) ? p.slack : (i == 25) ? p.obs_pen : (i == 26) ? p.term_scale : 0.f;
+      else { const int o = (i - 28) / 3, c = (i - 28) % 3; const bool on = o < p.n_circles; v = on ? p.circ[o][c] : (c == 2 ? -1.f : 0.f); }   // d^2 <= -1 never holds
+      hot[i] = v;
+    }
+  }
+  pdl_wait();   // programmatic dependent of begin_kernel: x0 / U_nom are read from here on
+  const double* Ub = buf.U + size_t(b) * 2 * N;
+  for (int j = t; j < N; j += PIPE_BS) {
+    const float u0 = float(Ub[j]), u1 = float(Ub[N + j]);
+    sU[j] = make_float4(u0, u1, p.G00 * u0 + p.G01 * u1, p.G10 * u0 + p.G11 * u1);   // g_j = lambda inv(Sigma) U_nom[j] (MPPIUtils.jl:45, hoisted)
+  }
+  if (t >= 32 && t < 37) s_x0[t - 32] = float(buf.x0[size_t(b) * MPPI_MAX_NX + t - 32]);
+  __syncthreads();
+
+  const int w = wid & (PIPE_PAIRS_W - 1);                 // the pair this warp belongs to
+  const int pair = w * 32 + lane;                         // sample pair within the CTA
+  float4* row = slab + pair;
+  constexpr int RS = PIPE_SAMPLES / 2;                    // float4 per horizon row
+
+  if (wid < PIPE_PAIRS_W) {
+    // ---------------- stage A: controls, (sa, ux), tan(sa)/L, their cost terms and bounds ----------------
+    const float CL0 = sh.CL0, CU0 = sh.CU0, CL1 = sh.CL1, CU1 = sh.CU1, w2 = sh.w2, w3 = sh.w3, w4 = sh.w4;
+    const float dt = sh.dt, inv_Lwb = sh.inv_Lwb, XL3 = sh.XL[3], XU3 = sh.XU[3], XL4 = sh.XL[4], XU4 = sh.XU[4];
+    V sa = V(s_x0[4]), ux = V(s_x0[3]);
+    V stage = V(0.f), viol = V(0.f);
+#pragma unroll PIPE_UNROLL
+    for (int j = 0; j < N; ++j) {
+      if ((j % EPS_GROUP) == 0) mbar_wait(&s_bar[j / EPS_GROUP], 0);
+      const float4 e = row[size_t(j) * RS];               // eps of the pair: (e0, e1) of sample a, (e0, e1) of sample b
+      const float4 nu = sU[j];
+      const V u0 = M::fmin(M::fmax(V(nu.x) + V(e.x, e.z), V(CL0)), V(CU0));   // PushInBounds (MPPIUtils.jl:13-20)
+      const V u1 = M::fmin(M::fmax(V(nu.y) + V(e.y, e.w), V(CL1)), V(CU1));
+      stage += M::fma(V(nu.z), u0 - V(nu.x), V(nu.w) * (u1 - V(nu.y)));       // lambda U_nom' inv(Sigma) (u - U_nom) (:45)
+      stage += M::fma(V(w4), sa * sa, M::fma(V(w3), u0 * u0, V(w2) * (u1 * u1)));   // pre-step state's sa^2, effort (vehicledynamics.jl:52)
+      sa = M::fma(u0, V(dt), sa);                         // Heun with a constant derivative: x + dt (k + k) / 2
+      ux = M::fma(u1, V(dt), ux);
+      const V tn = M::tan(sa) * V(inv_Lwb);
+      viol += M::fmax(M::fmax(V(XL3) - ux, ux - V(XU3)), V(0.f));             // BoundEvaluation of the new state (:135-151)
+      viol += M::fmax(M::fmax(V(XL4) - sa, sa - V(XU4)), V(0.f));
+      row[size_t(j) * RS] = make_float4(ux.v.x, ux.v.y, tn.v.x, tn.v.y);      // in place of the eps just consumed
+      if ((j % PIPE_HAND) == PIPE_HAND - 1 && j != N - 1) mbar_arrive(&s_prog[w][j / PIPE_HAND]);
+    }
+    stage += V(w4) * (sa * sa);                           // terminal slot: VehicleDynamics(x_N, [0, 0]) (:49,:53), sa part
+    s_handA[pair] = make_float4(stage.v.x, stage.v.y, viol.v.x, viol.v.y);
+    mbar_arrive(&s_prog[w][(N - 1) / PIPE_HAND]);         // last unit + the partial sums
+    pdl_trigger();
+    return;
+  }
+
+  // ---------------- stage B: psi, x, y, their cost terms, circle tests, bounds, terminal term ----------------
+  const float dt = sh.dt, half_dt = sh.half_dt, w5 = sh.w5, inv_Lwb = sh.inv_Lwb;
+  const float XL0 = sh.XL[0], XU0 = sh.XU[0], XL1 = sh.XL[1], XU1 = sh.XU[1], XL2 = sh.XL[2], XU2 = sh.XU[2];
+  float cx[NQ > 0 ? NQ : 1], cy[NQ > 0 ? NQ : 1], cr[NQ > 0 ? NQ : 1];
+#pragma unroll
+  for (int o = 0; o < NQ; ++o) { cx[o] = sh.circ[o][0]; cy[o] = sh.circ[o][1]; cr[o] = sh.circ[o][2]; }
+  V x = V(s_x0[0]), y = V(s_x0[1]), psi = V(s_x0[2]);
+  V ux = V(s_x0[3]), tn = V(__tanf(s_x0[4]) * inv_Lwb);
+  V sn, cs;
+  M::sincos(psi, &sn, &cs);
+  const V gx0 = x - V(sh.goal0), gy0 = y - V(sh.goal1);
+  const V d0 = M::fma(gx0, gx0, gy0 * gy0);
+  V stage = V(0.f), viol = V(0.f);
+  Count2 hits{0, 0};
+#pragma unroll PIPE_UNROLL
+  for (int j = 0; j < N; ++j) {
+    if ((j % PIPE_HAND) == 0) mbar_wait(&s_prog[w][j / PIPE_HAND], 0);
+    const float4 q = row[size_t(j) * RS];
+    const V uxn = V(q.x, q.y), tnn = V(q.z, q.w);
+    stage += V(w5) * (y * y);                             // pre-step state's y^2
+    const V k1p = ux * tn;
+    const V psit = M::fma(k1p, V(dt), psi);               // predictor heading
+    V st, ct;
+    M::sincos(psit, &st, &ct);
+    x = M::fma(V(half_dt), M::fma(uxn, ct, ux * cs), x);  // corrector x + dt (k1 + k2) / 2 (MPPIUtils.jl:76-90)
+    y = M::fma(V(half_dt), M::fma(uxn, st, ux * sn), y);
+    psi = M::fma(V(half_dt), M::fma(uxn, tnn, k1p), psi);
+    ux = uxn; tn = tnn;
+    M::sincos(psi, &sn, &cs);
+#pragma unroll
+    for (int o = 0; o < NQ; ++o) {                        // ObstacleEvaluation of x_{j+1} (:120-132)
+      const V dx = x - V(cx[o]), dy = y - V(cy[o]);
+      hits += M::count(M::le(M::fma(dx, dx, dy * dy), V(cr[o])));
+    }
+    viol += M::fmax(M::fmax(V(XL0) - x, x - V(XU0)), V(0.f));
+    viol += M::fmax(M::fmax(V(XL1) - y, y - V(XU1)), V(0.f));
+    viol += M::fmax(M::fmax(V(XL2) - psi, psi - V(XU2)), V(0.f));
+  }
+  stage += V(w5) * (y * y);                               // terminal slot, y part
+  const float4 a = s_handA[pair];                         // ordered behind the producer's last arrival (waited on in the last group)
+  stage += V(a.x, a.y);
+  viol += V(a.z, a.w);
+  const V gx = x - V(sh.goal0), gy = y - V(sh.goal1);
+  const V term = M::div(M::fma(gx, gx, gy * gy), d0) * V(sh.term_scale);   // (:54)
+  const V cost = M::fma(V(sh.slack), viol, M::fma(V(sh.obs_pen), M::to_real(hits), stage)) + term;
+  unsigned long long key = ~0ull;
+  int n_feas = 0;
+  const int k = k0 + 2 * pair;
+#pragma unroll
+  for (int l = 0; l < 2; ++l) {
+    if (k + l < K) {
+      const float c = M::lane(cost, l), vl = M::lane(viol, l);
+      const int hl = M::lane(hits, l);
+      const bool feas = hl == 0 && !(vl > 0.f);
+      buf.costs[size_t(b) * K + k + l] = c;
+      buf.flags[size_t(b) * K + k + l] = uint8_t((feas ? MPPI_FLAG_FEASIBLE : 0) | (hl ? MPPI_FLAG_COLLIDED : 0) | ((vl > 0.f) ? MPPI_FLAG_OOB : 0));
+      const unsigned long long kk = make_key(c, (unsigned int)(k + l));
+      key = kk < key ? kk : key;
+      n_feas += feas ? 1 : 0;
+    }
+  }
+  key = warp_min_u64(key);
+  n_feas = warp_sum(n_feas);
+  if (lane == 0) { s_key[w] = key; s_feas[w] = n_feas; }
+  asm volatile("bar.sync 1, 128;" ::: "memory");          // the four consumer warps only: the producers have left
+  if (t == PIPE_BS / 2) {
+    int f = 0;
+#pragma unroll
+    for (int i = 0; i < PIPE_PAIRS_W; ++i) { key = s_key[i] < key ? s_key[i] : key; f += s_feas[i]; }
+    atomicMin(&buf.scratch[b].rho_key, key);
+    if (f) atomicAdd(&buf.scratch[b].feasible_count, f);
+    if (buf.trace) atomicMax(&buf.dbg[9], globaltimer_ns());
+  }
+  pdl_trigger();
+}
+
+}  // namespace mppi

@@ -118,6 +118,22 @@ inline cudaError_t launch_scan(int N, int n_circles, dim3 grid, size_t smem, cud
   return n_circles <= 3 ? launch_scan_cn<13, 3>(grid, smem, s, dependent, p, buf) : launch_scan_cn<13, 8>(grid, smem, s, dependent, p, buf);
 }
 
+// the two-stage warp pipeline (mppi_pipe.cuh) runs this step's rollout when the handle asked for it and the scene has circles only
+inline bool pipe_eligible(const mppi_handle* h) {
+  return h->pipe && h->ref_path.empty() && h->blocks.empty() && h->circles.size() / 3 <= size_t(HOT_CIRCLES);
+}
+inline cudaError_t launch_pipe(int n_circles, dim3 grid, size_t smem, cudaStream_t s, bool dependent, const StaticParams<float>& p, const Buffers<float>& buf) {
+  static unsigned long long prepared = 0;
+  if (first_on_device(prepared)) {
+    prefer_shared_carveout(rollout_pipe_kernel<3>);
+    prefer_shared_carveout(rollout_pipe_kernel<8>);
+    cudaFuncSetAttribute(rollout_pipe_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, PIPE_SLAB_MAX + 8192);
+    cudaFuncSetAttribute(rollout_pipe_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, PIPE_SLAB_MAX + 8192);
+  }
+  if (n_circles <= 3) return launch_step_kernel(rollout_pipe_kernel<3>, grid, dim3(PIPE_BS), smem, s, dependent, p, buf);
+  return launch_step_kernel(rollout_pipe_kernel<8>, grid, dim3(PIPE_BS), smem, s, dependent, p, buf);
+}
+
 template <class R, class Model, int SRC>
 int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all events, 2 = inner boundaries only (graph nodes)
   const StaticParams<R>& p = params_of<R>(h);
@@ -198,7 +214,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
     }
   }
   if ((v & V_LOCAL) && !scan_done) {
-    bool launched = pregen;
+    bool launched = pregen, piped = false;
     if constexpr (std::is_same<R, float>::value && SRC != SRC_DWA) {
       if (h->cfg.strict_math) {   // verification flavour: the reference's operation sequence in unfused IEEE FP32 (mppi_strict.cuh); reads eps
         if (SRC == SRC_PHILOX) {
@@ -212,7 +228,14 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
         launched = true;
       }
     }
-    if (pregen) {   // eps read back (the host keeps V_PREGEN off for tracking handles)
+    if constexpr (std::is_same<R, float>::value && std::is_same<Model, Kin5<float>>::value && SRC != SRC_DWA) {
+      if (!h->cfg.strict_math && (SRC == SRC_SUPPLIED || pregen) && pipe_eligible(h)) {   // two-stage warp pipeline: stage A / stage B warps per sample pair
+        const size_t smemP = ((size_t(N) * 16 + 127) & ~size_t(127)) + size_t(N) * PIPE_SAMPLES * 8;
+        MPPI_CUDA(h, launch_pipe(p.n_circles, dim3((K + PIPE_SAMPLES - 1) / PIPE_SAMPLES, B), smemP, s, pdl_in, p, buf));
+        launched = piped = true;
+      }
+    }
+    if (pregen && !piped) {   // eps read back (the host keeps V_PREGEN off for tracking handles)
       bool done = false;
       if constexpr (std::is_same<R, float>::value) {
         if (h->packed) {

@@ -202,6 +202,41 @@ def test_batched_many_instances_small_blocks_path(built, monkeypatch):
     monkeypatch.delenv("MPPI_UPDATE_JSPLIT")
 
 
+def test_batched_full_size_cfg5_spot_parity(built):
+    """BASELINE.json config 5 at its full size (4,096 instances x K = 1,024 x N = 50, FP32, Philox): 16 instances spread over
+    the batch are replayed through the FP64 oracle on the device's own noise (costs of every sample, U_new, nominal cost), and
+    size-independent properties hold for ALL instances: U_new inside [CL, CU], finite, and an instance's result does not
+    depend on its position in the batch (instances 0..3 equal those of a 4-instance handle)."""
+    B, K, N = 4096, 1024, 50
+    args, kw, circles, blocks = sc.config(4, K=K)
+    x0s = sc.jittered_x0(B)
+    Us = np.stack([warm_nominal(N, seed=b % 7) for b in range(B)], axis=2)
+    big = make(args[:3] + (x0s,) + args[4:], dict(kw, B=B), circles, blocks)
+    Uout, costs, feas = big.step_batched(x0s, Us)
+    assert np.isfinite(Uout).all() and np.isfinite(costs).all()
+    assert (Uout >= np.array(sc.CL)[None, :, None] - 1e-6).all() and (Uout <= np.array(sc.CU)[None, :, None] + 1e-6).all()
+    eps = np.empty((B, N, K, 2), dtype=np.float32)
+    big._check(big._lib.mppi_get_noise(big._h, eps.ctypes.data_as(m.mppi.C.c_void_p)))
+    allc = big.p.costs.reshape(B, K)
+    allf = big.p.flags.reshape(B, K)
+    n_guard = 0
+    for b in np.linspace(0, B - 1, 16).astype(int):
+        ref = orc.plan(orc.make_config(args, dict(kw, B=1, precision=capi.FP64)), circles, blocks, x0s[:, b], Us[:, :, b],
+                       eps[b].astype(np.float64), capi.FP64, threads=8, want_margin=True)
+        ok = ref["margins"] > GUARD
+        n_guard += int((~ok).sum())
+        assert (np.abs(allc[b] - ref["costs"]) / np.abs(ref["costs"]))[ok].max() <= FP32_TOL
+        assert np.array_equal(allf[b][ok], ref["flags"][ok])
+        assert np.abs(Uout[:, :, b] - ref["Control"]).max() <= FP32_TOL * max(1.0, np.abs(ref["Control"]).max())
+        if ref["nominal_margin"] > GUARD:
+            assert costs[b] == pytest.approx(ref["cost"], rel=FP32_TOL) and bool(feas[b]) == ref["feasible"]
+    print(f"[guard band] {n_guard} of {16 * K} samples excluded")
+    assert n_guard <= 0.02 * 16 * K
+    small = make(args[:3] + (x0s[:, :4],) + args[4:], dict(kw, B=4), circles, blocks)
+    Uo2, c2, f2 = small.step_batched(x0s[:, :4], Us[:, :, :4])
+    assert np.allclose(Uout[:, :, :4], Uo2, rtol=2e-6, atol=1e-7) and np.allclose(costs[:4], c2, rtol=1e-6) and np.array_equal(feas[:4], f2)
+
+
 def test_sample_xy_export(built):
     args, kw, circles, blocks = sc.config(0)
     kw = dict(kw, precision=capi.FP64)
@@ -376,7 +411,7 @@ def test_closed_loop_stops_at_goal_and_shift_option(built, tmp_path):
     assert g2 <= 36.0
 
 
-@pytest.mark.parametrize("cfg_idx,K,N", [(1, 65536, 50), (2, 262144, 80), (3, 131072, 100)])
+@pytest.mark.parametrize("cfg_idx,K,N", [(1, 65536, 50), (2, 262144, 80), (3, 131072, 100), (3, 1048576, 100)])
 def test_full_size_properties(built, cfg_idx, K, N):
     """BASELINE.json sizes (cfg4 at the 8-GPU per-rank shard), checked through size-independent
     properties: rho is the cost of the argmin sample and the minimum of all costs; eta equals the
@@ -393,15 +428,18 @@ def test_full_size_properties(built, cfg_idx, K, N):
     assert mppi.r.eta == pytest.approx(w.sum(), rel=2e-5)
     assert mppi.r.FeasibleTrajCount == int((flags & capi.FLAG_FEASIBLE).sum())
     assert mppi.r.RolloutCount == K + 1
-    eps = mppi.noise().astype(np.float64)
-    u = np.clip(U[:, None, :] + eps, sc.CL, sc.CU)
-    Uref = np.einsum("k,jkc->jc", w / w.sum(), u)
+    eps = mppi.noise()
+    Uref = np.zeros((N, 2))
+    wn = w / w.sum()
+    for c0 in range(0, K, 65536):   # chunked: the full cfg4 tensor is 0.8 GB in FP32
+        u = np.clip(U[:, None, :] + eps[:, c0:c0 + 65536, :].astype(np.float64), sc.CL, sc.CU)
+        Uref += np.einsum("k,jkc->jc", wn[c0:c0 + 65536], u)
     assert np.abs(mppi.r.Control - Uref).max() <= FP32_TOL * np.abs(Uref).max()
     assert (mppi.r.Control >= np.array(sc.CL) - 1e-6).all() and (mppi.r.Control <= np.array(sc.CU) + 1e-6).all()
     # spot parity: 256 samples spread over the shard replayed through the oracle
     idx = np.linspace(0, K - 1, 256).astype(int)
     sub = orc.plan(orc.make_config(args[:5] + (256,) + args[6:], dict(kw, FeasibilityCount=256)), circles, blocks,
-                   args[3], U, np.ascontiguousarray(eps[:, idx, :]), capi.FP64, threads=8, want_margin=True)
+                   args[3], U, np.ascontiguousarray(eps[:, idx, :].astype(np.float64)), capi.FP64, threads=8, want_margin=True)
     ok = sub["margins"] > GUARD
     rel = np.abs(costs[idx] - sub["costs"]) / np.abs(sub["costs"])
     assert rel[ok].max() <= FP32_TOL and np.array_equal(flags[idx][ok], sub["flags"][ok])

@@ -39,7 +39,11 @@ WORKLOADS = {
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu captures
 # (profiles/r02_ncu_*.md): (rollout / scan kernel, update kernel); N = 1 only.
-NCU_TRAFFIC = {   # key: (--config, --walls)
+NCU_TRAFFIC = {   # key: (--config, --walls); the start pose does not change the traffic
+    (1, 0): (26245376 + 0, 26491392 + 0),                          # profiles/r02_ncu_cfg2_K65536_N50.md
+    (2, 0): (545536 + 112067072, 168837120 + 3288832),             # profiles/r02_ncu_cfg3_K262144_N80.md (eps written by the rollout: Philox inside)
+    (3, 0): (838968576 + 8367104, 843080192 + 3372800),            # profiles/r02_ncu_cfg4_K1M_N100_walls_reached.md (eps read back: pre-generated)
+    (4, 0): (4166000 + 1685743000, 1697900000 + 3697000),          # profiles/r02_ncu_cfg5_B4096.md
 }
 
 
@@ -51,6 +55,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", type=int, default=1, help="index into BASELINE.json configs (default 1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the extra.cfg4 strong-scaling block that rides along with the default line")
     ap.add_argument("--walls", type=int, default=0, help="cfg4 only: number of wall blocks M_p (default 3; SURVEY 8(d) asks for 3 and 16)")
     ap.add_argument("--x0", default="", help="override the start state, comma separated (cfg4: a pose from which the walls are reached)")
     ap.add_argument("--noise-policy", type=int, default=0, help="0 auto | 1 latency (pre-generated noise) | 2 throughput (Philox inside the rollout)")
@@ -304,6 +309,56 @@ def parity_across_ranks(m, mdist, args, kw, circles, blocks, exchange, rank, wor
     return out
 
 
+def strong_scaling_cfg4(m, mdist, exchange, rank, world, local_rank, steps=20, warm=5):
+    """BASELINE.json config 4 (dynamic bicycle + polygon walls, K = 1,048,576 TOTAL, N = 100) on `world` GPUs, strong scaling:
+    device time per step (CUDA events on the library stream, L2 flushed, max over ranks) and the exchange's parity check.
+    Reported as `extra.cfg4` of the headline line so that the driver's 1/2/4/8-GPU record carries the north-star target."""
+    import torch
+
+    args, kw, circles, blocks, scaling, K, off, kl = workload(3, world, rank)
+    N = args[7]
+    kw.update(device=local_rank, precision=m.capi.FP32, noise_mode=m.capi.NOISE_PHILOX)
+    parity = None
+    if world > 1:
+        parity = parity_across_ranks(m, mdist, args, kw, circles, blocks, exchange, rank, world, local_rank, iters=2)
+    mp = m.defineMPPI(*args, **kw)
+    m.defineMPPIblocks(mp, blocks)
+    if world > 1:
+        (mdist.init_peer_exchange if exchange == "peer" else mdist.init_library_comm)(mp)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
+    st = torch.cuda.ExternalStream(mp.stream(), device=torch.device("cuda", local_rank))
+    sync_t = torch.zeros(1, device="cuda")
+    m.MPPIPlan(mp)
+    for _ in range(warm):
+        mp.step_async(adopt=True)
+    mp.sync()
+    mp.adopt_nominal()
+    e0 = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    e1 = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    if world > 1:
+        torch.distributed.barrier()
+    torch.cuda.synchronize()
+    for i in range(steps):
+        with torch.cuda.stream(st):
+            flush.zero_()
+            if world > 1:
+                torch.distributed.all_reduce(sync_t)
+        e0[i].record(st)
+        mp.step_async(adopt=False)
+        e1[i].record(st)
+    mp.sync()
+    total = float(np.sum([e0[i].elapsed_time(e1[i]) for i in range(steps)])) * 1e-3
+    if world > 1:
+        t = torch.tensor([total], dtype=torch.float64, device="cuda")
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        total = float(t.item())
+    info = mp.plan_info()
+    mp.close()
+    del flush
+    return {"workload": WORKLOADS[3], "scaling": "strong", "K_total": K, "K_per_gpu": kl, "N": N, "steps": steps, "ms_per_step": total / steps * 1e3,
+            "value": K * N * steps / total, "unit": UNIT, "plan_info": info, "parity_n": parity}
+
+
 def run_ours(a, rank, world, local_rank):
     import torch
 
@@ -494,6 +549,14 @@ def run_ours(a, rank, world, local_rank):
         sat_frac = wall_tests / float(warps * N * len(blocks))
         F_exec = F - 102 * len(blocks) * (1.0 - sat_frac)
 
+    # the north star's multi-GPU target (cfg4, strong scaling) rides along with the headline line at every N
+    extra_cfg4 = None
+    if a.config == 1 and not a.no_extra:
+        mppi.close()
+        del flush
+        torch.cuda.empty_cache()
+        extra_cfg4 = strong_scaling_cfg4(m, mdist, exchange if world > 1 else "none", rank, world, local_rank)
+
     line = None
     if rank == 0:
         line = {
@@ -570,6 +633,8 @@ def run_ours(a, rank, world, local_rank):
                                                 if in_l2 else "eps exceeds the L2: the in-graph figure is an HBM rate")}
         if parity_n is not None:
             line["parity_n"] = parity_n
+        if extra_cfg4 is not None:
+            line["extra"] = {"cfg4": extra_cfg4}
         if not a.no_cpu_baseline:
             cb, _, _ = cpu_baseline(a.config if a.config != 4 else 0)
             line["cpu_baseline"] = cb

@@ -284,7 +284,10 @@ int32_t mppi_peer_init(mppi_handle_t* h, const uint8_t* handles /* n_ranks x 64,
                        int32_t rank, int32_t n_ranks);
 
 /* timings of the last step in microseconds (CUDA events on the handle's stream):
- * [0] rollout, [1] softmin+update, [2] combine+nominal rollout, [3] whole device step */
+ * [0] rollout, [1] softmin+update, [2] combine+nominal rollout, [3] whole device step.
+ * [0..2] need mppi_set_profiling(h, 1).  [3] under graph replay: the two timestamp operations that bracket a replay are
+ * recorded only from the first mppi_get_timings / mppi_set_profiling call on (they cost ~2 us of every step), so the first
+ * call returns 0 in [3] and arms them for the steps that follow. */
 int32_t mppi_get_timings(mppi_handle_t* h, float us[4]);
 /* the CUDA stream (cudaStream_t) every step of this handle is enqueued on, so that callers can
  * order their own work or record their own events against it */

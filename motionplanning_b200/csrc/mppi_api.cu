@@ -183,6 +183,7 @@ static int create_impl(mppi_handle* h) {
     int variant = c.rollout_variant;
     if (const char* e = getenv("MPPI_ROLLOUT_VARIANT")) variant = atoi(e);
     if (const char* e = getenv("MPPI_PDL")) h->pdl = atoi(e) != 0;
+    if (const char* e = getenv("MPPI_STEP_EVENTS")) h->step_events = atoi(e) != 0;
     const bool can_pack = c.precision == MPPI_FP32 && (h->K_local % 2) == 0;
     // pre-generated noise (variants 0-2): single-instance Philox MPPI steps; 3 / 4 keep Philox inside the rollout
     // noise_policy: latency = pre-generate (one more HBM pass over eps, the result arrives earlier), throughput = Philox inside

@@ -131,6 +131,8 @@ struct mppi_handle {
   int64_t launches = 0;
   bool stepped = false;
   bool timings_pending = false;   // events of the last step not yet read back
+  bool step_events = false;       // graph replays are bracketed by ev[0] / ev[4] (armed by the first mppi_get_timings / mppi_set_profiling call)
+  bool step_timed = false;        // ... and the last replay was
   bool x0_dirty = false, u_dirty = false;   // pinned x0 / U_nom changed since the last upload
   bool in_flight = false;   // work enqueued on the stream and not yet synchronised
   bool inputs_busy = false; // a step that reads the pinned input block may not have consumed it yet

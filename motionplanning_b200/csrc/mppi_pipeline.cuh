@@ -529,9 +529,12 @@ inline int run_variant(mppi_handle* h, int v) {
   auto it = h->graphs.find(graph_key(h, v));
   // bracket the replay with events on the launching stream so callers can read the
   // device time of the whole step (mppi_get_timings()[3]) without a profiler
-  MPPI_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
+  // The bracket costs two timestamp operations on the stream around every replay, so it is recorded only once a caller has
+  // asked for timings (mppi_get_timings / mppi_set_profiling arm it; MPPI_STEP_EVENTS=1 forces it from the first step).
+  if (h->step_events) MPPI_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
   MPPI_CUDA(h, cudaGraphLaunch(it->second, h->stream));
-  MPPI_CUDA(h, cudaEventRecord(h->ev[4], h->stream));
+  if (h->step_events) MPPI_CUDA(h, cudaEventRecord(h->ev[4], h->stream));
+  h->step_timed = h->step_events;
   h->launches += kernels_in(h, v & V_ENQ_MASK);
   h->noise_ready = (v & V_PREGEN) != 0;   // any other step leaves this iteration's own noise (or none) in eps
   if (v & (V_COMBINE | V_FUSED_FINAL | V_XFINAL)) h->seq_launched++;

@@ -41,6 +41,9 @@ constexpr int PIPE_SLAB_MAX = 112 * 1024;             // N * PIPE_SAMPLES * 8 by
 #ifndef MPPI_PIPE_HAND
 #define MPPI_PIPE_HAND 4                              // horizon steps per producer -> consumer hand-over (divides EPS_GROUP)
 #endif
+#ifndef MPPI_PIPE_SPIN
+#define MPPI_PIPE_SPIN 0   // bit 0: spin (test_wait) on the TMA barriers, bit 1: on the hand-over barriers; measured equal to try_wait (15.6 vs 15.3 us), so the parking wait stays
+#endif
 #ifndef MPPI_PIPE_UNROLL
 #define MPPI_PIPE_UNROLL 2                            // steps per loop body: lets the scheduler overlap the MUFU chains of neighbouring steps
 #endif
@@ -56,7 +59,30 @@ struct PipeHot {
   float circ[HOT_CIRCLES][3];
 };
 
+// float index of PipeHot field i (i < 28) inside StaticParams<float>; -1 = padding
+__device__ __forceinline__ int pipe_hot_offset(int i) {
+  using P = StaticParams<float>;
+  constexpr int CL = offsetof(P, CL) >> 2, CU = offsetof(P, CU) >> 2, W = offsetof(P, w) >> 2, XL = offsetof(P, XL) >> 2, XU = offsetof(P, XU) >> 2;
+  constexpr int tab[28] = {CL, CU, CL + 1, CU + 1, W + 2, W + 3, W + 4, W + 5,
+                           int(offsetof(P, dt) >> 2), int(offsetof(P, half_dt) >> 2), int(offsetof(P, inv_Lwb) >> 2), -1,
+                           XL, XL + 1, XL + 2, XL + 3, XL + 4, XU, XU + 1, XU + 2, XU + 3, XU + 4,
+                           int(offsetof(P, goal) >> 2), int(offsetof(P, goal) >> 2) + 1, int(offsetof(P, slack) >> 2), int(offsetof(P, obs_pen) >> 2),
+                           int(offsetof(P, term_scale) >> 2), -1};
+  int r = -1;
+#pragma unroll
+  for (int k = 0; k < 28; ++k) r = (i == k) ? tab[k] : r;   // select chain over immediates: no memory, no branches
+  return r;
+}
 static_assert(sizeof(PipeHot) == (28 + 3 * HOT_CIRCLES) * 4, "PipeHot is filled field by field through a float view");
+// Spin on the barrier's phase without suspending: mbarrier.try_wait parks the thread for an implementation-defined time, which is
+// the right thing for long waits and the wrong one for a hand-over that is expected within a few hundred cycles.
+__device__ __forceinline__ void mbar_spin(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  } while (!done);
+}
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -105,29 +131,34 @@ rollout_pipe_kernel(const __grid_constant__ StaticParams<float> p, const Buffers
     }
   }
   for (int i = t; i < PIPE_PAIRS_W * n_hands; i += PIPE_BS) mbar_init(&s_prog[i / n_hands][i % n_hands], 32);
+  // hot parameters: thread 64 + i copies field i of PipeHot from the kernel parameter block through an offset table (ONE indexed
+  // constant load per thread; a chain of selects cost 1.8 us of cold constant-cache misses in front of the block barrier)
   {
-    float* hot = reinterpret_cast<float*>(&sh);
     constexpr int NHOT = sizeof(PipeHot) / 4;
     if (t >= 64 && t < 64 + NHOT) {
       const int i = t - 64;
-      float v = 0.f;
-      if (i < 4) v = (i == 0) ? p.CL[0] : (i == 1) ? p.CU[0] : (i == 2) ? p.CL[1] : p.CU[1];
-      else if (i < 8) v = p.w[i - 2];                                         // w2, w3, w4, w5
-      else if (i < 12) v = (i == 8) ? p.dt : (i == 9) ? p.half_dt : (i == 10) ? p.inv_Lwb : 0.f;
-      else if (i < 17) v = p.XL[i - 12];
-      else if (i < 22) v = p.XU[i - 17];
-      else if (i < 28) v = (i == 22) ? p.goal[0] : (i == 23) ? p.goal[1] : (i == 24) ? p.slack : (i == 25) ? p.obs_pen : (i == 26) ? p.term_scale : 0.f;
-      else { const int o = (i - 28) / 3, c = (i - 28) % 3; const bool on = o < p.n_circles; v = on ? p.circ[o][c] : (c == 2 ? -1.f : 0.f); }   // d^2 <= -1 never holds
-      hot[i] = v;
+      const float* pf = reinterpret_cast<const float*>(&p);
+      float v;
+      if (i < 28) {
+        const int off = pipe_hot_offset(i);
+        v = off >= 0 ? pf[off] : 0.f;
+      } else {
+        const int o = (i - 28) / 3, c = (i - 28) % 3;
+        v = o < p.n_circles ? pf[(offsetof(StaticParams<float>, circ) >> 2) + 3 * o + c] : (c == 2 ? -1.f : 0.f);   // d^2 <= -1 never holds
+      }
+      reinterpret_cast<float*>(&sh)[i] = v;
     }
   }
   pdl_wait();   // programmatic dependent of begin_kernel: x0 / U_nom are read from here on
+  // x0 and U_nom are cold in HBM after an L2 flush (~1 us a miss): x0 is fetched by another warp than U_nom so that the two misses
+  // overlap instead of following each other in one warp (they used to put the block barrier at 3.3 us)
   const double* Ub = buf.U + size_t(b) * 2 * N;
+  if (t >= PIPE_BS - 32 && t < PIPE_BS - 32 + 5) s_x0[t - (PIPE_BS - 32)] = float(buf.x0[size_t(b) * MPPI_MAX_NX + t - (PIPE_BS - 32)]);
   for (int j = t; j < N; j += PIPE_BS) {
-    const float u0 = float(Ub[j]), u1 = float(Ub[N + j]);
+    const double d0 = Ub[j], d1 = Ub[N + j];
+    const float u0 = float(d0), u1 = float(d1);
     sU[j] = make_float4(u0, u1, p.G00 * u0 + p.G01 * u1, p.G10 * u0 + p.G11 * u1);   // g_j = lambda inv(Sigma) U_nom[j] (MPPIUtils.jl:45, hoisted)
   }
-  if (t >= 32 && t < 37) s_x0[t - 32] = float(buf.x0[size_t(b) * MPPI_MAX_NX + t - 32]);
   __syncthreads();
 
   const int w = wid & (PIPE_PAIRS_W - 1);                 // the pair this warp belongs to
@@ -143,7 +174,7 @@ rollout_pipe_kernel(const __grid_constant__ StaticParams<float> p, const Buffers
     V stage = V(0.f), viol = V(0.f);
 #pragma unroll PIPE_UNROLL
     for (int j = 0; j < N; ++j) {
-      if ((j % EPS_GROUP) == 0) mbar_wait(&s_bar[j / EPS_GROUP], 0);
+      if ((j % EPS_GROUP) == 0) { if (MPPI_PIPE_SPIN & 1) mbar_spin(&s_bar[j / EPS_GROUP], 0); else mbar_wait(&s_bar[j / EPS_GROUP], 0); }
       const float4 e = row[size_t(j) * RS];               // eps of the pair: (e0, e1) of sample a, (e0, e1) of sample b
       const float4 nu = sU[j];
       const V u0 = M::fmin(M::fmax(V(nu.x) + V(e.x, e.z), V(CL0)), V(CU0));   // PushInBounds (MPPIUtils.jl:13-20)
@@ -181,7 +212,7 @@ rollout_pipe_kernel(const __grid_constant__ StaticParams<float> p, const Buffers
   Count2 hits{0, 0};
 #pragma unroll PIPE_UNROLL
   for (int j = 0; j < N; ++j) {
-    if ((j % PIPE_HAND) == 0) mbar_wait(&s_prog[w][j / PIPE_HAND], 0);
+    if ((j % PIPE_HAND) == 0) { if (MPPI_PIPE_SPIN & 2) mbar_spin(&s_prog[w][j / PIPE_HAND], 0); else mbar_wait(&s_prog[w][j / PIPE_HAND], 0); }
     const float4 q = row[size_t(j) * RS];
     const V uxn = V(q.x, q.y), tnn = V(q.z, q.w);
     stage += V(w5) * (y * y);                             // pre-step state's y^2

@@ -124,7 +124,9 @@ struct Buffers {
   int ksplit;
   int n_ranks;
   int rank;
-  PeerWindow* const* peers;   // [n_ranks] exchange windows of all ranks (own + IPC-mapped peers), or nullptr
+  PeerWindow* const* peers;   // non-null: the in-kernel peer exchange is set up (device copy of the table below; only tested against nullptr)
+  PeerWindow* peer_w[PEER_MAX_RANKS];   // exchange windows of all ranks (own + peer-mapped), BY VALUE in the parameter block: a kernel reaches a
+                                        // window through one indexed constant load instead of a dependent global load that is cold after an L2 flush
   unsigned long long seq_base;   // *seq when the peer exchange was set up: exchange flags count steps from there
   const int* halt;      // closed loop: nonzero once the episode is over; the step's kernels then do nothing (nullptr otherwise)
   int trace;            // 1: kernels stamp %globaltimer at first-CTA start / last-CTA end into dbg[8..]

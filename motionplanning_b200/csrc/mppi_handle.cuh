@@ -263,6 +263,7 @@ Buffers<R> make_buffers(const mppi_handle* h) {
   b.n_ranks = h->n_ranks;
   b.rank = h->rank;
   b.peers = h->p2p ? h->d_peers : nullptr;
+  for (int g = 0; g < PEER_MAX_RANKS; ++g) b.peer_w[g] = h->p2p ? h->peer_ptr[g] : nullptr;
   b.seq_base = h->seq_base;
   b.trace = h->profiling == 2 ? 1 : 0;
   b.halt = nullptr;

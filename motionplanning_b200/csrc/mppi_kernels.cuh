@@ -424,11 +424,11 @@ __global__ void __launch_bounds__(CUTOFF_BS) cutoff_kernel(const __grid_constant
     const int par = int(step & 1ull);
     const uint32_t flag = uint32_t(step);
     if (t < G) {
-      ll_store(&buf.peers[t]->cnt[par][me], double(s_cnt[CUTOFF_BS - 1]), flag);
+      ll_store(&buf.peer_w[t]->cnt[par][me], double(s_cnt[CUTOFF_BS - 1]), flag);
       const unsigned long long t0 = globaltimer_ns();
       double v = 0.0;
-      while (!ll_try_load(&buf.peers[me]->cnt[par][t], flag, &v)) {
-        if (globaltimer_ns() - t0 > 2000000000ull) { buf.peers[me]->timeout = step; break; }   // finalize's exchange reports the failure
+      while (!ll_try_load(&buf.peer_w[me]->cnt[par][t], flag, &v)) {
+        if (globaltimer_ns() - t0 > 2000000000ull) { buf.peer_w[me]->timeout = step; break; }   // finalize's exchange reports the failure
       }
       s_rank_cnt[t] = int(v);
     }

@@ -430,7 +430,7 @@ __device__ __forceinline__ void finalize_block(const StaticParams<R>& p, const B
     const uint32_t flag = uint32_t(step);
     for (int i = t; i < plen; i += BS) {
       const double v = sOwn[i];
-      for (int g = 0; g < G; ++g) ll_store(&buf.peers[g]->line[par][me][i], v, flag);
+      for (int g = 0; g < G; ++g) ll_store(&buf.peer_w[g]->line[par][me][i], v, flag);
     }
     __shared__ int s_timeout;
     if (t == 0) s_timeout = 0;
@@ -438,10 +438,10 @@ __device__ __forceinline__ void finalize_block(const StaticParams<R>& p, const B
     const unsigned long long t0 = globaltimer_ns();
     for (int i = t; i < G * plen; i += BS) {
       const int g = i / plen, e = i - g * plen;
-      const uint4* src = &buf.peers[me]->line[par][g][e];
+      const uint4* src = &buf.peer_w[me]->line[par][g][e];
       double v = 0.0;
       while (!ll_try_load(src, flag, &v)) {
-        if (globaltimer_ns() - t0 > 2000000000ull) { s_timeout = 1; buf.peers[me]->timeout = step; break; }
+        if (globaltimer_ns() - t0 > 2000000000ull) { s_timeout = 1; buf.peer_w[me]->timeout = step; break; }
       }
       sGat[i] = v;
     }

@@ -209,10 +209,15 @@ static int create_impl(mppi_handle* h) {
     const long long pack_min = h->pregen_ok ? MPPI_PACK_MIN_SAMPLES_PREGEN : MPPI_PACK_MIN_SAMPLES;
     h->packed = !c.strict_math && can_pack && (variant == 2 || variant == 4 || variant == 6 || (variant == 0 && samples >= pack_min));
     // two-stage warp pipeline (mppi_pipe.cuh): packed FP32 kinematic rollout that READS eps; obstacle kind / reference path are
-    // checked per step (pipe_eligible).  auto uses it wherever it would have used the packed sequential kernel; 2 keeps the latter.
-    h->pipe = h->packed && (variant == 0 || variant == 6) && c.model == MPPI_MODEL_KINEMATIC5 && c.planner == MPPI_PLANNER_MPPI &&
-              (c.noise_mode == MPPI_NOISE_SUPPLIED || h->pregen_ok) && size_t(c.N) * PIPE_SAMPLES * 8 <= size_t(PIPE_SLAB_MAX) &&
-              c.N <= EPS_GROUP * EPS_MAX_GROUPS;
+    // checked per step (pipe_eligible).  auto uses it at EVERY sample count (its 50-step chain is the shortest of the three
+    // rollouts from 64 samples up: 9.3 us against 10.8 one sample per thread and 12.4 packed, tools/dbg/spans.py); where a step
+    // does not qualify (walls, reference path) a handle below the packing threshold falls back to one sample per thread.
+    const bool pipe_cfg = !c.strict_math && can_pack && c.model == MPPI_MODEL_KINEMATIC5 && c.planner == MPPI_PLANNER_MPPI && c.B == 1 &&
+                          (c.noise_mode == MPPI_NOISE_SUPPLIED || h->pregen_ok) && size_t(c.N) * PIPE_SAMPLES * 8 <= size_t(PIPE_SLAB_MAX) &&
+                          c.N <= EPS_GROUP * EPS_MAX_GROUPS;
+    h->pipe = pipe_cfg && (variant == 0 || variant == 6);
+    h->packed_seq = h->packed;            // the sequential rollout packs (what a step that cannot take the pipeline runs)
+    h->packed = h->packed || h->pipe;
     if (const char* e = getenv("MPPI_PIPE")) h->pipe = h->pipe && atoi(e) != 0;
     if (variant == 6 && !h->pipe) { h->err = "rollout_variant 6 (two-stage warp pipeline) needs FP32, even K_local, the kinematic model, the MPPI planner, eps read from memory (SUPPLIED or pre-generated noise) and N <= 56"; return MPPI_EINVAL; }
   }

@@ -56,6 +56,7 @@ struct mppi_handle {
   int K_local = 0, ksplit = 1, jsplit = 1, plen = 0;   // update_kernel grid = (ksplit, jsplit, B)
   bool cutoff = false;
   bool packed = false;   // rollout carries two samples per thread as f32x2 (FP32, even K_local)
+  bool packed_seq = false;   // the SEQUENTIAL rollout packs (a handle may use the pipeline below the packing threshold and fall back to one-sample threads)
   bool pipe = false;     // ... and, where the step qualifies (pipe_eligible), as the two-stage warp pipeline of mppi_pipe.cuh
   std::vector<double> circles, blocks;   // host copies (3 x Mc, 5 x Mp col-major)
   // device

@@ -178,7 +178,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   // copies when the slab is small enough to keep the occupancy: N rows of ROLLOUT_BS * LANES samples.
   size_t smemE = 0;
   if ((SRC == SRC_SUPPLIED || pregen) && (v & V_LOCAL)) {
-    const int lanes = (h->packed && sizeof(R) == 4) ? 2 : 1;
+    const int lanes = (h->packed_seq && sizeof(R) == 4) ? 2 : 1;
     const size_t slab = size_t(N) * ROLLOUT_BS * lanes * 2 * sizeof(R);
     const bool aligned = sizeof(R) == 8 || (K % 2) == 0;   // rows start and end on 16-byte boundaries
     if (slab <= size_t(lanes == 2 ? EPS_SLAB_MAX : 32 * 1024) && aligned && N <= EPS_GROUP * EPS_MAX_GROUPS && !getenv("MPPI_NO_EPS_STAGE")) {
@@ -238,7 +238,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
     if (pregen && !piped) {   // eps read back (the host keeps V_PREGEN off for tracking handles)
       bool done = false;
       if constexpr (std::is_same<R, float>::value) {
-        if (h->packed) {
+        if (h->packed_seq) {
           using PK = typename Rebind<Model, f32x2>::type;
           dim3 grid((K + 2 * ROLLOUT_BS - 1) / (2 * ROLLOUT_BS), B);
           static unsigned long long carved = 0;
@@ -258,7 +258,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
       }
     }
     if constexpr (std::is_same<R, float>::value) {
-      if (h->packed && !pregen && !launched) {   // two samples per thread on the packed FP32 pipe (mppi_pack.cuh)
+      if (h->packed_seq && !pregen && !launched) {   // two samples per thread on the packed FP32 pipe (mppi_pack.cuh)
         dim3 grid((K + 2 * ROLLOUT_BS - 1) / (2 * ROLLOUT_BS), B);
         if constexpr (SRC != SRC_SUPPLIED) {
           if (track) rollout_kernel<f32x2, typename Rebind<Model, f32x2>::type, SRC, true><<<grid, ROLLOUT_BS, smemU, s>>>(p, buf);

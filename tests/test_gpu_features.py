@@ -70,7 +70,9 @@ def test_logical_shards_match_unsharded(built, precision, G):
     argmin / counts identical, U_new equal up to the rounding of the rescale."""
     K = 8192
     args, kw, circles, blocks = sc.config(1, K=K)
-    kw = dict(kw, precision=precision)
+    # one rollout flavour on both sides (the split-phase step keeps the in-rollout Philox generator, where auto would give the
+    # unsharded handle the warp pipeline, whose cost sum has another order): what is compared here is the sharding arithmetic
+    kw = dict(kw, precision=precision, rollout_variant=3)
     U = warm_nominal(50)
     whole = make(args, kw, circles, blocks, U)
     m.MPPIPlan(whole)
@@ -355,7 +357,9 @@ def test_closed_loop_on_device_matches_host_loop_with_oracle_plant(built, model_
     args, kw, circles, blocks = sc.config(model_cfg, K=2048, N=30)
     kw = dict(kw, precision=precision, noise_mode=capi.NOISE_PHILOX)
     dev = make(args, kw, circles, blocks)
-    host = make(args, kw, circles, blocks)
+    # the closed-loop chain draws its noise inside the (one-sample) rollout; the host loop is pinned to that flavour, since auto would
+    # give it the warp pipeline, whose cost sum has another order (1e-7 relative in FP32, more than this test's 1e-9)
+    host = make(args, dict(kw, rollout_variant=3), circles, blocks)
     his, log = dev.run_closed_loop(max_iters=iters, plant_steps=steps)
     cfg = host._cfg
     x = np.array(args[3], dtype=np.float64)

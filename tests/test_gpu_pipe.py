@@ -126,6 +126,21 @@ def test_pipe_falls_back_where_it_does_not_apply(built):
     assert mp.plan_info()["packed"] == 1
     m.MPPIPlan(mp)
     mp.close()
+    # auto: the pipeline at every (even) sample count; below the packing threshold a step that cannot take it (walls) falls back to
+    # one sample per thread, at or above it to the packed sequential kernel
+    for K, fallback in ((1024, 0), (65536, 1)):
+        args, kw, circles, blocks = _args(K, 50)
+        mp = m.defineMPPI(*args, **dict(kw, precision=capi.FP32, noise_mode=capi.NOISE_PHILOX))
+        m.defineMPPIobs(mp, circles)
+        assert mp.plan_info()["packed"] == 2
+        m.defineMPPIblocks(mp, sc.PARKING_BLOCKS)
+        assert mp.plan_info()["packed"] == fallback
+        m.MPPIPlan(mp)
+        mp.close()
+    args, kw, circles, blocks = _args(1023, 50)           # odd K cannot pack
+    mp = m.defineMPPI(*args, **dict(kw, precision=capi.FP32, noise_mode=capi.NOISE_PHILOX))
+    assert mp.plan_info()["packed"] == 0
+    mp.close()
     with pytest.raises(m.MPPIError, match="two-stage warp pipeline"):
         m.defineMPPI(*_args(4096, 80)[0], **dict(_args(4096, 80)[1], precision=capi.FP32, noise_mode=capi.NOISE_PHILOX, rollout_variant=6))
     a7, k7, c7, b7 = sc.config(3, K=4096)

@@ -256,43 +256,6 @@ __device__ __forceinline__ Scratch fresh_scratch(int K_local) {
   fresh.rho_key = ~0ull; fresh.argmin = ~0u; fresh.feasible_count = 0; fresh.k_eff = K_local; fresh.pad = 0;
   return fresh;
 }
-// In-kernel all-gather over NVLink peer memory (B == 1), LL protocol (see PeerWindow): this rank's partial (sOwn) goes into slot
-// [parity][rank] of every rank's window, then the block polls its own window until all G x plen lines carry this step's flag.
-// Out of line on purpose: with the exchange inlined, everything finalize executes AFTER it (U_new, nominal rollout, costing, result
-// block) ran 2-3x slower on its first and only pass than the same code in the single-rank instantiation (3,900 against 800
-// cycles for U_new; a second pass over the same code took 860) — cold instruction fetch behind the poll loop's code.
-// Must be called by all threads of the block.  Returns true when the 2 s time-out fired.
-template <class R, int BS>
-__device__ __noinline__ bool peer_allgather(const Buffers<R>& buf, const double* sOwn, double* sGat, int plen, unsigned long long seq_all, bool push) {
-  __shared__ int s_timeout;
-  const int t = threadIdx.x, G = buf.n_ranks, me = buf.rank;
-  // exchange steps are counted from mppi_peer_init (seq_base), so ranks whose handles ran different numbers of
-  // steps before the exchange was set up still agree on the flag; from then on they step in lockstep
-  const unsigned long long step = seq_all - buf.seq_base + 1ull;
-  const int par = int(step & 1ull);
-  const uint32_t flag = uint32_t(step);
-  if (push) {
-    for (int i = t; i < plen; i += BS) {
-      const double v = sOwn[i];
-      for (int g = 0; g < G; ++g) ll_store(&buf.peer_w[g]->line[par][me][i], v, flag);
-    }
-  }
-  if (t == 0) s_timeout = 0;
-  __syncthreads();
-  const unsigned long long t0 = globaltimer_ns();
-  for (int i = t; i < G * plen; i += BS) {
-    const int g = i / plen, e = i - g * plen;
-    const uint4* src = &buf.peer_w[me]->line[par][g][e];
-    double v = 0.0;
-    while (!ll_try_load(src, flag, &v)) {
-      if (globaltimer_ns() - t0 > 2000000000ull) { s_timeout = 1; buf.peer_w[me]->timeout = step; break; }
-    }
-    sGat[i] = v;
-  }
-  __syncthreads();
-  return s_timeout != 0;
-}
-
 // The block-level body: called by finalize_kernel (one block per instance) and by the LAST block of
 // scan_rollout_kernel to finish (mppi_scan.cuh), which saves the launch and the inter-kernel gap.
 // `wait_prev`: issue griddepcontrol.wait before the first read of the previous kernel's output.
@@ -458,7 +421,32 @@ __device__ __forceinline__ void finalize_block(const StaticParams<R>& p, const B
   size_t gstride = size_t(p.B) * plen;
   bool xchg_timeout = false;
   if (xchg) {
-    xchg_timeout = peer_allgather<R, BS>(buf, sOwn, sGat, plen, seq_all, true);
+    // In-kernel all-gather over NVLink peer memory (B == 1), LL protocol (see PeerWindow).
+    const int me = buf.rank;
+    // exchange steps are counted from mppi_peer_init (seq_base), so ranks whose handles ran different numbers of
+    // steps before the exchange was set up still agree on the flag; from then on they step in lockstep
+    const unsigned long long step = seq_all - buf.seq_base + 1ull;
+    const int par = int(step & 1ull);
+    const uint32_t flag = uint32_t(step);
+    for (int i = t; i < plen; i += BS) {
+      const double v = sOwn[i];
+      for (int g = 0; g < G; ++g) ll_store(&buf.peer_w[g]->line[par][me][i], v, flag);
+    }
+    __shared__ int s_timeout;
+    if (t == 0) s_timeout = 0;
+    __syncthreads();
+    const unsigned long long t0 = globaltimer_ns();
+    for (int i = t; i < G * plen; i += BS) {
+      const int g = i / plen, e = i - g * plen;
+      const uint4* src = &buf.peer_w[me]->line[par][g][e];
+      double v = 0.0;
+      while (!ll_try_load(src, flag, &v)) {
+        if (globaltimer_ns() - t0 > 2000000000ull) { s_timeout = 1; buf.peer_w[me]->timeout = step; break; }
+      }
+      sGat[i] = v;
+    }
+    __syncthreads();
+    xchg_timeout = s_timeout != 0;
     gat = sGat;
     gstride = plen;
   }

@@ -338,6 +338,8 @@ def strong_scaling_cfg4(m, mdist, exchange, rank, world, local_rank, steps=20, w
     if world > 1:
         torch.distributed.barrier()
     torch.cuda.synchronize()
+    with torch.cuda.stream(st):
+        torch.cuda._sleep(16_000_000)   # the host enqueues the timed iterations while the stream spins (see run_ours)
     for i in range(steps):
         with torch.cuda.stream(st):
             flush.zero_()
@@ -437,6 +439,11 @@ def run_ours(a, rank, world, local_rank):
     ev1 = [torch.cuda.Event(enable_timing=True) for _ in range(a.steps)]
     barrier()
     clocks.start()
+    # Host jitter must not reach the device-timed spans: the stream first spins for ~8 ms (torch.cuda._sleep), during which the host
+    # enqueues the timed iterations, so every rank's GPU then runs them back to back out of a full queue.  (Seen at 8 GPUs without
+    # it: one 1.8 ms step in a hundred — a rank whose host thread fell behind its stream — which the summed time then carries.)
+    with torch.cuda.stream(lib_stream):
+        torch.cuda._sleep(16_000_000)
     for i in range(a.steps):
         with torch.cuda.stream(lib_stream):
             flush.zero_()
@@ -576,8 +583,8 @@ def run_ours(a, rank, world, local_rank):
                                  if exchange == "peer" else f"samples sharded x{world}, one NCCL all-gather per step") if world > 1 and not batched
                                 else ("instances sharded, no collective" if batched and world > 1 else "1 GPU")),
                 "l2": "flushed between timed iterations (256 MiB write)",
-                "timing": "CUDA events on the library stream around one graph launch per iteration (flush + step enqueued asynchronously), "
-                          "summed, max over ranks" + ("; ranks aligned by a one-element all-reduce between flush and first event" if world > 1 and not batched else ""),
+                "timing": "CUDA events on the library stream around one graph launch per iteration (flush + step enqueued asynchronously behind "
+                          "an 8 ms device-side spin, so the queue is full when the timed iterations run), summed, max over ranks" + ("; ranks aligned by a one-element all-reduce between flush and first event" if world > 1 and not batched else ""),
                 "plan_info": info},
             "latency_us": {"device_median": float(np.median(dev_us)), "device_p99": float(np.percentile(dev_us, 99)),
                            "device_max": float(np.max(dev_us)),

@@ -55,7 +55,14 @@ struct StaticParams {
   R circ[MPPI_MAX_CIRCLES][3];  // x, y, r^2
   R blk_all[4];                 // bounding circle of ALL walls: cx, cy, broad-phase d^2, pad
   R blk[MPPI_MAX_BLOCKS][8];    // cx, cy, cos(psi), sin(psi), half_len, half_wid, broad-phase d^2, pad
+  // many walls (n_blocks > 4): x-binned candidate masks.  Bit b of wall_mask[i] is set iff wall b's broad-phase circle can be
+  // reached from SOME pose whose rectangle centre has x in bin i (any y); a wall whose bit is clear is provably free for
+  // every such pose by the same criterion the per-wall vote applies, so only the set bits are voted on (WALL_BINS bins over
+  // [wall_x0, wall_x0 + WALL_BINS / wall_inv_w]; outside that range no wall is reachable).
+  R wall_x0, wall_inv_w;
+  uint32_t wall_mask[32];
 };
+constexpr int WALL_BINS = 32;
 
 // per-instance scratch; initialised at create and re-armed by finalize once it has been consumed
 struct Scratch {

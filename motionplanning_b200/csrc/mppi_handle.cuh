@@ -209,6 +209,26 @@ void build_params(const mppi_handle* h, StaticParams<R>* p) {
     const double Rv = std::hypot(c.veh_L / 2, c.veh_W / 2), Rw = std::hypot(bl[3], bl[4]);
     p->blk[b][6] = R(2.0 * (Rv + Rw) * (Rv + Rw) * (1.0 + 1e-5)); p->blk[b][7] = R(0);
   }
+  if (p->n_blocks > 4) {   // x-binned candidate masks (StaticParams::wall_mask); reach = radius of the broad-phase circle, with slack for FP32 binning
+    const double Rv = std::hypot(c.veh_L / 2, c.veh_W / 2);
+    double lo = 1e300, hi = -1e300;
+    std::vector<double> reach(p->n_blocks);
+    for (int b = 0; b < p->n_blocks; ++b) {
+      const double* bl = &h->blocks[5 * b];
+      const double Rw = std::hypot(bl[3], bl[4]);
+      reach[b] = std::sqrt(2.0 * (Rv + Rw) * (Rv + Rw) * (1.0 + 1e-5)) * (1.0 + 1e-4) + 1e-3;
+      lo = std::min(lo, bl[0] - reach[b]); hi = std::max(hi, bl[0] + reach[b]);
+    }
+    const double w = std::max((hi - lo) / WALL_BINS, 1e-6);
+    p->wall_x0 = R(lo); p->wall_inv_w = R(1.0 / w);
+    for (int i = 0; i < WALL_BINS; ++i) {
+      const double b_lo = lo + (i - 0.01) * w, b_hi = lo + (i + 1.01) * w;   // 1 % overlap: the device bins in FP32
+      uint32_t m = 0;
+      for (int b = 0; b < p->n_blocks; ++b)
+        if (h->blocks[5 * b] + reach[b] >= b_lo && h->blocks[5 * b] - reach[b] <= b_hi) m |= 1u << b;
+      p->wall_mask[i] = m;
+    }
+  }
 }
 
 inline void build_strict_params(const mppi_handle* h, StrictParams* p) {

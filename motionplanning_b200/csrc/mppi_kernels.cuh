@@ -128,7 +128,7 @@ __device__ __forceinline__ void rollout_horizon(const StaticParams<typename Math
     veh.step(hp, u0, u1);                          // Rungekutta2 (:76-90)
     if (NQ >= 0) acc.hits += circle_hits_regs<V, (NQ > 0 ? NQ : 0)>(hp, veh.s[0], veh.s[1]);   // x_{j+1}: ObstacleEvaluation
     else acc.hits += circle_hits<V>(p, veh.s[0], veh.s[1]);
-    if (walls) acc.hits += block_hits<V>(hp, hp.blk_all, sBlk, p.n_blocks, veh.s[0], veh.s[1], veh.sn, veh.cs, wall_stat);
+    if (walls) acc.hits += block_hits<V>(hp, hp.blk_all, sBlk, p.n_blocks, veh.s[0], veh.s[1], veh.sn, veh.cs, wall_stat, &p);
     acc.viol += bound_violation<V, Model::NX>(hp, veh.s);                 // BoundEvaluation
   };
   if (SRC == SRC_PHILOX) {

@@ -202,9 +202,22 @@ template <> __device__ __forceinline__ int hits_from_free<double>(int tested, in
 // with register index per field).  V carries veh_off / veh_hl / veh_hw (StaticParams or HotParams).
 // `stat` (diagnostics, profiling mode 2 only, nullptr otherwise): incremented by the number of walls a warp-step tests EXACTLY,
 // so that a benchmark can report which share of the rectangle tests the broad phase left standing (mppi_get_phase_clocks()[7]).
+// candidate walls of a rectangle centre x (StaticParams::wall_mask): none outside the binned range
+template <class S>
+__device__ __forceinline__ uint32_t wall_candidates(const StaticParams<S>& p, S vx) {
+  const S f = (vx - p.wall_x0) * p.wall_inv_w;
+  if (!(f > S(-0.005)) || !(f < S(WALL_BINS) + S(0.005))) return (f != f) ? 0xFFFFFFFFu : 0u;   // NaN pose: test everything
+  const int i = min(max(int(f), 0), WALL_BINS - 1);
+  return p.wall_mask[i];
+}
+__device__ __forceinline__ uint32_t wall_candidates(const StaticParams<float>& p, f32x2 vx) {
+  return wall_candidates<float>(p, vx.v.x) | wall_candidates<float>(p, vx.v.y);
+}
+
 template <class V, class P>
 __device__ __forceinline__ typename Math<V>::Count block_hits(const P& veh, const typename Math<V>::S* all4, const typename Math<V>::S* tbl,
-                                                              int n_blocks, V x, V y, V sn, V cs, unsigned long long* stat = nullptr) {
+                                                              int n_blocks, V x, V y, V sn, V cs, unsigned long long* stat = nullptr,
+                                                              const StaticParams<typename Math<V>::S>* bins = nullptr) {
   using M = Math<V>;
   using S = typename M::S;
   using S4 = typename Vec4<S>::type;
@@ -238,8 +251,12 @@ __device__ __forceinline__ typename Math<V>::Count block_hits(const P& veh, cons
       freec += exact(w0, w1, vx - V(w0.x), vy - V(w0.y));
     }
     tested = n_blocks;
-  } else {               // many walls: per-wall bounding-circle vote first
-    for (int b = 0; b < n_blocks; ++b) {
+  } else {               // many walls: x-binned candidates (warp-wide OR), then the per-wall bounding-circle vote
+    uint32_t cand = (n_blocks >= 32) ? 0xFFFFFFFFu : ((1u << n_blocks) - 1u);
+    if (bins != nullptr) cand &= __reduce_or_sync(mask, wall_candidates(*bins, vx));
+    while (cand) {
+      const int b = __ffs(cand) - 1;
+      cand &= cand - 1u;
       const S4 w0 = t4[2 * b], w1 = t4[2 * b + 1];
       const V dx = vx - V(w0.x), dy = vy - V(w0.y);
       if (__ballot_sync(mask, M::any(M::lt(M::fma(dx, dx, dy * dy), V(w1.z)))) == 0u) continue;   // provably free for every lane
@@ -252,7 +269,7 @@ __device__ __forceinline__ typename Math<V>::Count block_hits(const P& veh, cons
 }
 template <class V>
 __device__ __forceinline__ typename Math<V>::Count block_hits(const StaticParams<typename Math<V>::S>& p, V x, V y, V sn, V cs) {
-  return block_hits<V>(p, p.blk_all, &p.blk[0][0], p.n_blocks, x, y, sn, cs);
+  return block_hits<V>(p, p.blk_all, &p.blk[0][0], p.n_blocks, x, y, sn, cs, nullptr, &p);
 }
 
 // BoundEvaluation (MPPIUtils.jl:135-151): sum of violations |x - XL|, |x - XU|

@@ -145,6 +145,13 @@ def test_config4_dynamic_polygon_walls(built, precision, M_p):
     args, kw, circles, blocks = sc.config(3, K=4096, N=100, M_p=M_p)
     mppi, ref = run_pair(args, kw, circles, blocks, precision, Unom=warm_nominal(100))
     check(mppi, ref, precision)
+    # a start from which the walls are reached and hit (the default start never gets within reach of the first wall): the exact
+    # rectangle tests behind the broad phases — all-walls circle, x-binned candidate masks (M_p > 4), per-wall circle — decide
+    for x0 in ([38.0, -2.3, 0.0, 0.0, 0.0, 8.0, 0.0], [58.0, 1.9, 0.0, 0.0, -0.03, 6.0, 0.0]):   # 56-97 % of the samples hit a wall
+        a2 = args[:3] + (x0,) + args[4:]
+        mppi, ref = run_pair(a2, kw, circles, blocks, precision, Unom=warm_nominal(100))
+        assert (ref["flags"] & capi.FLAG_COLLIDED).any() and not (ref["flags"] & capi.FLAG_COLLIDED).all()
+        check(mppi, ref, precision, guard_max=0.05)
 
 
 def test_odd_sizes_and_ragged_tail(built):

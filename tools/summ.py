@@ -10,6 +10,9 @@ for path in sys.argv[1:]:
     for line in lines:
         if line.startswith("{"):
             d = json.loads(line)
+            if 'roofline' not in d:   # the reference arm's line
+                print(f"{path}: impl={d.get('impl')} ms/step={d.get('ms_per_step', 0):.3f} value={d.get('value', 0):.3e}")
+                continue
             k = d.get("kernels_us", {})
             g = d.get("kernels_us_in_graph") or {}
             lat = d.get("latency_us", {})

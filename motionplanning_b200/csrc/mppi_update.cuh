@@ -192,7 +192,87 @@ struct NominalStates<Kin5<R>> {
     }
   }
   static __device__ __forceinline__ void sub_barrier() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+  // ---- N <= 64: the whole recurrence in ONE warp's registers (lane l owns steps l and l + 32) ----
+  // Same arithmetic as the shared-memory form below, operation for operation (the scans are the same shuffle prefix sums with
+  // the same carry between the two 32-step chunks), so the states are bit-identical; what disappears are five block-level
+  // barriers and every shared-memory round trip between the phases: 3,980 -> ~1,500 SM cycles at N = 50.
+  static __device__ __forceinline__ void scan2(R v[2], R init, int lane) {
+    R carry = init;
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      R x = v[c];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const R n = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += n;
+      }
+      x += carry;
+      v[c] = x;
+      carry = __shfl_sync(0xffffffffu, x, 31);
+    }
+  }
+  // value of the previous horizon step: lane - 1 of the same chunk, lane 31 of chunk 0 for lane 0 of chunk 1, `first` for step 0
+  static __device__ __forceinline__ void prev2(const R v[2], R first, int lane, R out[2]) {
+    const R last0 = __shfl_sync(0xffffffffu, v[0], 31);
+    const R p0 = __shfl_up_sync(0xffffffffu, v[0], 1), p1 = __shfl_up_sync(0xffffffffu, v[1], 1);
+    out[0] = lane == 0 ? first : p0;
+    out[1] = lane == 0 ? last0 : p1;
+  }
+  static __device__ __forceinline__ void run_warp(const StaticParams<R>& p, const double* x0, const R* sNew, R* sX, int N, int lane) {
+    const R X0 = R(x0[0]), Y0 = R(x0[1]), PSI0 = R(x0[2]), UX0 = R(x0[3]), SA0 = R(x0[4]);
+    R sa[2], ux[2], tn[2], ps[2], sn[2], cs[2], xs[2], ys[2];
+    bool on[2];
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const int j = lane + 32 * c;
+      on[c] = j < N;
+      sa[c] = on[c] ? p.dt * sNew[2 * j] : R(0);
+      ux[c] = on[c] ? p.dt * sNew[2 * j + 1] : R(0);
+    }
+    scan2(sa, SA0, lane);   // sa_{j+1}
+    scan2(ux, UX0, lane);   // ux_{j+1}
+    const R tn0 = M::over(M::tan(SA0), p.Lwb, p.inv_Lwb);
+#pragma unroll
+    for (int c = 0; c < 2; ++c) tn[c] = M::over(M::tan(sa[c]), p.Lwb, p.inv_Lwb);   // tan(sa_{j+1}) / L
+    R uxp[2], tnp[2];
+    prev2(ux, UX0, lane, uxp);   // ux_j
+    prev2(tn, tn0, lane, tnp);   // tan(sa_j) / L
+#pragma unroll
+    for (int c = 0; c < 2; ++c) ps[c] = on[c] ? p.half_dt * M::fma(ux[c], tn[c], uxp[c] * tnp[c]) : R(0);   // dt/2 (k1p + k2p)
+    scan2(ps, PSI0, lane);  // psi_{j+1}
+    R sn0, cs0;
+    M::sincos(PSI0, &sn0, &cs0);
+#pragma unroll
+    for (int c = 0; c < 2; ++c) M::sincos(ps[c], &sn[c], &cs[c]);
+    R psp[2], snp[2], csp[2];
+    prev2(ps, PSI0, lane, psp);
+    prev2(sn, sn0, lane, snp);
+    prev2(cs, cs0, lane, csp);
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const R psit = M::fma(uxp[c] * tnp[c], p.dt, psp[c]);   // predictor heading
+      R st, ct;
+      M::sincos(psit, &st, &ct);
+      xs[c] = on[c] ? p.half_dt * M::fma(ux[c], ct, uxp[c] * csp[c]) : R(0);   // dt/2 (k1x + k2x)
+      ys[c] = on[c] ? p.half_dt * M::fma(ux[c], st, uxp[c] * snp[c]) : R(0);
+    }
+    scan2(xs, X0, lane);
+    scan2(ys, Y0, lane);
+    if (lane == 0) { sX[0] = X0; sX[1] = Y0; sX[2] = PSI0; sX[3] = UX0; sX[4] = SA0; sX[5] = sn0; sX[6] = cs0; }
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      if (on[c]) {
+        R* row = sX + (lane + 32 * c + 1) * ROW;
+        row[0] = xs[c]; row[1] = ys[c]; row[2] = ps[c]; row[3] = ux[c]; row[4] = sa[c]; row[5] = sn[c]; row[6] = cs[c];
+      }
+    }
+  }
   static __device__ __forceinline__ void run(const StaticParams<R>& p, const double* x0, const R* sNew, R* sX, R* sT, int N, int t) {
+    if (N <= 64) {
+      if (t < 32) run_warp(p, x0, sNew, sX, N, t);
+      __syncthreads();
+      return;
+    }
     // At most 257 rows: four warps do all of it and meet on a NAMED barrier (bar.sync 1, 128); a block-wide barrier of
     // 32 warps costs ~250 cycles and this routine needs six of them.  The other warps go straight to the closing barrier.
     constexpr int nt = 128;

@@ -17,7 +17,7 @@ for G, fl in ((1, 1), (2, 1), (2, 0), (1, 0)):
     for i in range(40):
         if fl: flush.zero_(); torch.cuda.synchronize()
         mp.step_async(adopt=False); mp.sync()
-        c = mp.phase_clocks(); ph.append([c[j + 1] - c[j] for j in range(6)] + [c[7] - c[2], c[3] - c[7]])
+        c = mp.phase_clocks(); ph.append([c[j + 1] - c[j] for j in range(6)])
     ph = np.median(np.array(ph[5:]), axis=0)
-    print(f"G={G} flush={fl}: partial {ph[0]:.0f} xchg+combine {ph[1]:.0f} U_new {ph[2]:.0f} states {ph[3]:.0f} costing {ph[4]:.0f} sum/write {ph[5]:.0f} | U_new first pass {ph[6]:.0f} second pass {ph[7]:.0f}", flush=True)
+    print(f"G={G} flush={fl}: partial {ph[0]:.0f} xchg+combine {ph[1]:.0f} U_new {ph[2]:.0f} states {ph[3]:.0f} costing {ph[4]:.0f} sum/write {ph[5]:.0f}", flush=True)
     mp.close()

@@ -272,7 +272,7 @@ def parity_across_ranks(m, mdist, args, kw, circles, blocks, exchange, rank, wor
         mdist.init_library_comm(sh)
     info = sh.plan_info()
     kw_ref = dict(kw, k_offset=0, K_local=0)
-    kw_ref["rollout_variant"] = 5 if info["scan"] else ({2: 6, 1: 2}.get(info["packed"], 1))   # 6 = two-stage warp pipeline, 2 = packed sequential
+    kw_ref["rollout_variant"] = 5 if info["scan"] else ({3: 7, 2: 6, 1: 2}.get(info["packed"], 1))   # 6 = two-stage warp pipeline, 2 = packed sequential
     kw_ref["noise_policy"] = 1 if info["pregen"] else 2
     ref = m.defineMPPI(*args, **kw_ref)
     if circles:
@@ -544,6 +544,7 @@ def run_ours(a, rank, world, local_rank):
     F = sc.flop_per_sample_step(kw["model"], len(circles), len(blocks))
     local_units = kl * N * B
     fused = bool(info["scan"])
+    folded = info["packed"] == 3   # warp pipeline whose blocks also do the softmin update (rollout_variant 7): no update_kernel
     roll_tflops = local_units * F / (k_us[0] * 1e-6) / 1e12
     eps_bytes = local_units * 2 * 4
     upd_bytes = eps_bytes + kl * B * 4 + N * 2 * 4 * B
@@ -575,8 +576,9 @@ def run_ours(a, rank, world, local_rank):
                 "K_per_gpu": kl, "walls": len(blocks), "circles": len(circles),
                 "step": ("scan-form fused kernel: horizon-parallel rollout + cost + online softmin + weighted update, tail (fold, exchange, "
                          "combine, nominal rollout) in its last CTA" if fused else
-                         ("rollout_pipe_kernel (two-stage warp pipeline: producer / consumer warps per sample pair) -> update_kernel -> finalize_kernel"
-                          if info["packed"] == 2 else "rollout_kernel -> update_kernel -> finalize_kernel")),
+                         ("rollout_pipe_kernel (two-stage warp pipeline, softmin update in its blocks) -> finalize_kernel (folds one partial per block)" if folded else
+                          ("rollout_pipe_kernel (two-stage warp pipeline: producer / consumer warps per sample pair) -> update_kernel -> finalize_kernel"
+                           if info["packed"] == 2 else "rollout_kernel -> update_kernel -> finalize_kernel"))),
                 "noise": ("philox4x32-10 on the device, one tensor per step inside the timed region: noise_kernel draws the NEXT iteration's tensor "
                           "behind the step, the rollout reads it back" if info["pregen"] else "philox4x32-10 inside the rollout kernel"),
                 "parallelism": ((f"samples sharded x{world}, softmin all-gather inside the step kernel over NVLink peer memory"
@@ -604,7 +606,8 @@ def run_ours(a, rank, world, local_rank):
                 "rollout_start_to_finalize_end": float(g_us[3]),
                 "noise_next_iteration": float(g_us[4]), "rollout_start_to_last_kernel_end": float(g_us[5]),
                 "source": "%globaltimer spans written by the kernels themselves inside the replayed graph (mppi_set_profiling(2))"},
-            "roofline": {"kernel": "scan_rollout_kernel (rollout + cost + softmin + weighted update)" if fused else ("rollout_pipe_kernel" if info["packed"] == 2 else "rollout_kernel"),
+            "roofline": {"kernel": "scan_rollout_kernel (rollout + cost + softmin + weighted update)" if fused else ("rollout_pipe_kernel<., true> (rollout + cost + softmin weights + weighted update of the block's samples)" if folded else
+                                                                                                                ("rollout_pipe_kernel" if info["packed"] == 2 else "rollout_kernel")),
                          "bound": "fp32", "achieved": roll_tflops, "peak": fp32_peak,
                          "unit": "TFLOP/s",
                          # wall scenes: `frac` counts only the rectangle tests the kernel actually ran (sat_exact_fraction, counted by the
@@ -622,7 +625,11 @@ def run_ours(a, rank, world, local_rank):
                          if (fused or info["pregen"]) else None},
             "clocks": clocks.summary(),
         }
-        if fused:
+        if folded:
+            line["roofline_update"] = {"kernel": None, "fused": True,
+                                       "note": "no update kernel: every block of rollout_pipe_kernel weights its own 256 samples and sums their clamped controls "
+                                               "from a second fetch of its eps slab (L2 hits), finalize folds one partial per block"}
+        elif fused:
             line["roofline_update"] = {"kernel": None, "fused": True,
                                        "note": "no separate update kernel at this size: the weighted control sum is accumulated by the scan kernel from "
                                                "the eps values it already holds in registers, so eps is read ONCE per step (update_kernel's second pass, "

@@ -96,7 +96,9 @@ typedef struct mppi_config {
   int32_t rollout_variant;   /* 0 auto | 1 one sample per thread | 2 two samples per thread (packed FP32x2; FP32 and
                               * even K_local only) | 3, 4 = 1, 2 with the Philox noise always drawn inside the
                               * rollout | 5 scan-form fused step | 6 two-stage warp pipeline (kinematic model, packed; what
-                              * auto picks wherever it packs and the scene has circles only).  0-2, 5, 6 pre-generate the
+                              * auto picks wherever it packs and the scene has circles only) | 7 = 6 with the softmin update
+                              * done by the rollout's own blocks (no update kernel; no cut-off; the device-timed step is
+                              * shorter, the result reaches the host later: for device-chained loops).  0-2, 5-7 pre-generate the
                               * next iteration's noise beside finalize whenever the step is a single-instance Philox MPPI
                               * step.
                               * Environment MPPI_ROLLOUT_VARIANT overrides; MPPI_PREGEN=0 disables pre-generation. */
@@ -306,7 +308,7 @@ int32_t mppi_set_profiling(mppi_handle_t* h, int32_t on);
 /* which kernels the next single-instance step of this handle runs (diagnostics, tests, bench):
  * [0] 1 = scan-form fused step (rollout + softmin + update + tail in one kernel), 0 = rollout / update / finalize kernels
  * [1] 1 = the next iteration's Philox noise is pre-generated behind the step ("latency" policy)
- * [2] 1 = packed FP32x2 sequential rollout, 2 = packed two-stage warp pipeline (mppi_pipe.cuh)   [3] CTAs of the scan kernel   [4] update ksplit   [5] update jsplit
+ * [2] 1 = packed FP32x2 sequential rollout, 2 = packed two-stage warp pipeline (mppi_pipe.cuh), 3 = that pipeline with the softmin update in its blocks   [3] CTAs of the scan kernel   [4] update ksplit   [5] update jsplit
  * [6] strict_math   [7] GPUs driven by this handle */
 int32_t mppi_get_plan_info(mppi_handle_t* h, int32_t info[8]);
 /* number of kernels the library launched on this handle so far */

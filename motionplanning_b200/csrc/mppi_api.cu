@@ -107,7 +107,7 @@ static int validate(const mppi_config_t* c, std::string* why) {
   if (c->precision != MPPI_FP32 && c->precision != MPPI_FP64) { *why = "unknown precision"; return MPPI_EINVAL; }
   if (c->noise_mode != MPPI_NOISE_SUPPLIED && c->noise_mode != MPPI_NOISE_PHILOX) { *why = "unknown noise_mode"; return MPPI_EINVAL; }
   if (c->planner != MPPI_PLANNER_MPPI && c->planner != MPPI_PLANNER_DWA) { *why = "unknown planner"; return MPPI_EINVAL; }
-  if (c->rollout_variant < 0 || c->rollout_variant > 6) { *why = "rollout_variant must be 0..6"; return MPPI_EINVAL; }
+  if (c->rollout_variant < 0 || c->rollout_variant > 7) { *why = "rollout_variant must be 0..7"; return MPPI_EINVAL; }
   if (c->noise_policy < 0 || c->noise_policy > 2) { *why = "noise_policy must be 0 (auto), 1 (latency) or 2 (throughput)"; return MPPI_EINVAL; }
   if (c->strict_math != 0 && c->strict_math != 1) { *why = "strict_math must be 0 or 1"; return MPPI_EINVAL; }
   if (c->strict_math && (c->precision != MPPI_FP32 || c->planner != MPPI_PLANNER_MPPI || c->B != 1)) { *why = "strict_math is the FP32 verification flavour of a single-instance MPPI step"; return MPPI_EINVAL; }
@@ -207,7 +207,7 @@ static int create_impl(mppi_handle* h) {
     // per-lane Philox / Box-Muller work out of the loop it pays from 65,536 samples (tools/sweep_pregen.py)
     const long long samples = (long long)h->K_local * c.B;
     const long long pack_min = h->pregen_ok ? MPPI_PACK_MIN_SAMPLES_PREGEN : MPPI_PACK_MIN_SAMPLES;
-    h->packed = !c.strict_math && can_pack && (variant == 2 || variant == 4 || variant == 6 || (variant == 0 && samples >= pack_min));
+    h->packed = !c.strict_math && can_pack && (variant == 2 || variant == 4 || variant == 6 || variant == 7 || (variant == 0 && samples >= pack_min));
     // two-stage warp pipeline (mppi_pipe.cuh): packed FP32 kinematic rollout that READS eps; obstacle kind / reference path are
     // checked per step (pipe_eligible).  auto uses it at EVERY sample count (its 50-step chain is the shortest of the three
     // rollouts from 64 samples up: 9.3 us against 10.8 one sample per thread and 12.4 packed, tools/dbg/spans.py); where a step
@@ -215,10 +215,18 @@ static int create_impl(mppi_handle* h) {
     const bool pipe_cfg = !c.strict_math && can_pack && c.model == MPPI_MODEL_KINEMATIC5 && c.planner == MPPI_PLANNER_MPPI && c.B == 1 &&
                           (c.noise_mode == MPPI_NOISE_SUPPLIED || h->pregen_ok) && size_t(c.N) * PIPE_SAMPLES * 8 <= size_t(PIPE_SLAB_MAX) &&
                           c.N <= EPS_GROUP * EPS_MAX_GROUPS;
-    h->pipe = pipe_cfg && (variant == 0 || variant == 6);
+    h->pipe = pipe_cfg && (variant == 0 || variant == 6 || variant == 7);
     h->packed_seq = h->packed;            // the sequential rollout packs (what a step that cannot take the pipeline runs)
     h->packed = h->packed || h->pipe;
     if (const char* e = getenv("MPPI_PIPE")) h->pipe = h->pipe && atoi(e) != 0;
+    // ... with the softmin update done by the rollout's own blocks (no update_kernel; rollout_variant 7, or MPPI_PIPE_FOLD=1 with the
+    // auto variant).  Opt-in: on B200 the device-timed step gets 1.2 us shorter (the next iteration's noise starts 2.8 us earlier)
+    // and the result reaches the host 1.3 us LATER (folding 256 per-block partials in finalize costs more than the 64-way tree
+    // behind update_kernel), DESIGN.md 4.5
+    bool want_fold = variant == 7;
+    if (const char* e = getenv("MPPI_PIPE_FOLD")) want_fold = want_fold || (variant == 0 && atoi(e) != 0);
+    h->pipe_fold = h->pipe && want_fold && !h->cutoff && (h->K_local + PIPE_SAMPLES - 1) / PIPE_SAMPLES <= FOLD_MAX_CTAS;
+    if (variant == 7 && !h->pipe_fold) { h->err = "rollout_variant 7 (warp pipeline with the update in its blocks) needs what variant 6 needs, no feasibility cut-off (FeasibilityCount >= SamplingNumber) and at most 163,840 samples per GPU"; return MPPI_EINVAL; }
     if (variant == 6 && !h->pipe) { h->err = "rollout_variant 6 (two-stage warp pipeline) needs FP32, even K_local, the kinematic model, the MPPI planner, eps read from memory (SUPPLIED or pre-generated noise) and N <= 56"; return MPPI_EINVAL; }
   }
   MPPI_CUDA(h, cudaMalloc(&h->d_in, B * (MPPI_MAX_NX + 2 * N) * sizeof(double)));
@@ -236,6 +244,7 @@ static int create_impl(mppi_handle* h) {
   MPPI_CUDA(h, cudaMalloc(&h->d_res, B * (RES_SCALARS + 2 * N + (N + 1) * c.n_x) * sizeof(double)));
   h->d_traj = h->d_res + B * (RES_SCALARS + 2 * N);
   if (c.planner == MPPI_PLANNER_DWA) MPPI_CUDA(h, cudaMalloc(&h->d_cand, K * 2 * sizeof(double)));
+  if (h->pipe && !h->scan_ok) MPPI_CUDA(h, cudaMalloc(&h->d_cta_part, size_t(2 * N + 2) * FOLD_MAX_CTAS * sizeof(float)));
   if (h->scan_ok) {
     const int tiles = (h->K_local + SCAN_SPW - 1) / SCAN_SPW;
     const int want = h->sm_count * 3;   // __launch_bounds__(SCAN_BS, 3): one resident wave

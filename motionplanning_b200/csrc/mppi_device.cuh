@@ -141,6 +141,7 @@ struct Buffers {
   // scan-form fused step (mppi_scan.cuh)
   R* cta_part;          // [2N + 2][n_cta] per-CTA softmin partials: 2N weighted control sums ([j][c] interleaved), eta, rho_cta
   int n_cta;            // CTAs of scan_rollout_kernel (columns of cta_part)
+  int fold_off;         // PH_FOLD: byte offset in finalize's dynamic shared memory where cta_part is staged by one bulk copy; 0 = read it from global memory
   unsigned int* ticket; // arrival counter: the last CTA to finish runs the step's tail (fold, exchange, combine, nominal rollout)
   int tail_in_kernel;   // 1: that tail runs inside scan_rollout_kernel's last CTA; 0: finalize_kernel<PH_FOLD|...> follows as its own launch
 };

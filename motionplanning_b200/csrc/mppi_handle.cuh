@@ -57,6 +57,7 @@ struct mppi_handle {
   bool cutoff = false;
   bool packed = false;   // rollout carries two samples per thread as f32x2 (FP32, even K_local)
   bool packed_seq = false;   // the SEQUENTIAL rollout packs (a handle may use the pipeline below the packing threshold and fall back to one-sample threads)
+  bool pipe_fold = false;   // ... whose blocks also do their share of the softmin update (no update_kernel in the step; pipe_folds)
   bool pipe = false;     // ... and, where the step qualifies (pipe_eligible), as the two-stage warp pipeline of mppi_pipe.cuh
   std::vector<double> circles, blocks;   // host copies (3 x Mc, 5 x Mp col-major)
   // device
@@ -292,6 +293,7 @@ Buffers<R> make_buffers(const mppi_handle* h) {
   b.ref = static_cast<const R*>(h->d_ref);
   b.cta_part = (R*)h->d_cta_part;
   b.n_cta = h->scan_ctas;
+  b.fold_off = 0;
   b.ticket = h->d_ticket;
   b.tail_in_kernel = 0;
   return b;

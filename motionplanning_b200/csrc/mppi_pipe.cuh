@@ -87,7 +87,73 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-template <int NQ>
+// FOLD tail: this block's share of the weighted control update, all eight warps.  Called at the END of the producer branch and at
+// the end of the consumer branch (two call sites, each followed by the thread's exit, instead of one behind the re-joined
+// branches: with a common continuation the compiler wraps both stage loops in convergence barriers and the 50-step walk gets
+// 2 us slower).  The block barrier is the same barrier 0 from both sites.
+__device__ __forceinline__ void pipe_fold_tail(const StaticParams<float>& p, const Buffers<float>& buf, const PipeHot& sh, const float4* sU, float4* slab,
+                                               uint64_t* s_bar, const float2* s_w, const float* s_eta, const unsigned long long* s_key,
+                                               const float2* src, uint32_t row_bytes) {
+  const int N = p.N, K = p.K_local, t = threadIdx.x, lane = t & 31, wid = t >> 5;
+  // Every consumer warp is past its last read of the slab (barrier 1, all 256 threads, at the call sites): fetch the eps again, rows
+  // in the same groups on the same barriers (second phase).  ALL eight warps issue, a group of 8 rows each: a bulk copy issued by a
+  // lane costs ~60 cycles of its warp, and 50 of them from one warp put 1.7 us in front of the sums.
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  for (int g = wid; g * EPS_GROUP < N; g += PIPE_BS / 32) {
+    const int j0 = g * EPS_GROUP, j1 = min(j0 + EPS_GROUP, N);
+    if (lane == 0) mbar_arrive_expect_tx(&s_bar[g], row_bytes * uint32_t(j1 - j0));
+    __syncwarp();
+    const int j = j0 + lane;
+    if (j < j1) bulk_load(slab + size_t(j) * (PIPE_SAMPLES / 2), src + size_t(j) * K, row_bytes, &s_bar[g]);
+  }
+  __syncthreads();                                        // weights and eta are in shared memory
+  trace_begin(buf.dbg, buf.trace, 1);
+  {
+    const int n_cta = gridDim.x, cta = blockIdx.x;
+    float* part = buf.cta_part + cta;
+    const float CL0 = sh.CL0, CU0 = sh.CU0, CL1 = sh.CL1, CU1 = sh.CU1;
+    float2 wv[PIPE_PAIRS_W];
+#pragma unroll
+    for (int i = 0; i < PIPE_PAIRS_W; ++i) wv[i] = s_w[lane + 32 * i];
+    constexpr int NWARP = PIPE_BS / 32;
+    static_assert(NWARP == EPS_GROUP, "warp w sums rows w, w + 8, ...: one row of every copy group");
+    for (int j = wid; j < N; j += NWARP) {
+      mbar_wait(&s_bar[j / EPS_GROUP], 1);
+      const float4 nu = sU[j];
+      float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+      for (int i = 0; i < PIPE_PAIRS_W; ++i) {
+        const float4 e = slab[size_t(j) * (PIPE_SAMPLES / 2) + lane + 32 * i];
+        // the CLAMPED controls are averaged (:187-190 after PushInBounds :13-20); a lane past the last sample carries weight 0 and
+        // whatever the hand-over left in its slot, which max / min turn into a finite number
+        const float ua0 = fminf(fmaxf(nu.x + e.x, CL0), CU0), ua1 = fminf(fmaxf(nu.y + e.y, CL1), CU1);
+        const float ub0 = fminf(fmaxf(nu.x + e.z, CL0), CU0), ub1 = fminf(fmaxf(nu.y + e.w, CL1), CU1);
+        a0 = fmaf(wv[i].y, ub0, fmaf(wv[i].x, ua0, a0));
+        a1 = fmaf(wv[i].y, ub1, fmaf(wv[i].x, ua1, a1));
+      }
+      a0 = warp_sum(a0);
+      a1 = warp_sum(a1);
+      if (lane == 0) { part[size_t(2 * j) * n_cta] = a0; part[size_t(2 * j + 1) * n_cta] = a1; }
+    }
+    if (t == 0) {
+      float eta = 0.f;
+      unsigned long long kc = s_key[0];
+#pragma unroll
+      for (int i = 0; i < PIPE_PAIRS_W; ++i) { eta += s_eta[i]; kc = s_key[i] < kc ? s_key[i] : kc; }
+      part[size_t(2 * N) * n_cta] = eta;
+      part[size_t(2 * N + 1) * n_cta] = key_cost(kc, 0.f);
+    }
+  }
+  trace_end(buf.dbg, buf.trace, 1);
+}
+
+// FOLD: the block also does its share of the softmin update (MPPIUtils.jl:154-167,186-190) before it leaves, so the step needs no
+// update_kernel: weights against the BLOCK's own minimum, the eps slab fetched a second time into the same shared memory (the
+// hand-over has overwritten it; the lines are L2 hits, the block read them a few microseconds ago), every warp sums a few horizon
+// rows over the block's 256 samples, and the block leaves one column of Buffers::cta_part ([2N + 2][n_cta]: weighted control sums,
+// eta, rho of the block) that finalize folds against the global minimum (PH_FOLD) — the softmin combine of the multi-GPU step,
+// applied once more inside the GPU.  No cut-off (the cut needs all costs before any weight).
+template <int NQ, bool FOLD>
 __global__ void __launch_bounds__(PIPE_BS, 2)
 rollout_pipe_kernel(const __grid_constant__ StaticParams<float> p, const Buffers<float> buf) {
   using V = f32x2;
@@ -102,6 +168,8 @@ rollout_pipe_kernel(const __grid_constant__ StaticParams<float> p, const Buffers
   __shared__ unsigned long long s_key[PIPE_PAIRS_W];
   __shared__ int s_feas[PIPE_PAIRS_W];
   __shared__ float s_x0[8];
+  __shared__ float2 s_w[FOLD ? PIPE_BS / 2 : 1];                              // FOLD: softmin weights of the block's samples, per pair
+  __shared__ float s_eta[PIPE_PAIRS_W];
 
   const int N = p.N, K = p.K_local, b = blockIdx.y;
   const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
@@ -193,6 +261,10 @@ rollout_pipe_kernel(const __grid_constant__ StaticParams<float> p, const Buffers
     s_handA[pair] = make_float4(stage.v.x, stage.v.y, viol.v.x, viol.v.y);
     mbar_arrive(&s_prog[w][(N - 1) / PIPE_HAND]);         // last unit + the partial sums
     pdl_trigger();
+    if (FOLD) {
+      asm volatile("bar.sync 1, %0;" ::"n"(PIPE_BS) : "memory");   // the consumers have finished with the slab
+      pipe_fold_tail(p, buf, sh, sU, slab, s_bar, s_w, s_eta, s_key, src, row_bytes);
+    }
     return;
   }
 
@@ -260,7 +332,19 @@ rollout_pipe_kernel(const __grid_constant__ StaticParams<float> p, const Buffers
   key = warp_min_u64(key);
   n_feas = warp_sum(n_feas);
   if (lane == 0) { s_key[w] = key; s_feas[w] = n_feas; }
-  asm volatile("bar.sync 1, 128;" ::: "memory");          // the four consumer warps only: the producers have left
+  if (FOLD) asm volatile("bar.sync 1, %0;" ::"n"(PIPE_BS) : "memory");   // with the producers, which wait here to help with the tail
+  else asm volatile("bar.sync 1, 128;" ::: "memory");     // the four consumer warps only: the producers have left
+  if (FOLD) {
+    unsigned long long kc = s_key[0];
+#pragma unroll
+    for (int i = 1; i < PIPE_PAIRS_W; ++i) kc = s_key[i] < kc ? s_key[i] : kc;
+    const float rho_c = key_cost(kc, 0.f);
+    const float w0 = (k < K) ? Math<float>::exp((rho_c - M::lane(cost, 0)) * p.inv_lambda) : 0.f;       // CalculateMPPIWeights (:154-167)
+    const float w1 = (k + 1 < K) ? Math<float>::exp((rho_c - M::lane(cost, 1)) * p.inv_lambda) : 0.f;
+    s_w[pair] = make_float2(w0, w1);
+    const float es = warp_sum(w0 + w1);
+    if (lane == 0) s_eta[w] = es;
+  }
   if (t == PIPE_BS / 2) {
     int f = 0;
 #pragma unroll
@@ -270,6 +354,7 @@ rollout_pipe_kernel(const __grid_constant__ StaticParams<float> p, const Buffers
     if (buf.trace) atomicMax(&buf.dbg[9], globaltimer_ns());
   }
   pdl_trigger();
+  if (FOLD) pipe_fold_tail(p, buf, sh, sU, slab, s_bar, s_w, s_eta, s_key, src, row_bytes);
 }
 
 }  // namespace mppi

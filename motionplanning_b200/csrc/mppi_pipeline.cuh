@@ -122,16 +122,23 @@ inline cudaError_t launch_scan(int N, int n_circles, dim3 grid, size_t smem, cud
 inline bool pipe_eligible(const mppi_handle* h) {
   return h->pipe && h->ref_path.empty() && h->blocks.empty() && h->circles.size() / 3 <= size_t(HOT_CIRCLES);
 }
-inline cudaError_t launch_pipe(int n_circles, dim3 grid, size_t smem, cudaStream_t s, bool dependent, const StaticParams<float>& p, const Buffers<float>& buf) {
+// ... and its block also does its share of the softmin update (rollout_pipe_kernel<., true>), so the step has no update_kernel: no
+// cut-off (the cut needs every cost before any weight), one column of cta_part per block
+inline bool pipe_folds(const mppi_handle* h) {
+  return pipe_eligible(h) && h->pipe_fold && !h->cutoff && (h->K_local + PIPE_SAMPLES - 1) / PIPE_SAMPLES <= FOLD_MAX_CTAS;
+}
+template <int NQ, bool FOLD>
+cudaError_t launch_pipe_nq(dim3 grid, size_t smem, cudaStream_t s, bool dependent, const StaticParams<float>& p, const Buffers<float>& buf) {
   static unsigned long long prepared = 0;
   if (first_on_device(prepared)) {
-    prefer_shared_carveout(rollout_pipe_kernel<3>);
-    prefer_shared_carveout(rollout_pipe_kernel<8>);
-    cudaFuncSetAttribute(rollout_pipe_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, PIPE_SLAB_MAX + 8192);
-    cudaFuncSetAttribute(rollout_pipe_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, PIPE_SLAB_MAX + 8192);
+    prefer_shared_carveout(rollout_pipe_kernel<NQ, FOLD>);
+    cudaFuncSetAttribute(rollout_pipe_kernel<NQ, FOLD>, cudaFuncAttributeMaxDynamicSharedMemorySize, PIPE_SLAB_MAX + 8192);
   }
-  if (n_circles <= 3) return launch_step_kernel(rollout_pipe_kernel<3>, grid, dim3(PIPE_BS), smem, s, dependent, p, buf);
-  return launch_step_kernel(rollout_pipe_kernel<8>, grid, dim3(PIPE_BS), smem, s, dependent, p, buf);
+  return launch_step_kernel(rollout_pipe_kernel<NQ, FOLD>, grid, dim3(PIPE_BS), smem, s, dependent, p, buf);
+}
+inline cudaError_t launch_pipe(int n_circles, bool fold, dim3 grid, size_t smem, cudaStream_t s, bool dependent, const StaticParams<float>& p, const Buffers<float>& buf) {
+  if (fold) return n_circles <= 3 ? launch_pipe_nq<3, true>(grid, smem, s, dependent, p, buf) : launch_pipe_nq<8, true>(grid, smem, s, dependent, p, buf);
+  return n_circles <= 3 ? launch_pipe_nq<3, false>(grid, smem, s, dependent, p, buf) : launch_pipe_nq<8, false>(grid, smem, s, dependent, p, buf);
 }
 
 template <class R, class Model, int SRC>
@@ -193,7 +200,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   }
   if (timed == 1) MPPI_CUDA(h, cudaEventRecord(h->ev[5], s));   // the rollout's interval starts after the inputs are staged
   // ---- scan-form fused step: rollout + cost + online softmin + weighted sum in ONE kernel whose last CTA also runs the tail ----
-  bool scan_done = false, scan_tail = false;
+  bool scan_done = false, scan_tail = false, folded = false;   // folded: the pipeline kernel left per-block softmin partials, no update_kernel
   if constexpr (std::is_same<R, float>::value && std::is_same<Model, Kin5<float>>::value && SRC != SRC_DWA) {
     if ((v & V_LOCAL) && (v & V_SCAN)) {
       const int C = scan_chunk(N);
@@ -215,6 +222,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   }
   if ((v & V_LOCAL) && !scan_done) {
     bool launched = pregen, piped = false;
+    folded = false;
     if constexpr (std::is_same<R, float>::value && SRC != SRC_DWA) {
       if (h->cfg.strict_math) {   // verification flavour: the reference's operation sequence in unfused IEEE FP32 (mppi_strict.cuh); reads eps
         if (SRC == SRC_PHILOX) {
@@ -231,7 +239,10 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
     if constexpr (std::is_same<R, float>::value && std::is_same<Model, Kin5<float>>::value && SRC != SRC_DWA) {
       if (!h->cfg.strict_math && (SRC == SRC_SUPPLIED || pregen) && pipe_eligible(h)) {   // two-stage warp pipeline: stage A / stage B warps per sample pair
         const size_t smemP = ((size_t(N) * 16 + 127) & ~size_t(127)) + size_t(N) * PIPE_SAMPLES * 8;
-        MPPI_CUDA(h, launch_pipe(p.n_circles, dim3((K + PIPE_SAMPLES - 1) / PIPE_SAMPLES, B), smemP, s, pdl_in, p, buf));
+        const dim3 pgrid((K + PIPE_SAMPLES - 1) / PIPE_SAMPLES, B);
+        folded = pipe_folds(h);
+        if (folded) buf.n_cta = int(pgrid.x);
+        MPPI_CUDA(h, launch_pipe(p.n_circles, folded, pgrid, smemP, s, pdl_in, p, buf));
         launched = piped = true;
       }
     }
@@ -292,7 +303,7 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
       h->launches++;
     }
     if (timed) MPPI_CUDA(h, cudaEventRecord(h->ev[1], s));
-    if (SRC != SRC_DWA) {
+    if (SRC != SRC_DWA && !folded) {
       const int ngroups = (N + UPDATE_JG - 1) / UPDATE_JG;
       dim3 ug(h->ksplit, h->jsplit, B);
       const size_t smemR = size_t((ngroups + h->jsplit - 1) / h->jsplit) * (UPDATE_BS / 32) * 2 * UPDATE_JG * sizeof(R);
@@ -314,20 +325,29 @@ int enqueue_variant(mppi_handle* h, int v, int timed) {   // timed: 1 = all even
   const size_t smemF = (RES_SCALARS + 2 * size_t(N) + size_t(N + 1) * Model::NX + plen) * sizeof(double) +
                        (size_t(N) * 6 + size_t(N + 1) * (Model::NX + 2 + 3 + 1) + size_t(2) * p.n_ref) * sizeof(R);
   const size_t smemX = smemF + size_t(h->n_ranks) * plen * sizeof(double);
-  if (scan_done) {
+  if (scan_done || folded) {
     if constexpr (std::is_same<R, float>::value && std::is_same<Model, Kin5<float>>::value && SRC != SRC_DWA) {
+      const bool dep = folded && pdl_final;   // behind the pipeline kernel finalize is its programmatic dependent, as it is behind update_kernel
+      // the per-block partial table staged in finalize's shared memory by one bulk copy, when it fits behind the block's own data
+      const size_t tab = ((size_t(2 * N + 2) * size_t(buf.n_cta) * sizeof(R)) + 15) & ~size_t(15);
+      const bool xf = (v & V_XFINAL) != 0;
+      const size_t base = ((xf ? smemX : smemF) + 15) & ~size_t(15);
+      const bool stage = folded && B == 1 && base + tab <= size_t(200) * 1024;
+      if (stage) buf.fold_off = int(base);
+      const size_t smF = stage ? base + tab : smemF, smX = stage ? base + tab : smemX;
       if (!scan_tail && (v & V_FUSED_FINAL)) {
-        MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_FOLD | PH_COMBINE>(B, smemF, s, false, p, buf)));
+        MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_FOLD | PH_COMBINE>(B, smF, s, dep, p, buf)));
         h->launches++;
       }
-      if (!scan_tail && (v & V_XFINAL)) {
-        MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_FOLD | PH_XCHG | PH_COMBINE>(B, smemX, s, false, p, buf)));
+      if (!scan_tail && xf) {
+        MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_FOLD | PH_XCHG | PH_COMBINE>(B, smX, s, dep, p, buf)));
         h->launches++;
       }
       if (v & V_PARTIAL) {
-        MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_FOLD>(B, smemF, s, false, p, buf)));
+        MPPI_CUDA(h, (launch_finalize<R, Model, SRC, PH_FOLD>(B, smF, s, dep, p, buf)));
         h->launches++;
       }
+      buf.fold_off = 0;
     }
   } else {
   if (v & V_FUSED_FINAL) {
@@ -415,7 +435,9 @@ inline int kernels_in(const mppi_handle* h, int v) {
     return n;
   }
   if ((v & V_LOCAL) && h->cfg.strict_math && h->cfg.noise_mode == MPPI_NOISE_PHILOX && !dwa) n++;   // strict flavour draws its noise ahead of the rollout
-  if (v & V_LOCAL) n += 1 + ((h->cutoff && !dwa) ? 1 : 0) + (dwa ? 0 : 1);
+  const bool reads_eps = h->cfg.noise_mode == MPPI_NOISE_SUPPLIED || (v & V_PREGEN);
+  const bool folded = (v & V_LOCAL) && !dwa && !h->cfg.strict_math && reads_eps && pipe_folds(h);
+  if (v & V_LOCAL) n += 1 + ((h->cutoff && !dwa) ? 1 : 0) + ((dwa || folded) ? 0 : 1);
   if ((v & V_LOCAL) && (v & V_PREGEN)) n += 1 + ((v & V_NOISE_NOW) ? 1 : 0);
   if (v & V_FUSED_FINAL) n++;
   if (v & V_XFINAL) n++;

@@ -385,6 +385,22 @@ __device__ __forceinline__ void finalize_block(const StaticParams<R>& p, const B
     }
   }
   if (wait_prev) pdl_wait();   // the loads above do not depend on the update kernel; everything below does
+  // PH_FOLD: the per-block partial table and its rho row are asked for BEFORE the scratch is read, so that the three fetches share
+  // one L2 round trip.  Staged form (the table fits beside this block's own shared memory: buf.fold_off != 0): ONE bulk copy brings
+  // the whole table into shared memory.  (Lanes across CTAs with a load loop per column took 8.7 us at 256 CTAs: eight dependent
+  // round trips per column, four columns per warp.)
+  __shared__ __align__(8) uint64_t s_fbar;
+  R fold_rc0 = R(0);
+  if (PHASES & PH_FOLD) {
+    const uint32_t bytes = (uint32_t(2 * N + 2) * uint32_t(buf.n_cta) * uint32_t(sizeof(R)) + 15u) & ~15u;   // the buffer is FOLD_MAX_CTAS wide: the round-up stays inside
+    if (buf.fold_off != 0 && t == 0) {
+      mbar_init(&s_fbar, 1);
+      mbar_init_fence();
+      mbar_arrive_expect_tx(&s_fbar, bytes);
+      bulk_load(smem_raw + buf.fold_off, buf.cta_part, bytes, &s_fbar);
+    }
+    if (t < buf.n_cta) fold_rc0 = buf.cta_part[size_t(2 * N + 1) * buf.n_cta + t];
+  }
   const Scratch sc = buf.scratch[b];
   constexpr bool PART_TO_GLOBAL = !(PHASES & PH_COMBINE);   // only a partial-only launch has a consumer outside this block
   double* pdst = PART_TO_GLOBAL ? part : sOwn;
@@ -397,15 +413,18 @@ __device__ __forceinline__ void finalize_block(const StaticParams<R>& p, const B
     const int n_cta = buf.n_cta;
     const R* Cp = buf.cta_part;
     const double rho = double(key_cost(sc.rho_key, R(0)));
+    const int lane = t & 31, wid = t >> 5;
+    constexpr int NW = BS / 32;
+    const bool staged = buf.fold_off != 0;
+    const R* tab = staged ? reinterpret_cast<const R*>(smem_raw + buf.fold_off) : Cp;
     for (int c = t; c < n_cta; c += BS) {
-      const double rc = double(Cp[size_t(2 * N + 1) * n_cta + c]);
+      const double rc = double(c == t ? fold_rc0 : Cp[size_t(2 * N + 1) * n_cta + c]);
       s_cscale[c] = (rc < 1e300 && rc == rc) ? exp(-(rc - rho) / double(p.lambda)) : 0.0;   // a CTA that saw no sample carries rho = +inf
     }
     __syncthreads();
-    const int lane = t & 31, wid = t >> 5;
-    constexpr int NW = BS / 32;
+    if (staged) mbar_wait(&s_fbar, 0);
     for (int col = wid; col <= 2 * N; col += NW) {
-      const R* src = Cp + size_t(col) * n_cta;
+      const R* src = tab + size_t(col) * n_cta;
       double s0 = 0.0;
       for (int c = lane; c < n_cta; c += 32) s0 += double(src[c]) * s_cscale[c];
       s0 = warp_sum(s0);

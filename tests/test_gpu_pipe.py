@@ -146,3 +146,76 @@ def test_pipe_falls_back_where_it_does_not_apply(built):
     a7, k7, c7, b7 = sc.config(3, K=4096)
     with pytest.raises(m.MPPIError, match="two-stage warp pipeline"):
         m.defineMPPI(*a7, **dict(k7, precision=capi.FP32, noise_mode=capi.NOISE_PHILOX, rollout_variant=6))
+
+
+# ---- rollout_variant 7: the pipeline's blocks also do the softmin update (no update_kernel), finalize folds one partial per block ----
+@pytest.mark.parametrize("K,N", [(1024, 50), (1022, 50), (4096, 23), (770, 8), (64, 1), (65536, 50)])
+def test_pipe_with_in_block_update_matches_oracle(built, K, N):
+    """Whole MPPIPlan on supplied noise (MPPIUtils.jl:154-167 weights, :186-190 weighted sum of the clamped controls): per-block
+    weights against the block's own minimum, rescaled against the global one in finalize; ragged last block, N = 1."""
+    args, kw, circles, blocks = _args(K, N)
+    mppi, ref = run_pair(args, dict(kw, rollout_variant=7), circles, blocks, capi.FP32, Unom=warm_nominal(N))
+    assert mppi.plan_info()["packed"] == 3
+    check(mppi, ref, capi.FP32)
+
+
+def test_pipe_in_block_update_equals_update_kernel(built):
+    """Same noise through variant 7 and variant 6 (pipeline + update_kernel): identical costs and flags (same rollout code), U_new to
+    FP32 rounding (different partition of the weighted sum), one kernel fewer per step; Philox chain of four iterations."""
+    args, kw, circles, blocks = _args(16384, 50, x0=[38.0, -1.0, 0.05, 8.0, 0.02])
+    kw = dict(kw, precision=capi.FP32, noise_mode=capi.NOISE_PHILOX)
+    a = m.defineMPPI(*args, **dict(kw, rollout_variant=7))
+    b = m.defineMPPI(*args, **dict(kw, rollout_variant=6))
+    for mp in (a, b):
+        m.defineMPPIobs(mp, circles)
+    Ua = Ub = np.zeros((50, 2))
+    for it in range(4):
+        m.defineMPPINominalControl(a, Ua); m.MPPIPlan(a)
+        m.defineMPPINominalControl(b, Ub); m.MPPIPlan(b)
+        if it == 0:
+            assert np.array_equal(a.p.costs, b.p.costs) and np.array_equal(a.p.flags, b.p.flags)
+        assert a.r.argmin == b.r.argmin and a.r.RolloutCount == b.r.RolloutCount and a.r.FeasibleTrajCount == b.r.FeasibleTrajCount
+        assert np.abs(a.r.Control - b.r.Control).max() < 2e-6 * max(1.0, np.abs(b.r.Control).max())
+        assert abs(a.r.cost - b.r.cost) <= 1e-5 * abs(b.r.cost)
+        Ua, Ub = a.r.Control.copy(), b.r.Control.copy()
+    assert np.array_equal(a.noise(), b.noise())
+    n0 = a.launch_count(); m.MPPIPlan(a); na = a.launch_count() - n0
+    n0 = b.launch_count(); m.MPPIPlan(b); nb = b.launch_count() - n0
+    assert na == nb - 1
+    a.close(); b.close()
+
+
+@pytest.mark.parametrize("G", [2, 4])
+def test_pipe_in_block_update_across_shards(built, G):
+    """One handle, G logical shards (and real GPUs when the box has them): every shard folds its own blocks' partials, the peer
+    exchange combines the shards (PH_FOLD | PH_XCHG | PH_COMBINE)."""
+    import torch
+    args, kw, circles, blocks = _args(8192, 50)
+    kw = dict(kw, precision=capi.FP32, noise_mode=capi.NOISE_PHILOX)
+    one = m.defineMPPI(*args, **dict(kw, rollout_variant=6))
+    m.defineMPPIobs(one, circles)
+    m.MPPIPlan(one)
+    for ids in [[0] * G] + ([list(range(G))] if torch.cuda.device_count() >= G else []):
+        mp = m.defineMPPI(*args, **dict(kw, rollout_variant=7, n_gpus=G, device_ids=ids))
+        m.defineMPPIobs(mp, circles)
+        m.MPPIPlan(mp)
+        assert np.array_equal(mp.p.costs, one.p.costs) and mp.r.argmin == one.r.argmin
+        assert np.abs(mp.r.Control - one.r.Control).max() < 2e-6 * max(1.0, np.abs(one.r.Control).max())
+        mp.close()
+    one.close()
+
+
+def test_pipe_in_block_update_needs_no_cutoff(built):
+    args, kw, circles, blocks = _args(4096, 50)
+    with pytest.raises(m.MPPIError, match="no feasibility cut-off"):
+        m.defineMPPI(*args, **dict(kw, precision=capi.FP32, noise_mode=capi.NOISE_PHILOX, rollout_variant=7, FeasibilityCount=100))
+    mp = m.defineMPPI(*args, **dict(kw, precision=capi.FP32, noise_mode=capi.NOISE_PHILOX, rollout_variant=7))
+    m.defineMPPIobs(mp, circles)
+    assert mp.plan_info()["packed"] == 3
+    m.defineMPPIblocks(mp, sc.PARKING_BLOCKS)   # a wall arrives: sequential packed rollout + update_kernel from the next step on
+    assert mp.plan_info()["packed"] == 1
+    m.MPPIPlan(mp)
+    m.defineMPPIblocks(mp, [])
+    assert mp.plan_info()["packed"] == 3
+    m.MPPIPlan(mp)
+    mp.close()

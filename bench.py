@@ -272,7 +272,7 @@ def parity_across_ranks(m, mdist, args, kw, circles, blocks, exchange, rank, wor
         mdist.init_library_comm(sh)
     info = sh.plan_info()
     kw_ref = dict(kw, k_offset=0, K_local=0)
-    kw_ref["rollout_variant"] = 5 if info["scan"] else ({3: 7, 2: 6, 1: 2}.get(info["packed"], 1))   # 6 = two-stage warp pipeline, 2 = packed sequential
+    kw_ref["rollout_variant"] = 5 if info["scan"] else ({3: 6, 2: 6, 1: 2}.get(info["packed"], 1))   # 3 (in-block update) -> 6: same rollout, and K_total may exceed variant 7's block limit   # 6 = two-stage warp pipeline, 2 = packed sequential
     kw_ref["noise_policy"] = 1 if info["pregen"] else 2
     ref = m.defineMPPI(*args, **kw_ref)
     if circles:

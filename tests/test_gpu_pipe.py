@@ -219,3 +219,52 @@ def test_pipe_in_block_update_needs_no_cutoff(built):
     assert mp.plan_info()["packed"] == 3
     m.MPPIPlan(mp)
     mp.close()
+
+
+def test_pipe_in_block_update_split_phase_and_device_loops(built):
+    """The other callers of the step with variant 7: split-phase shards on supplied noise (PH_FOLD alone -> exchange format ->
+    combine), the device-resident chain (mppi_step_async with adopt) and the closed loop on the device (main.jl:58-83)."""
+    from motionplanning_b200 import dist as mdist
+    K, N, G = 4096, 50, 2
+    args, kw, circles, blocks = _args(K, N)
+    eps = orc.generate_noise(args[6], sc.SEED, 0, K, N, capi.FP64).astype(np.float32)
+    U = warm_nominal(N)
+    kws = dict(kw, precision=capi.FP32, noise_mode=capi.NOISE_SUPPLIED)
+    whole = m.defineMPPI(*args, **dict(kws, rollout_variant=6))
+    m.defineMPPIobs(whole, circles)
+    m.defineMPPINominalControl(whole, U)
+    m.MPPIPlan(whole, eps)
+    shards, partials = [], []
+    for g in range(G):
+        off, kl = mdist.shard_range(K, g, G)
+        s = m.defineMPPI(*args, **dict(kws, rollout_variant=7, k_offset=off, K_local=kl))
+        m.defineMPPIobs(s, circles)
+        m.defineMPPINominalControl(s, U)
+        assert s.plan_info()["packed"] == 3
+        partials.append(s.step_local(np.ascontiguousarray(eps[:, off:off + kl, :])))
+        shards.append(s)
+    assert np.array_equal(np.concatenate([s.p.costs for s in shards]), whole.p.costs)
+    for s in shards:
+        s.step_combine(partials)
+        assert s.r.argmin == whole.r.argmin and s.r.RolloutCount == whole.r.RolloutCount and s.r.rho == whole.r.rho
+        assert np.abs(s.r.Control - whole.r.Control).max() <= 2e-6 * max(1.0, np.abs(whole.r.Control).max())
+        s.close()
+    whole.close()
+    # device-resident loops, Philox noise
+    kwp = dict(kw, precision=capi.FP32, noise_mode=capi.NOISE_PHILOX)
+    a = m.defineMPPI(*args, **dict(kwp, rollout_variant=7))
+    b = m.defineMPPI(*args, **dict(kwp, rollout_variant=6))
+    for mp in (a, b):
+        m.defineMPPIobs(mp, circles)
+        m.MPPIPlan(mp)
+        for _ in range(4):
+            mp.step_async(adopt=True)
+        mp.sync()
+        mp.fetch_result()
+    assert a.r.argmin == b.r.argmin
+    assert np.abs(a.r.Control - b.r.Control).max() <= 1e-4 * max(1.0, np.abs(b.r.Control).max())   # five chained FP32 updates
+    ha, la = a.run_closed_loop(max_iters=4, plant_steps=20)
+    hb, lb = b.run_closed_loop(max_iters=4, plant_steps=20)
+    assert ha.shape == hb.shape and np.isfinite(ha).all()
+    assert np.abs(ha - hb).max() <= 1e-3 * max(1.0, np.abs(hb).max())
+    a.close(); b.close()

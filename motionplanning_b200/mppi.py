@@ -74,18 +74,41 @@ class MPPIPlanner:  # types.jl:32-34
         return self._m._sample_xy(stride)
 
 
-@dataclass
 class MPPIResult:  # types.jl:36-44
-    Traj: np.ndarray = None
-    Control: np.ndarray = None
-    Feasibility: str = "InFeasible"
-    cost: float = 1e6
-    time: float = 0.0
-    FeasibleTrajCount: int = 0
-    RolloutCount: int = 0
-    argmin: int = 0
-    rho: float = 0.0
-    eta: float = 0.0
+    """mppi.r of the reference.  `Control` and `Traj` are fresh arrays per plan, like the reference's; on the per-step path they are
+    copied out of the handle's staging buffers when first READ (a 20 ms control loop reads Control[1, :] and rarely the
+    trajectory: two unconditional copies cost 1 us of every step's host time)."""
+
+    def __init__(self):
+        self._Traj = self._Control = self._pending = None
+        self.Feasibility = "InFeasible"
+        self.cost = 1e6
+        self.time = 0.0
+        self.FeasibleTrajCount = 0
+        self.RolloutCount = 0
+        self.argmin = 0
+        self.rho = 0.0
+        self.eta = 0.0
+
+    @property
+    def Control(self):
+        if self._Control is None and self._pending is not None:
+            self._Control = self._pending[0].copy(order="F")
+        return self._Control
+
+    @Control.setter
+    def Control(self, v):
+        self._Control = v
+
+    @property
+    def Traj(self):
+        if self._Traj is None and self._pending is not None:
+            self._Traj = self._pending[1].copy(order="F")
+        return self._Traj
+
+    @Traj.setter
+    def Traj(self, v):
+        self._Traj = v
 
 
 class MPPISearcher:  # types.jl:46-50
@@ -117,6 +140,10 @@ class MPPISearcher:  # types.jl:46-50
         self._ctrl_buf = np.zeros((cfg.N, 2), dtype=np.float64, order="F")
         self._traj_buf = np.zeros((cfg.N + 1, cfg.n_x), dtype=np.float64, order="F")
         self._ctrl_ptr, self._traj_ptr = self._ctrl_buf.ctypes.data, self._traj_buf.ctypes.data
+        self._pending = (self._ctrl_buf, self._traj_buf)
+        self._res_step = capi.Result()
+        self._res_step.Control, self._res_step.Traj = self._ctrl_ptr, self._traj_ptr
+        self._res_step_ptr = C.addressof(self._res_step)
 
     # -- plumbing ---------------------------------------------------------
     def _check(self, rc):
@@ -464,15 +491,20 @@ def ShiftInitialCondition(mppi, X0):
 
 def MPPIPlan(mppi, noise=None):
     """MPPIPlan (MPPIUtils.jl:169-203).  `noise` (N, K, m) only in SUPPLIED-noise mode."""
+    if noise is None:   # the per-step call (main.jl:61): its own result struct, whose two array addresses are set once
+        res = mppi._res_step
+        if mppi._f_step(mppi._hv, None, mppi._res_step_ptr):
+            mppi._check(1)
+        r = mppi.r   # the staging buffers stay untouched until the next per-step plan, which re-arms this
+        r._Control = r._Traj = None
+        r._pending = mppi._pending
+        r.Feasibility = "Feasible" if res.feasible else "InFeasible"  # MPPIUtils.jl:195
+        r.cost, r.RolloutCount, r.FeasibleTrajCount, r.time = res.cost, res.rollout_count, res.feasible_count, res.time_s  # :196-200
+        r.argmin, r.rho, r.eta = res.argmin_index, res.rho, res.eta
+        return None
     cfg = mppi._cfg
     N, nx = cfg.N, cfg.n_x
     res = mppi._res
-    if noise is None:   # the per-step call (main.jl:61)
-        res.Control, res.Traj = mppi._ctrl_ptr, mppi._traj_ptr
-        if mppi._f_step(mppi._hv, None, mppi._res_ptr):
-            mppi._check(1)
-        _store(mppi, res, mppi._ctrl_buf.copy(order="F"), mppi._traj_buf.copy(order="F"))
-        return None
     ctrl = np.empty((N, 2), dtype=np.float64, order="F")
     traj = np.empty((N + 1, nx), dtype=np.float64, order="F")
     res.Control, res.Traj = ctrl.ctypes.data, traj.ctypes.data

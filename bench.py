@@ -505,6 +505,18 @@ def run_ours(a, rank, world, local_rank):
     e2e_value = units_per_step * a.steps / e2e_total
     h2d = B * (nx + 2 * N) * 8
     d2h = B * (8 + 2 * N) * 8 + (0 if batched else (N + 1) * nx * 8)
+    # ---- the same three calls made by a COMPILED caller (what Julia's ccall pays): timed inside the library with the host's steady
+    #      clock, nothing but mppi_set_x0 + mppi_set_nominal + mppi_step in the span, L2 flushed before every span
+    #      (mppi_time_reference_calls).  The e2e key above stays the Python mirror's number; this one isolates the interpreter's share. ----
+    c_abi = None
+    if not batched and world == 1:
+        torch.cuda.synchronize()
+        res_us, idle_us = mppi.time_reference_calls(x_host, U_host, a.steps + 3, flush.data_ptr(), flush.numel())
+        c_abi = {"result_median_us": float(np.median(res_us[3:])), "result_p99_us": float(np.percentile(res_us[3:], 99)),
+                 "idle_median_us": float(np.median(idle_us[3:])),
+                 "value": units_per_step * a.steps / float(np.sum(idle_us[3:]) * 1e-6), "unit": UNIT,
+                 "source": "mppi_time_reference_calls: mppi_set_x0 + mppi_set_nominal + mppi_step from host buffers, host steady clock inside the library, "
+                           "L2 flushed before every span; `value` counts every span to stream idle like the e2e key"}
     # ---- per-kernel times: eager launches bracketed by CUDA events on the library stream (mppi_set_profiling(1)); the L2
     #      flush is enqueued on the same stream right before, without a host synchronise in between, so the events do not
     #      also time an idle GPU's launch latency.  The scan-form step launches its tail as a separate kernel in this mode. ----
@@ -596,6 +608,7 @@ def run_ours(a, rank, world, local_rank):
                     "span": "call start -> result in host memory -> handle's stream idle (the tail a step leaves behind its result is inside)",
                     "api": ("mppi_step_batched (host x0s/Us in, Us_out/costs/feasible out, synchronous)" if batched else
                             "ShiftInitialCondition + defineMPPINominalControl + MPPIPlan (host buffers, synchronous)")},
+            "e2e_c_abi": c_abi,
             "gpu_launches": int(launches),
             "kernels_us": {"rollout_cost": float(k_us[0]), "softmin_update": float(k_us[1]), "finalize_nominal": float(k_us[2]),
                            "step_eager": float(k_us[3]),

@@ -335,6 +335,17 @@ int32_t mppi_check_poses_static(mppi_handle_t* h, const double* poses, int32_t n
  * (denominator of the rollout kernel's roofline) */
 int32_t mppi_measure_fp32_peak(mppi_handle_t* h, double* tflops);
 
+/* Measurement aid (no counterpart in the reference): the per-iteration call sequence of OptimalControl/MPPI/main.jl:59-61 —
+ * mppi_set_x0 (ShiftInitialCondition), mppi_set_nominal (defineMPPINominalControl!), mppi_step (MPPIPlan) — made n times from
+ * HOST buffers x0 [n_x] and U [N x 2 col-major], each iteration timed with the host's steady clock and NOTHING but those three
+ * entry points inside the timed span: what a compiled caller (Julia's ccall) pays, without the interpreter overhead of the
+ * Python mirror.  result_us[i] = call start -> mppi_step returned (the plan is in host memory); idle_us[i] = ... -> the
+ * handle's stream is idle (mppi_sync; includes the next iteration's pre-generated noise).  If flush_dev is non-null, flush_bytes
+ * of device memory at flush_dev are overwritten (and the stream drained) before every timed span, so that the L2 is cold.
+ * Single-instance handles only (B = 1). */
+int32_t mppi_time_reference_calls(mppi_handle_t* h, const double* x0, const double* U, int32_t n, void* flush_dev, size_t flush_bytes,
+                                  double* result_us, double* idle_us);
+
 #ifdef __cplusplus
 }
 #endif

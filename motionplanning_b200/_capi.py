@@ -132,6 +132,7 @@ SIGNATURES = {
     "mppi_check_poses": (_i, [_H, _P(_d), _i, _P(_i)]),
     "mppi_check_poses_static": (_i, [_H, _P(_d), _i, _P(_i)]),
     "mppi_measure_fp32_peak": (_i, [_H, _P(_d)]),
+    "mppi_time_reference_calls": (_i, [_H, _P(_d), _P(_d), _i, C.c_void_p, C.c_size_t, _P(_d), _P(_d)]),
 }
 
 _lib = None

@@ -268,6 +268,16 @@ class MPPISearcher:  # types.jl:46-50
         self._check(self._lib.mppi_measure_fp32_peak(self._h, C.byref(v)))
         return v.value
 
+    def time_reference_calls(self, x0, U, n, flush_ptr=None, flush_bytes=0):
+        """n iterations of mppi_set_x0 + mppi_set_nominal + mppi_step from host buffers, timed inside the library with nothing else in
+        the timed span (what a compiled caller pays); returns (result_us, idle_us) arrays."""
+        xa = np.ascontiguousarray(np.asarray(x0, dtype=np.float64))
+        Ua = np.asfortranarray(np.asarray(U, dtype=np.float64))
+        res, idle = np.zeros(n), np.zeros(n)
+        self._check(self._lib.mppi_time_reference_calls(self._h, _dptr(xa), _dptr(Ua), int(n), C.c_void_p(flush_ptr) if flush_ptr else None,
+                                                        C.c_size_t(int(flush_bytes)), _dptr(res), _dptr(idle)))
+        return res, idle
+
     def check_poses(self, poses):
         """hit count per pose (x, y, psi) against the handle's circles and blocks
         (block_collision_check, HybridAstar/src/hybrid_astar_utils.jl:193-201)."""

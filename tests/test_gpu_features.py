@@ -493,3 +493,25 @@ def test_pregenerated_noise_is_bit_identical_to_in_rollout_philox(built, precisi
     same()
     # the pre-generating handle launched one extra kernel per step (+ one when it had to draw ahead of the rollout)
     assert pre.launch_count() > ref.launch_count()
+
+
+def test_time_reference_calls_measures_the_three_entry_points(built):
+    """mppi_time_reference_calls (measurement aid): n iterations of mppi_set_x0 + mppi_set_nominal + mppi_step from host buffers
+    (main.jl:59-61), timed inside the library; the handle is left as after n ordinary plans."""
+    args, kw, circles, blocks = sc.config(0)
+    a = make(args, kw, circles, blocks)
+    b = make(args, kw, circles, blocks)
+    U = warm_nominal(50)
+    x0 = np.asarray(args[3], dtype=np.float64)
+    res, idle = a.time_reference_calls(x0, U, 4)
+    assert res.shape == (4,) and (res > 0).all() and (idle >= res).all() and (res < 1e5).all()
+    for _ in range(4):
+        m.ShiftInitialCondition(b, x0)
+        m.defineMPPINominalControl(b, U)
+        m.MPPIPlan(b)
+    a.fetch_result()
+    assert np.array_equal(a.r.Control, b.r.Control) and a.r.cost == b.r.cost and a.r.argmin == b.r.argmin
+    args5, kw5, c5, b5 = sc.config(4, K=64)
+    many = m.defineMPPI(*args5, **dict(kw5, B=3))
+    with pytest.raises(m.MPPIError, match="single-instance"):
+        many.time_reference_calls(np.zeros(5), np.zeros((50, 2)), 1)

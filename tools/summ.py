@@ -23,4 +23,5 @@ for path in sys.argv[1:]:
                   f"| graph roll={g.get('rollout_cost', 0):.1f} upd={g.get('softmin_update', 0):.1f} fin={g.get('finalize_nominal', 0):.1f} "
                   f"span={g.get('rollout_start_to_finalize_end', 0):.1f} "
                   f"| fp32frac={d['roofline']['frac']:.3f} ingraph={d['roofline'].get('frac_in_graph') or 0:.3f} hbmfrac={ru.get('frac') or 0:.3f} "
-                  f"value={d['value']:.3e} e2e={d['e2e']['value']:.3e} launches={d.get('gpu_launches')}")
+                  f"value={d['value']:.3e} e2e={d['e2e']['value']:.3e} launches={d.get('gpu_launches')}"
+                  + (f" | c_abi res={d['e2e_c_abi']['result_median_us']:.1f} idle={d['e2e_c_abi']['idle_median_us']:.1f} value={d['e2e_c_abi']['value']:.3e}" if d.get('e2e_c_abi') else ""))

@@ -273,4 +273,15 @@ function MPPIClosedLoop(mppi::MPPISearcher; max_iters = nothing, shift_nominal =
     return his[:, 1:ncols[]], log[:, 1:niters[]]
 end
 
+# Measurement aid (no counterpart in the reference): n iterations of the three per-iteration calls of main.jl:59-61
+# (mppi_set_x0, mppi_set_nominal, mppi_step) from host buffers, each timed inside the library; returns
+# (result_us, idle_us): call start -> plan in host memory, -> the handle's stream idle.
+function TimeReferenceCalls(mppi::MPPISearcher, X0::Vector{Float64}, U::Matrix{Float64}, n::Integer)
+    res = zeros(n); idle = zeros(n)
+    check(mppi.h, ccall((:mppi_time_reference_calls, LIB), Int32,
+                        (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Int32, Ptr{Cvoid}, Csize_t, Ptr{Float64}, Ptr{Float64}),
+                        mppi.h, X0, U, Int32(n), C_NULL, Csize_t(0), res, idle))
+    return res, idle
+end
+
 end # module
